@@ -1,0 +1,26 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLD = os.path.join(ROOT, 'tests', 'golden')
+
+
+def pytest_configure(config):
+    config.addinivalue_line('markers', 'gpu: needs a CUDA device (run on the B200 box)')
+
+
+@pytest.fixture(scope='session')
+def weights():
+    return dict(np.load(os.path.join(GOLD, 'sevennet0_weights.npz')))
+
+
+@pytest.fixture(scope='session')
+def gold():
+    def _load(name):
+        return dict(np.load(os.path.join(GOLD, name)))
+    return _load
