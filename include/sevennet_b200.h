@@ -1,0 +1,160 @@
+/* sevennet_b200.h - C ABI of the B200-native SevenNet message-passing hot path.
+ *
+ * Drop-in boundary: the reference has no FFI of its own - its seam is the Python
+ * nn.Module contract of sevenn.nn (forward(data: Dict[str, Tensor]) -> Dict[str, Tensor]) and, on the
+ * native side, the TorchScript call made by pair_e3gnn.cpp / pair_e3gnn_parallel.cpp.  Every entry
+ * point below is what a binding for one of those call sites needs; each cites the reference
+ * interface it replaces (paths relative to the reference root).
+ *
+ * Conventions: plain pointers and sizes only; all array pointers are DEVICE pointers unless the name
+ * ends in _host; fp32 features in the e3nn irreps-blocked layout [mul, 2l+1] (m fastest); int32
+ * indices; `stream` is a cudaStream_t passed as void*; no allocation happens inside (callers pass
+ * workspaces); every function returns B200_OK (0) or an error code, message via b200_last_error().
+ * There is no CPU fallback: the library needs an sm_100a device.
+ */
+#ifndef SEVENNET_B200_H
+#define SEVENNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_ERR_INVALID 1 /* bad argument / unsupported shape */
+#define B200_ERR_CUDA 2    /* CUDA runtime reported an error  */
+
+#define B200_CUTOFF_POLY 0  /* PolynomialCutoff, sevenn/nn/edge_embedding.py:119-145 */
+#define B200_CUTOFF_XPLOR 1 /* XPLORCutoff,      sevenn/nn/edge_embedding.py:148-173 */
+
+const char* b200_last_error(void);
+int b200_version(void);
+
+/* ---- edge embedding: sevenn/nn/edge_embedding.py:202-230 (EdgeEmbedding.forward) ------------------ */
+typedef struct EdgeParams {
+  int num_basis;      /* BesselBasis.num_basis                       (:80-116) */
+  int cutoff_kind;    /* B200_CUTOFF_*                                        */
+  int normalize_sph;  /* SphericalEncoding(normalize=...)            (:177-198) */
+  float r_cut;        /* cutoff_length                                         */
+  float r_on;         /* XPLOR cutoff_on                                       */
+  float poly_p;       /* PolynomialCutoff p                                    */
+} EdgeParams;
+
+/* edge_vec[E,3] -> edge_length[E] (may be NULL), edge_attr Y[E,9], edge_embedding emb[E,num_basis] */
+int b200_edge_embed_fwd(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* bessel_coeffs,
+                        float* edge_length, float* edge_attr, float* edge_embedding, void* stream);
+/* d edge_vec[E,3] = J^T (d edge_attr[E,9] (NULL ok), d edge_embedding[E,nb] (NULL ok)) */
+int b200_edge_embed_bwd(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* bessel_coeffs,
+                        const float* d_edge_attr, const float* d_edge_embedding, float* d_edge_vec, void* stream);
+
+/* ---- radial MLP: sevenn/nn/convolution.py:97-106 (weight_nn = FullyConnectedNet([nb,H1,H2,wn])) ---- */
+typedef struct MlpDesc {
+  int nb, h1, h2, wn;
+} MlpDesc;
+/* weights in the reference's parameter layout: layer{k}.weight is [in, out] row-major, un-normalised */
+int b200_radial_mlp_fwd(const MlpDesc* d, int64_t n_edges, const float* emb, const float* W0, const float* W1,
+                        const float* W2, float* weight_out, void* stream);
+int b200_radial_mlp_bwd(const MlpDesc* d, int64_t n_edges, const float* emb, const float* W0, const float* W1,
+                        const float* W2, const float* d_weight, float* d_emb, int accumulate, void* stream);
+
+/* ---- convolution: sevenn/nn/convolution.py:105-121 (TensorProduct 'uvu' + message_gather + /denominator) ----
+ * x irreps m0x0e+m1x1e+m2x2e, filter 0e+1e+2e, output keeps l3 <= lout (0 or 2); instruction and slot
+ * order as built by IrrepsConvolution.__init__ (:72-95).  Edges are given as a CSR sorted by
+ * edge_index[0] (the aggregation destination, :112-113): rowptr[n_dst+1], src[E] = edge_index[1]. */
+int b200_conv_dims(int m0, int m1, int m2, int lout, int* weight_numel, int* out_dim);
+int b200_conv_fwd(int m0, int m1, int m2, int lout, int n_dst, const int32_t* rowptr, const int32_t* src,
+                  const float* x, const float* edge_attr, const float* weight, float denominator, float* out,
+                  void* stream);
+/* d weight[E,wn] and d edge_attr[E,9] (component 0 untouched) from d out[n_dst,out_dim] */
+int b200_conv_bwd_edge(int m0, int m1, int m2, int lout, int n_dst, int64_t n_edges, const int32_t* rowptr,
+                       const int32_t* src, const float* x, const float* edge_attr, const float* weight,
+                       const float* d_out, float denominator, float* d_weight, float* d_edge_attr, int accumulate,
+                       void* stream);
+/* d x[n_src,x_dim]; rrowptr[n_src+1] / eid_by_src[E]: CSR of the same edges sorted by source, dst[E] = edge_index[0] */
+int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* rrowptr, const int32_t* eid_by_src,
+                    const int32_t* dst, const float* d_out, const float* edge_attr, const float* weight,
+                    float denominator, float* d_x, void* stream);
+
+/* ---- per-node irreps linear: sevenn/nn/linear.py:46-49 (IrrepsLinear -> e3nn o3.Linear), also
+ *      sevenn/nn/self_connection.py:60-62 (SelfConnectionLinearIntro) ------------------------------- */
+typedef struct LinBlock {
+  int d;        /* 2l+1 */
+  int mul_in, mul_out;
+  int in_off, out_off; /* offsets of the block in the input / output rows */
+  int w_off;           /* offset of W[mul_in, mul_out] in the flat weight vector */
+  float scale;         /* 1/sqrt(fan_in) */
+} LinBlock;
+typedef struct LinDesc {
+  int nblk;
+  LinBlock blk[4];
+  int in_dim, out_dim;
+} LinDesc;
+/* y[n, out block] (+)= scale * x[n, in block] . W ;  transpose=1: x-gradient (roles of in/out swapped, W^T) */
+int b200_irreps_linear(const LinDesc* d, int n_nodes, const float* x, const float* weight, float* y, int transpose,
+                       int accumulate, void* stream);
+/* dW (+)= scale * x^T dy  (flat, reference layout) */
+int b200_irreps_linear_wgrad(const LinDesc* d, int n_nodes, const float* x, const float* dy, float* d_weight,
+                             int accumulate, void* stream);
+
+/* ---- gate: sevenn/nn/equivariant_gate.py:59-61 (e3nn Gate, silu on scalars and gates) --------------- */
+/* in [n, ns+ng+3*m1+5*m2] = [scalars | gates | 1e | 2e], ng = m1+m2; out [n, ns+3*m1+5*m2] */
+int b200_gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, void* stream);
+int b200_gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* d_out, float* d_in, void* stream);
+
+/* ---- node embedding: sevenn/nn/node_embedding.py:39-48 + nn/linear.py:37-44 (one-hot . W / sqrt(n_species)) */
+int b200_embed_fwd(int n_nodes, int n_species, int dim, const int32_t* types, const float* W, float* x, void* stream);
+
+/* ---- rescale + reduce: sevenn/nn/scale.py:67-73, nn/linear.py:76-90 --------------------------------- */
+int b200_rescale_fwd(int n_nodes, const int32_t* types, const float* scaled, const float* scale, const float* shift,
+                     int species_wise, float* atomic_energy, void* stream);
+/* out[c] = sum_n in[n, c], c < ncol <= 8 (fp64 accumulation, deterministic) */
+int b200_colsum(int n_rows, int ncol, const float* in, float* out, void* stream);
+
+/* ---- forces / virial: sevenn/nn/force_output.py:158-215 (ForceStressOutputFromEdge) ----------------- */
+int b200_force_virial(int n_atoms, const int32_t* rowptr, const int32_t* rrowptr, const int32_t* eid_by_src,
+                      const float* edge_vec, const float* d_edge_vec, float* force, float* virial_atom, void* stream);
+
+/* ---- radius graph: sevenn/train/dataload.py:31-68 (ase primitive_neighbor_list 'ijDS' + self-pair filter),
+ *      LAMMPS analogue pair_e3gnn.cpp:155-182.  Two-phase: count (returns E, fills rowptr), then fill. ---- */
+size_t b200_graph_workspace_bytes(int n_atoms);
+int b200_graph_count(int n_atoms, const double* pos, const double* cell_host, const int* pbc_host, double cutoff,
+                     void* workspace, int32_t* rowptr, int64_t* n_edges_host, void* stream);
+int b200_graph_fill(int n_atoms, const double* pos, const double* cell_host, const int* pbc_host, double cutoff,
+                    void* workspace, const int32_t* rowptr, int32_t* src, int32_t* dst, int32_t* shift,
+                    float* edge_vec, uint64_t* tmp_keys /* [E] scratch */, void* stream);
+/* CSR of the same edge list sorted by source (stable in edge id) */
+size_t b200_transpose_workspace_bytes(int n_nodes, int64_t n_edges);
+int b200_csr_transpose(int n_nodes, int64_t n_edges, const int32_t* src, void* workspace, int32_t* rrowptr,
+                       int32_t* eid_by_src, void* stream);
+
+/* ---- whole-model E+F+S: the call PairE3GNN::compute makes (pair_e3gnn.cpp:205-266) and
+ *      SevenNetCalculator.calculate (sevennet_calculator.py:119-157) ---------------------------------- */
+typedef struct B200ModelConfig {
+  int n_layers;
+  int n_species;
+  int lmax;            /* 2 */
+  int mul[8][3];       /* node irreps entering layer t: mul[t][l]; mul[n_layers] = irreps after the last gate */
+  int hidden[2];       /* radial MLP hidden widths */
+  int readout_hidden;  /* reduce_input_to_hidden width */
+  EdgeParams edge;
+  int species_wise_rescale;
+} B200ModelConfig;
+typedef struct B200Model B200Model;
+/* weights_host: the reference state dict flattened in named_parameters() order */
+int b200_model_create(const B200ModelConfig* cfg, B200Model** out);
+int b200_model_set_param(B200Model* m, const char* name, const float* data_host, int64_t numel);
+void b200_model_destroy(B200Model* m);
+size_t b200_model_workspace_bytes(const B200Model* m, int n_atoms, int64_t n_edges);
+/* edge list must be sorted by dst (rowptr); outputs: energy[1], atomic_energy[n], force[n,3], virial[6]
+ * (sum over edges of [rx fx, ry fy, rz fz, rx fy, ry fz, rz fx]; stress = -virial / volume) */
+int b200_model_compute(B200Model* m, int n_atoms, int64_t n_edges, const int32_t* types, const int32_t* rowptr,
+                       const int32_t* src, const int32_t* dst, const float* edge_vec, void* workspace,
+                       size_t workspace_bytes, float* energy, float* atomic_energy, float* force, float* virial,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,627 @@
+// Channel-wise (uvu) Clebsch-Gordan tensor product fused with the weight multiply and the
+// sorted-segment sum to destination atoms, plus its two backward kernels.
+//
+// Reference semantics: sevenn/nn/convolution.py:105-121 (IrrepsConvolution.forward):
+//   message = TensorProduct_uvu(x[edge_src], edge_attr, weight);  x = scatter_sum(message, edge_dst) / denominator
+// No per-edge message or outer product ever reaches HBM: one CTA owns one destination atom (one CSR
+// row), a thread owns one channel u of one input irrep block and a sub-list of its paths, walks the
+// row's edges sequentially and keeps the (2 l3+1) partial sums of each path in registers.  The
+// per-edge coupling matrices M_p[m1][m3] = sum_m2 C_p[m1,m2,m3] Y[m2] are shared by all channels and
+// are staged once per edge in shared memory.
+//
+// Thread layout: blockDim = NG * mulpad, group g = tid / mulpad (warp-uniform), channel u = tid % mulpad.
+#include "cg_generated.cuh"
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int TE = 32;  // edges staged per chunk
+constexpr float kInvSqrt3 = 0.5773502691896258f;
+constexpr float kInvSqrt5 = 0.4472135954999579f;
+
+// ---- compile-time path table ------------------------------------------------------------------
+template <int PID> struct PathT;
+#define B200_PATH(PID, L1_, L2_, L3_, TAB_)                                                \
+  template <> struct PathT<PID> {                                                          \
+    static constexpr int L1 = L1_, L2 = L2_, L3 = L3_, D1 = 2 * L1_ + 1, D3 = 2 * L3_ + 1; \
+    static constexpr int TAB = TAB_; /* offset of M in the per-edge record, -1: trivial */  \
+  };
+B200_PATH(P000, 0, 0, 0, -1)
+B200_PATH(P011, 0, 1, 1, -1)
+B200_PATH(P022, 0, 2, 2, -1)
+B200_PATH(P101, 1, 0, 1, -1)
+B200_PATH(P110, 1, 1, 0, -1)
+B200_PATH(P111, 1, 1, 1, 12)
+B200_PATH(P112, 1, 1, 2, 24)
+B200_PATH(P121, 1, 2, 1, 40)
+B200_PATH(P122, 1, 2, 2, 52)
+B200_PATH(P202, 2, 0, 2, -1)
+B200_PATH(P211, 2, 1, 1, 12)
+B200_PATH(P212, 2, 1, 2, 28)
+B200_PATH(P220, 2, 2, 0, -1)
+B200_PATH(P221, 2, 2, 1, 56)
+B200_PATH(P222, 2, 2, 2, 72)
+#undef B200_PATH
+
+// per-edge shared-memory record: Y[9] (padded to 12) followed by the role's coupling matrices
+template <int ROLE, int LOUT> struct RoleT {
+  static constexpr int REC = (LOUT == 0 || ROLE == 0) ? 12 : (ROLE == 1 ? 68 : 100);
+  static constexpr int NTAB = (LOUT == 0 || ROLE == 0) ? 0 : 4;
+  static constexpr int D1 = 2 * ROLE + 1;
+};
+
+template <int PID> __device__ __forceinline__ void cg_M(const float* Y, float* M) {
+  if constexpr (PID == P111) cg_M_111(Y, M);
+  else if constexpr (PID == P112) cg_M_112(Y, M);
+  else if constexpr (PID == P121) cg_M_121(Y, M);
+  else if constexpr (PID == P122) cg_M_122(Y, M);
+  else if constexpr (PID == P211) cg_M_211(Y, M);
+  else if constexpr (PID == P212) cg_M_212(Y, M);
+  else if constexpr (PID == P221) cg_M_221(Y, M);
+  else if constexpr (PID == P222) cg_M_222(Y, M);
+}
+template <int PID> __device__ __forceinline__ void cg_dY(const float* G, float* dY) {
+  if constexpr (PID == P111) cg_dY_111(G, dY);
+  else if constexpr (PID == P112) cg_dY_112(G, dY);
+  else if constexpr (PID == P121) cg_dY_121(G, dY);
+  else if constexpr (PID == P122) cg_dY_122(G, dY);
+  else if constexpr (PID == P211) cg_dY_211(G, dY);
+  else if constexpr (PID == P212) cg_dY_212(G, dY);
+  else if constexpr (PID == P221) cg_dY_221(G, dY);
+  else if constexpr (PID == P222) cg_dY_222(G, dY);
+}
+
+template <int PID> __device__ __forceinline__ void load_M(const float* rec, float* M) {
+  constexpr int N = PathT<PID>::D1 * PathT<PID>::D3;
+  constexpr int N4 = (N + 3) / 4;
+  const float4* q = reinterpret_cast<const float4*>(rec + PathT<PID>::TAB);
+#pragma unroll
+  for (int i = 0; i < N4; ++i) {
+    float4 v = q[i];
+    M[4 * i] = v.x; M[4 * i + 1] = v.y; M[4 * i + 2] = v.z; M[4 * i + 3] = v.w;
+  }
+}
+
+// ---- per-path arithmetic ------------------------------------------------------------------------
+// forward: acc[c] += w * sum_a M[a][c] x[a]
+template <int PID> __device__ __forceinline__ void p_fwd(const float* rec, const float* x, float w, float* acc) {
+  using P = PathT<PID>;
+  if constexpr (PID == P000) {
+    acc[0] = fmaf(w, x[0], acc[0]);
+  } else if constexpr (PID == P011 || PID == P022) {
+    const float t = w * x[0];
+    constexpr int yo = (PID == P011) ? 1 : 4;
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) acc[c] = fmaf(t, rec[yo + c], acc[c]);
+  } else if constexpr (PID == P101 || PID == P202) {
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) acc[c] = fmaf(w, x[c], acc[c]);
+  } else if constexpr (PID == P110 || PID == P220) {
+    constexpr int yo = (PID == P110) ? 1 : 4;
+    float s = 0.f;
+#pragma unroll
+    for (int a = 0; a < P::D1; ++a) s = fmaf(x[a], rec[yo + a], s);
+    acc[0] = fmaf(w * ((PID == P110) ? kInvSqrt3 : kInvSqrt5), s, acc[0]);
+  } else {
+    float M[(P::D1 * P::D3 + 3) / 4 * 4];
+    load_M<PID>(rec, M);
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) {
+      float s = 0.f;
+#pragma unroll
+      for (int a = 0; a < P::D1; ++a) s = fmaf(M[a * P::D3 + c], x[a], s);
+      acc[c] = fmaf(w, s, acc[c]);
+    }
+  }
+}
+
+// backward wrt x: dx[a] += w * sum_c M[a][c] g[c]
+template <int PID> __device__ __forceinline__ void p_bwdx(const float* rec, const float* g, float w, float* dx) {
+  using P = PathT<PID>;
+  if constexpr (PID == P000) {
+    dx[0] = fmaf(w, g[0], dx[0]);
+  } else if constexpr (PID == P011 || PID == P022) {
+    constexpr int yo = (PID == P011) ? 1 : 4;
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) s = fmaf(rec[yo + c], g[c], s);
+    dx[0] = fmaf(w, s, dx[0]);
+  } else if constexpr (PID == P101 || PID == P202) {
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) dx[c] = fmaf(w, g[c], dx[c]);
+  } else if constexpr (PID == P110 || PID == P220) {
+    constexpr int yo = (PID == P110) ? 1 : 4;
+    const float t = w * g[0] * ((PID == P110) ? kInvSqrt3 : kInvSqrt5);
+#pragma unroll
+    for (int a = 0; a < P::D1; ++a) dx[a] = fmaf(t, rec[yo + a], dx[a]);
+  } else {
+    float M[(P::D1 * P::D3 + 3) / 4 * 4];
+    load_M<PID>(rec, M);
+#pragma unroll
+    for (int a = 0; a < P::D1; ++a) {
+      float s = 0.f;
+#pragma unroll
+      for (int c = 0; c < P::D3; ++c) s = fmaf(M[a * P::D3 + c], g[c], s);
+      dx[a] = fmaf(w, s, dx[a]);
+    }
+  }
+}
+
+// backward wrt the per-edge weight and the spherical harmonics:
+//   dw = sum_{a,c} M[a][c] x[a] g[c];   dY[b] += w * sum_{a,c} C[a,b,c] x[a] g[c]
+template <int PID>
+__device__ __forceinline__ void p_bwde(const float* rec, const float* x, const float* g, float w, float& dw, float* dY) {
+  using P = PathT<PID>;
+  if constexpr (PID == P000) {
+    dw = x[0] * g[0];
+  } else if constexpr (PID == P011 || PID == P022) {
+    constexpr int yo = (PID == P011) ? 1 : 4;
+    float s = 0.f;
+    const float t = w * x[0];
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) {
+      s = fmaf(rec[yo + c], g[c], s);
+      dY[yo + c] = fmaf(t, g[c], dY[yo + c]);
+    }
+    dw = x[0] * s;
+  } else if constexpr (PID == P101 || PID == P202) {
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) s = fmaf(x[c], g[c], s);
+    dw = s;
+  } else if constexpr (PID == P110 || PID == P220) {
+    constexpr int yo = (PID == P110) ? 1 : 4;
+    constexpr float k = (PID == P110) ? kInvSqrt3 : kInvSqrt5;
+    float s = 0.f;
+    const float t = w * g[0] * k;
+#pragma unroll
+    for (int a = 0; a < P::D1; ++a) {
+      s = fmaf(x[a], rec[yo + a], s);
+      dY[yo + a] = fmaf(t, x[a], dY[yo + a]);
+    }
+    dw = g[0] * k * s;
+  } else {
+    float M[(P::D1 * P::D3 + 3) / 4 * 4];
+    load_M<PID>(rec, M);
+    float G[P::D1 * P::D3];
+    float s = 0.f;
+#pragma unroll
+    for (int a = 0; a < P::D1; ++a)
+#pragma unroll
+      for (int c = 0; c < P::D3; ++c) {
+        G[a * P::D3 + c] = x[a] * g[c];
+        s = fmaf(M[a * P::D3 + c], G[a * P::D3 + c], s);
+      }
+    dw = s;
+    float t[9];
+#pragma unroll
+    for (int b = 0; b < 9; ++b) t[b] = 0.f;
+    cg_dY<PID>(G, t);
+    constexpr int yo = (P::L2 == 1) ? 1 : 4;
+#pragma unroll
+    for (int b = 0; b < 2 * P::L2 + 1; ++b) dY[yo + b] = fmaf(w, t[yo + b], dY[yo + b]);
+  }
+}
+
+// ---- path lists (one per thread group) ----------------------------------------------------------
+template <int... PIDS> struct PL;
+template <> struct PL<> {
+  static constexpr int NACC = 0;
+  static constexpr int NP = 0;
+  __device__ __forceinline__ static void load_w(const ConvDesc&, const float*, int, float*) {}
+  __device__ __forceinline__ static void fwd(const float*, const float*, const float*, float*) {}
+  __device__ __forceinline__ static void bwdx(const float*, const float*, const float*, float*) {}
+  __device__ __forceinline__ static void bwde(const float*, const float*, const float*, const float*, float*, float*) {}
+  __device__ __forceinline__ static void load_o(const ConvDesc&, const float*, int, float, float*) {}
+  __device__ __forceinline__ static void store_o(const ConvDesc&, float*, int, float, const float*) {}
+  __device__ __forceinline__ static void store_w(const ConvDesc&, float*, int, const float*) {}
+};
+template <int PID, int... REST> struct PL<PID, REST...> {
+  using P = PathT<PID>;
+  using R = PL<REST...>;
+  static constexpr int NACC = P::D3 + R::NACC;
+  static constexpr int NP = 1 + sizeof...(REST);
+  // wv[0..NP) <- weights of channel u for this edge
+  __device__ __forceinline__ static void load_w(const ConvDesc& d, const float* __restrict__ wrow, int u, float* wv) {
+    wv[0] = __ldg(wrow + d.woff[PID] + u);
+    R::load_w(d, wrow, u, wv + 1);
+  }
+  __device__ __forceinline__ static void store_w(const ConvDesc& d, float* __restrict__ wrow, int u, const float* wv) {
+    wrow[d.woff[PID] + u] = wv[0];
+    R::store_w(d, wrow, u, wv + 1);
+  }
+  __device__ __forceinline__ static void fwd(const float* rec, const float* x, const float* wv, float* acc) {
+    p_fwd<PID>(rec, x, wv[0], acc);
+    R::fwd(rec, x, wv + 1, acc + P::D3);
+  }
+  __device__ __forceinline__ static void bwdx(const float* rec, const float* g, const float* wv, float* dx) {
+    p_bwdx<PID>(rec, g, wv[0], dx);
+    R::bwdx(rec, g + P::D3, wv + 1, dx);
+  }
+  __device__ __forceinline__ static void bwde(const float* rec, const float* x, const float* g, const float* wv, float* dwv,
+                                              float* dY) {
+    p_bwde<PID>(rec, x, g, wv[0], dwv[0], dY);
+    R::bwde(rec, x, g + P::D3, wv + 1, dwv + 1, dY);
+  }
+  // o[0..NACC) <- scale * row[slot of channel u]
+  __device__ __forceinline__ static void load_o(const ConvDesc& d, const float* __restrict__ row, int u, float scale, float* o) {
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) o[c] = scale * __ldg(row + d.ooff[PID] + u * P::D3 + c);
+    R::load_o(d, row, u, scale, o + P::D3);
+  }
+  __device__ __forceinline__ static void store_o(const ConvDesc& d, float* __restrict__ row, int u, float denom, const float* o) {
+#pragma unroll
+    for (int c = 0; c < P::D3; ++c) row[d.ooff[PID] + u * P::D3 + c] = o[c] / denom;
+    R::store_o(d, row, u, denom, o + P::D3);
+  }
+};
+
+// group -> path list, per (ROLE, LOUT)
+template <int ROLE, int LOUT, int G> struct GroupT { using L = PL<>; };
+template <> struct GroupT<0, 2, 0> { using L = PL<P000, P011, P022>; };
+template <> struct GroupT<1, 2, 0> { using L = PL<P101, P110, P111, P121>; };
+template <> struct GroupT<1, 2, 1> { using L = PL<P112, P122>; };
+template <> struct GroupT<2, 2, 0> { using L = PL<P212>; };
+template <> struct GroupT<2, 2, 1> { using L = PL<P222>; };
+template <> struct GroupT<2, 2, 2> { using L = PL<P211, P202>; };
+template <> struct GroupT<2, 2, 3> { using L = PL<P221, P220>; };
+template <> struct GroupT<0, 0, 0> { using L = PL<P000>; };
+template <> struct GroupT<1, 0, 0> { using L = PL<P110>; };
+template <> struct GroupT<2, 0, 0> { using L = PL<P220>; };
+template <int ROLE, int LOUT> __host__ __device__ constexpr int num_groups() { return LOUT == 0 ? 1 : (ROLE == 0 ? 1 : (ROLE == 1 ? 2 : 4)); }
+constexpr int kMaxAcc = 10;
+
+// ---- staging of one chunk of edges ----------------------------------------------------------------
+// eid: optional indirection (edge ids sorted by source, for the backward-x pass); gidx: row to gather per edge
+template <int ROLE, int LOUT>
+__device__ __forceinline__ void stage_chunk(float* rec, int* s_e, int* s_g, const float* __restrict__ Y,
+                                            const int* __restrict__ eid, const int* __restrict__ gidx, int c0, int ne) {
+  using RT = RoleT<ROLE, LOUT>;
+  constexpr int NI = RT::NTAB + 1;
+  for (int it = threadIdx.x; it < ne * NI; it += blockDim.x) {
+    const int k = it / NI, tab = it % NI;
+    const int e = eid ? __ldg(eid + c0 + k) : c0 + k;
+    const float* Yg = Y + (size_t)e * 9;
+    float* r = rec + k * RT::REC;
+    if (tab == RT::NTAB) {
+#pragma unroll
+      for (int b = 0; b < 9; ++b) r[b] = __ldg(Yg + b);
+      s_e[k] = e;
+      s_g[k] = __ldg(gidx + e);
+    } else if constexpr (RT::NTAB > 0) {
+      float Yl[9];
+#pragma unroll
+      for (int b = 0; b < 9; ++b) Yl[b] = __ldg(Yg + b);
+      if constexpr (ROLE == 1) {
+        if (tab == 0) cg_M<P111>(Yl, r + PathT<P111>::TAB);
+        else if (tab == 1) cg_M<P112>(Yl, r + PathT<P112>::TAB);
+        else if (tab == 2) cg_M<P121>(Yl, r + PathT<P121>::TAB);
+        else cg_M<P122>(Yl, r + PathT<P122>::TAB);
+      } else {
+        if (tab == 0) cg_M<P211>(Yl, r + PathT<P211>::TAB);
+        else if (tab == 1) cg_M<P212>(Yl, r + PathT<P212>::TAB);
+        else if (tab == 2) cg_M<P221>(Yl, r + PathT<P221>::TAB);
+        else cg_M<P222>(Yl, r + PathT<P222>::TAB);
+      }
+    }
+  }
+}
+
+template <int ROLE> __device__ __forceinline__ int role_mul(const ConvDesc& d) { return ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2); }
+template <int ROLE> __device__ __forceinline__ int role_xoff(const ConvDesc& d) {
+  return ROLE == 0 ? 0 : (ROLE == 1 ? d.m0 : d.m0 + 3 * d.m1);
+}
+
+// ---- forward ------------------------------------------------------------------------------------
+template <int ROLE, int LOUT, int G>
+__device__ __forceinline__ void fwd_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
+                                          const float* __restrict__ x, const float* __restrict__ w, int u, float* acc) {
+  using L = typename GroupT<ROLE, LOUT, G>::L;
+  constexpr int D1 = RoleT<ROLE, LOUT>::D1;
+  const int xo = role_xoff<ROLE>(d) + u * D1;
+#pragma unroll 2
+  for (int k = 0; k < ne; ++k) {
+    float xv[D1], wv[L::NP > 0 ? L::NP : 1];
+    const float* xr = x + (size_t)s_g[k] * d.xdim + xo;
+#pragma unroll
+    for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
+    L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
+    L::fwd(rec + k * RoleT<ROLE, LOUT>::REC, xv, wv, acc);
+  }
+}
+
+template <int ROLE, int LOUT>
+__global__ void __launch_bounds__(256)
+conv_fwd_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
+                const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w, float denom,
+                float* __restrict__ out) {
+  using RT = RoleT<ROLE, LOUT>;
+  __shared__ __align__(16) float rec[TE * RT::REC];
+  __shared__ int s_e[TE], s_g[TE];
+  const int i = blockIdx.x;
+  const int e0 = rowptr[i], e1 = rowptr[i + 1];
+  const int grp = threadIdx.x / mulpad, u = threadIdx.x % mulpad;
+  const bool active = u < role_mul<ROLE>(d);
+  float acc[kMaxAcc];
+#pragma unroll
+  for (int c = 0; c < kMaxAcc; ++c) acc[c] = 0.f;
+  for (int c0 = e0; c0 < e1; c0 += TE) {
+    const int ne = min(TE, e1 - c0);
+    __syncthreads();
+    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne);
+    __syncthreads();
+    if (active) {
+      if (grp == 0) fwd_group<ROLE, LOUT, 0>(d, rec, s_e, s_g, ne, x, w, u, acc);
+      else if (grp == 1) fwd_group<ROLE, LOUT, 1>(d, rec, s_e, s_g, ne, x, w, u, acc);
+      else if (grp == 2) fwd_group<ROLE, LOUT, 2>(d, rec, s_e, s_g, ne, x, w, u, acc);
+      else fwd_group<ROLE, LOUT, 3>(d, rec, s_e, s_g, ne, x, w, u, acc);
+    }
+  }
+  if (active) {
+    float* orow = out + (size_t)i * d.odim;
+    if (grp == 0) GroupT<ROLE, LOUT, 0>::L::store_o(d, orow, u, denom, acc);
+    else if (grp == 1) GroupT<ROLE, LOUT, 1>::L::store_o(d, orow, u, denom, acc);
+    else if (grp == 2) GroupT<ROLE, LOUT, 2>::L::store_o(d, orow, u, denom, acc);
+    else GroupT<ROLE, LOUT, 3>::L::store_o(d, orow, u, denom, acc);
+  }
+}
+
+// ---- backward wrt x[src] --------------------------------------------------------------------------
+// One CTA per SOURCE atom j: walks the edges whose source is j (eid = edge ids sorted by source,
+// rrowptr = their CSR), gathers the output-gradient row of each edge's destination.
+template <int ROLE, int LOUT, int G>
+__device__ __forceinline__ void bwdx_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
+                                           const float* __restrict__ gout, const float* __restrict__ w, float inv_denom,
+                                           int u, float* dx) {
+  using L = typename GroupT<ROLE, LOUT, G>::L;
+#pragma unroll 2
+  for (int k = 0; k < ne; ++k) {
+    float gv[L::NACC > 0 ? L::NACC : 1], wv[L::NP > 0 ? L::NP : 1];
+    L::load_o(d, gout + (size_t)s_g[k] * d.odim, u, inv_denom, gv);
+    L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
+    L::bwdx(rec + k * RoleT<ROLE, LOUT>::REC, gv, wv, dx);
+  }
+}
+
+template <int ROLE, int LOUT>
+__global__ void __launch_bounds__(256)
+conv_bwdx_kernel(ConvDesc d, int mulpad, const int* __restrict__ rrowptr, const int* __restrict__ eid,
+                 const int* __restrict__ dst, const float* __restrict__ gout, const float* __restrict__ Y,
+                 const float* __restrict__ w, float inv_denom, float* __restrict__ dxo) {
+  using RT = RoleT<ROLE, LOUT>;
+  constexpr int D1 = RT::D1;
+  constexpr int NG = num_groups<ROLE, LOUT>();
+  __shared__ __align__(16) float rec[TE * RT::REC];
+  __shared__ int s_e[TE], s_g[TE];
+  extern __shared__ float s_part[];  // [(NG-1)][mulpad][D1] partial sums of groups 1..NG-1
+  const int j = blockIdx.x;
+  const int e0 = rrowptr[j], e1 = rrowptr[j + 1];
+  const int grp = threadIdx.x / mulpad, u = threadIdx.x % mulpad;
+  const bool active = u < role_mul<ROLE>(d);
+  float dx[D1];
+#pragma unroll
+  for (int a = 0; a < D1; ++a) dx[a] = 0.f;
+  for (int c0 = e0; c0 < e1; c0 += TE) {
+    const int ne = min(TE, e1 - c0);
+    __syncthreads();
+    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, eid, dst, c0, ne);
+    __syncthreads();
+    if (active) {
+      if (grp == 0) bwdx_group<ROLE, LOUT, 0>(d, rec, s_e, s_g, ne, gout, w, inv_denom, u, dx);
+      else if (grp == 1) bwdx_group<ROLE, LOUT, 1>(d, rec, s_e, s_g, ne, gout, w, inv_denom, u, dx);
+      else if (grp == 2) bwdx_group<ROLE, LOUT, 2>(d, rec, s_e, s_g, ne, gout, w, inv_denom, u, dx);
+      else bwdx_group<ROLE, LOUT, 3>(d, rec, s_e, s_g, ne, gout, w, inv_denom, u, dx);
+    }
+  }
+  if constexpr (NG > 1) {
+    if (active && grp > 0) {
+#pragma unroll
+      for (int a = 0; a < D1; ++a) s_part[((grp - 1) * mulpad + u) * D1 + a] = dx[a];
+    }
+    __syncthreads();
+    if (active && grp == 0) {
+      for (int g = 1; g < NG; ++g)
+#pragma unroll
+        for (int a = 0; a < D1; ++a) dx[a] += s_part[((g - 1) * mulpad + u) * D1 + a];
+    }
+  }
+  if (active && grp == 0) {
+    float* r = dxo + (size_t)j * d.xdim + role_xoff<ROLE>(d) + u * D1;
+#pragma unroll
+    for (int a = 0; a < D1; ++a) r[a] = dx[a];
+  }
+}
+
+// ---- backward wrt per-edge weights and spherical harmonics ---------------------------------------------
+// lanes with (lane & 3) == 0 end up with the warp sum of component m = ((lane>>4)&1)*4 + ((lane>>3)&1)*2 + ((lane>>2)&1)
+__device__ __forceinline__ float warp_reduce8(float* v, int lane) {
+  const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float send = h16 ? v[i] : v[i + 4], keep = h16 ? v[i + 4] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float send = h8 ? v[i] : v[i + 2], keep = h8 ? v[i + 2] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+  {
+    const float send = h4 ? v[0] : v[1], keep = h4 ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+  return v[0];
+}
+
+template <int ROLE, int LOUT, int G>
+__device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
+                                           const float* __restrict__ x, const float* __restrict__ w,
+                                           float* __restrict__ dw, const float* gv, int u, bool active, float* s_dY) {
+  using L = typename GroupT<ROLE, LOUT, G>::L;
+  constexpr int D1 = RoleT<ROLE, LOUT>::D1;
+  const int xo = role_xoff<ROLE>(d) + u * D1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int k = 0; k < ne; ++k) {
+    float dY[9];
+#pragma unroll
+    for (int b = 0; b < 9; ++b) dY[b] = 0.f;
+    if (active) {
+      float xv[D1], wv[L::NP > 0 ? L::NP : 1], dwv[L::NP > 0 ? L::NP : 1];
+      const float* xr = x + (size_t)s_g[k] * d.xdim + xo;
+#pragma unroll
+      for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
+      L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
+      L::bwde(rec + k * RoleT<ROLE, LOUT>::REC, xv, gv, wv, dwv, dY);
+      L::store_w(d, dw + (size_t)s_e[k] * d.wn, u, dwv);
+    }
+    if constexpr (LOUT == 0 && ROLE == 0) {
+      // only path 000: no dependence on Y
+    } else {
+      const float r = warp_reduce8(dY + 1, lane);
+      if ((lane & 3) == 0) s_dY[(warp * TE + k) * 8 + (lane >> 2)] = r;  // slot lane>>2 == component m
+    }
+  }
+}
+
+template <int ROLE, int LOUT>
+__global__ void __launch_bounds__(256)
+conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
+                 const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w,
+                 const float* __restrict__ gout, float inv_denom, float* __restrict__ dw, float* __restrict__ dYo,
+                 int accumulate) {
+  using RT = RoleT<ROLE, LOUT>;
+  constexpr int NG = num_groups<ROLE, LOUT>();
+  __shared__ __align__(16) float rec[TE * RT::REC];
+  __shared__ int s_e[TE], s_g[TE];
+  extern __shared__ float s_dY[];  // [nwarps][TE][8]
+  const int i = blockIdx.x;
+  const int e0 = rowptr[i], e1 = rowptr[i + 1];
+  const int grp = threadIdx.x / mulpad, u = threadIdx.x % mulpad;
+  const bool active = u < role_mul<ROLE>(d) && grp < NG;
+  const int nwarps = blockDim.x >> 5;
+  float gv[kMaxAcc];
+#pragma unroll
+  for (int c = 0; c < kMaxAcc; ++c) gv[c] = 0.f;
+  if (active) {
+    const float* grow = gout + (size_t)i * d.odim;
+    if (grp == 0) GroupT<ROLE, LOUT, 0>::L::load_o(d, grow, u, inv_denom, gv);
+    else if (grp == 1) GroupT<ROLE, LOUT, 1>::L::load_o(d, grow, u, inv_denom, gv);
+    else if (grp == 2) GroupT<ROLE, LOUT, 2>::L::load_o(d, grow, u, inv_denom, gv);
+    else GroupT<ROLE, LOUT, 3>::L::load_o(d, grow, u, inv_denom, gv);
+  }
+  for (int c0 = e0; c0 < e1; c0 += TE) {
+    const int ne = min(TE, e1 - c0);
+    __syncthreads();
+    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne);
+    __syncthreads();
+    if (grp == 0) bwde_group<ROLE, LOUT, 0>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
+    else if (grp == 1) bwde_group<ROLE, LOUT, 1>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
+    else if (grp == 2) bwde_group<ROLE, LOUT, 2>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
+    else bwde_group<ROLE, LOUT, 3>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
+    if constexpr (!(LOUT == 0 && ROLE == 0)) {
+      __syncthreads();
+      for (int it = threadIdx.x; it < ne * 8; it += blockDim.x) {
+        const int k = it >> 3, s = it & 7, m = s;
+        float tot = 0.f;
+        for (int wq = 0; wq < nwarps; ++wq) tot += s_dY[(wq * TE + k) * 8 + s];
+        float* p = dYo + (size_t)(c0 + k) * 9 + 1 + m;
+        *p = accumulate ? (*p + tot) : tot;
+      }
+    }
+  }
+}
+
+// ---- launchers ------------------------------------------------------------------------------------
+template <int ROLE, int LOUT>
+static void launch_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                       const float* w, float denom, float* out, cudaStream_t st) {
+  const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
+  if (mul == 0 || n_dst == 0) return;
+  const int mulpad = round_up(mul, 32);
+  const int threads = mulpad * num_groups<ROLE, LOUT>();
+  conv_fwd_kernel<ROLE, LOUT><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out);
+}
+template <int ROLE, int LOUT>
+static void launch_bwdx(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst,
+                        const float* gout, const float* Y, const float* w, float inv_denom, float* dx, cudaStream_t st) {
+  const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
+  if (mul == 0 || n_src == 0) return;
+  const int mulpad = round_up(mul, 32);
+  constexpr int NG = num_groups<ROLE, LOUT>();
+  const int threads = mulpad * NG;
+  const size_t sm = (size_t)(NG - 1) * mulpad * (2 * ROLE + 1) * sizeof(float);
+  conv_bwdx_kernel<ROLE, LOUT><<<n_src, threads, sm, st>>>(d, mulpad, rrowptr, eid, dst, gout, Y, w, inv_denom, dx);
+}
+template <int ROLE, int LOUT>
+static void launch_bwde(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                        const float* w, const float* gout, float inv_denom, float* dw, float* dY, int accumulate,
+                        cudaStream_t st) {
+  const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
+  if (mul == 0 || n_dst == 0) return;
+  const int mulpad = round_up(mul, 32);
+  const int threads = mulpad * num_groups<ROLE, LOUT>();
+  const size_t sm = (size_t)(threads / 32) * TE * 8 * sizeof(float);
+  conv_bwde_kernel<ROLE, LOUT><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
+                                                            accumulate);
+}
+
+static bool desc_ok(const ConvDesc& d) {
+  return (d.lout == 0 || d.lout == 2) && d.m0 >= 0 && d.m1 >= 0 && d.m2 >= 0 && d.m0 <= 256 && d.m1 <= 128 &&
+         d.m2 <= 64;
+}
+
+int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+             const float* w, float denom, float* out, cudaStream_t st) {
+  B200_REQUIRE(desc_ok(d), "conv_fwd: unsupported irreps (m0<=256, m1<=128, m2<=64, lout in {0,2})");
+  if (d.lout == 2) {
+    launch_fwd<0, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+    launch_fwd<1, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+    launch_fwd<2, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+  } else {
+    launch_fwd<0, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+    launch_fwd<1, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+    launch_fwd<2, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+  }
+  return check_launch("conv_fwd");
+}
+
+int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst, const float* gout,
+               const float* Y, const float* w, float denom, float* dx, cudaStream_t st) {
+  B200_REQUIRE(desc_ok(d), "conv_bwd_x: unsupported irreps");
+  const float inv = 1.0f / denom;
+  if (d.lout == 2) {
+    launch_bwdx<0, 2>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
+    launch_bwdx<1, 2>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
+    launch_bwdx<2, 2>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
+  } else {
+    launch_bwdx<0, 0>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
+    launch_bwdx<1, 0>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
+    launch_bwdx<2, 0>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
+  }
+  return check_launch("conv_bwd_x");
+}
+
+int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x, const float* Y,
+                  const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                  cudaStream_t st) {
+  B200_REQUIRE(desc_ok(d), "conv_bwd_edge: unsupported irreps");
+  const float inv = 1.0f / denom;
+  // the three role kernels run back to back on one stream: the first may overwrite dY, the rest add
+  int acc = accumulate;
+  if (d.lout == 2) {
+    if (d.m0) { launch_bwde<0, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+    if (d.m1) { launch_bwde<1, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+    if (d.m2) { launch_bwde<2, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+  } else {
+    // role 0 (path 000) does not touch dY
+    if (!acc && !d.m1 && !d.m2) cudaMemsetAsync(dY, 0, sizeof(float) * 9 * (size_t)n_edges, st);
+    launch_bwde<0, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st);
+    if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+    if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+  }
+  return check_launch("conv_bwd_edge");
+}
+
+}  // namespace b200

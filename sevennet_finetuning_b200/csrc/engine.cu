@@ -1,0 +1,334 @@
+// Whole-model energy + forces + virial: the call PairE3GNN::compute (pair_e3gnn.cpp:205-266) and
+// SevenNetCalculator.calculate (sevennet_calculator.py:119-157) make into the model, with a hand-written
+// reverse pass instead of autograd (ForceStressOutputFromEdge semantics, nn/force_output.py:158-215).
+//
+// Layer order follows sevenn/model_build.py:219-437 and nn/interaction_blocks.py:49-84:
+//   edge_embedding -> onehot embedding -> for t: sc_intro | self_interaction_1 -> convolution ->
+//   self_interaction_2 -> (+ self connection) -> gate;  readout 2 linears -> rescale -> sum.
+#include <map>
+#include <string>
+#include <vector>
+
+#include "ops.h"
+
+namespace b200 {
+
+void fill_conv_desc(int m0, int m1, int m2, int lout, ConvDesc& d) {
+  d.m0 = m0; d.m1 = m1; d.m2 = m2; d.lout = lout;
+  d.xdim = m0 + 3 * m1 + 5 * m2;
+  static const int L[kNumPaths][3] = {{0, 0, 0}, {0, 1, 1}, {0, 2, 2}, {1, 0, 1}, {1, 1, 0}, {1, 1, 1}, {1, 1, 2}, {1, 2, 1},
+                                      {1, 2, 2}, {2, 0, 2}, {2, 1, 1}, {2, 1, 2}, {2, 2, 0}, {2, 2, 1}, {2, 2, 2}};
+  const int mul[3] = {m0, m1, m2};
+  int woff = 0;
+  for (int p = 0; p < kNumPaths; ++p) {
+    d.woff[p] = -1;
+    d.ooff[p] = -1;
+    if (mul[L[p][0]] > 0 && L[p][2] <= lout) {
+      d.woff[p] = woff;
+      woff += mul[L[p][0]];
+    }
+  }
+  d.wn = woff;
+  int ooff = 0;
+  for (int l3 = 0; l3 <= lout; ++l3)
+    for (int p = 0; p < kNumPaths; ++p)
+      if (d.woff[p] >= 0 && L[p][2] == l3) {
+        d.ooff[p] = ooff;
+        ooff += mul[L[p][0]] * (2 * l3 + 1);
+      }
+  d.odim = ooff;
+}
+
+// irreps linear between two (m0,m1,m2)-shaped irreps; blocks exist where both sides have the l
+static LinDesc make_linear(const int in[3], const int out[3]) {
+  LinDesc d{};
+  int io = 0, oo = 0, wo = 0;
+  for (int l = 0; l < 3; ++l) {
+    const int D = 2 * l + 1;
+    if (in[l] > 0 && out[l] > 0) {
+      LinBlock& b = d.blk[d.nblk++];
+      b.d = D; b.mul_in = in[l]; b.mul_out = out[l]; b.in_off = io; b.out_off = oo; b.w_off = wo;
+      b.scale = 1.0f / sqrtf((float)in[l]);
+      wo += in[l] * out[l];
+    }
+    io += in[l] * D;
+    oo += out[l] * D;
+  }
+  d.in_dim = io;
+  d.out_dim = oo;
+  return d;
+}
+static int lin_numel(const LinDesc& d) {
+  int n = 0;
+  for (int i = 0; i < d.nblk; ++i) n += d.blk[i].mul_in * d.blk[i].mul_out;
+  return n;
+}
+static bool lin_covers_input(const LinDesc& d) {
+  int covered = 0;
+  for (int i = 0; i < d.nblk; ++i) covered += d.blk[i].mul_in * d.blk[i].d;
+  return covered == d.in_dim;
+}
+static bool lin_covers_output(const LinDesc& d) {
+  int covered = 0;
+  for (int i = 0; i < d.nblk; ++i) covered += d.blk[i].mul_out * d.blk[i].d;
+  return covered == d.out_dim;
+}
+
+struct Layer {
+  int in[3], out[3];      // node irreps entering / leaving the layer
+  int gin[3];             // gate input irreps: (ns+ng, m1, m2)
+  int msg[3];             // convolution output multiplicities per l
+  ConvDesc conv;
+  MlpDesc mlp;
+  LinDesc sc, si1, si2;
+  int lout;
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+struct B200Model {
+  B200ModelConfig cfg;
+  std::vector<Layer> layers;
+  LinDesc r1, r2;
+  std::map<std::string, std::pair<float*, long long>> params;  // name -> (device ptr, numel)
+  std::map<std::string, long long> expected;
+  std::vector<float> denom;  // host copies of {t}_convolution.denominator
+};
+
+static float* P(B200Model* m, const std::string& name) {
+  auto it = m->params.find(name);
+  return it == m->params.end() ? nullptr : it->second.first;
+}
+
+extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
+  B200_REQUIRE(cfg && out, "model_create: null argument");
+  B200_REQUIRE(cfg->n_layers >= 1 && cfg->n_layers <= 7 && cfg->lmax == 2, "model_create: 1..7 layers, lmax 2");
+  B200Model* m = new B200Model();
+  m->cfg = *cfg;
+  const int nl = cfg->n_layers;
+  m->denom.assign(nl, 1.0f);
+  for (int t = 0; t < nl; ++t) {
+    Layer L{};
+    for (int l = 0; l < 3; ++l) { L.in[l] = cfg->mul[t][l]; L.out[l] = cfg->mul[t + 1][l]; }
+    L.lout = (L.out[1] + L.out[2] > 0) ? 2 : 0;
+    L.gin[0] = L.out[0] + L.out[1] + L.out[2]; L.gin[1] = L.out[1]; L.gin[2] = L.out[2];
+    fill_conv_desc(L.in[0], L.in[1], L.in[2], L.lout, L.conv);
+    static const int L3[kNumPaths] = {0, 1, 2, 1, 0, 1, 2, 1, 2, 2, 1, 2, 0, 1, 2};
+    static const int L1[kNumPaths] = {0, 0, 0, 1, 1, 1, 1, 1, 1, 2, 2, 2, 2, 2, 2};
+    L.msg[0] = L.msg[1] = L.msg[2] = 0;
+    for (int p = 0; p < kNumPaths; ++p)
+      if (L.conv.woff[p] >= 0) L.msg[L3[p]] += L.in[L1[p]];
+    L.mlp = MlpDesc{cfg->edge.num_basis, cfg->hidden[0], cfg->hidden[1], L.conv.wn};
+    L.sc = make_linear(L.in, L.gin);
+    L.si1 = make_linear(L.in, L.in);
+    L.si2 = make_linear(L.msg, L.gin);
+    m->layers.push_back(L);
+    const std::string s = std::to_string(t);
+    m->expected[s + "_self_connection_intro.linear.weight"] = lin_numel(L.sc);
+    m->expected[s + "_self_interaction_1.linear.weight"] = lin_numel(L.si1);
+    m->expected[s + "_self_interaction_2.linear.weight"] = lin_numel(L.si2);
+    m->expected[s + "_convolution.weight_nn.layer0.weight"] = (long long)L.mlp.nb * L.mlp.h1;
+    m->expected[s + "_convolution.weight_nn.layer1.weight"] = (long long)L.mlp.h1 * L.mlp.h2;
+    m->expected[s + "_convolution.weight_nn.layer2.weight"] = (long long)L.mlp.h2 * L.mlp.wn;
+    m->expected[s + "_convolution.denominator"] = 1;
+  }
+  const int last[3] = {cfg->mul[nl][0], cfg->mul[nl][1], cfg->mul[nl][2]};
+  const int hid[3] = {cfg->readout_hidden, 0, 0}, one[3] = {1, 0, 0};
+  m->r1 = make_linear(last, hid);
+  m->r2 = make_linear(hid, one);
+  m->expected["onehot_to_feature_x.linear.weight"] = (long long)cfg->n_species * cfg->mul[0][0];
+  m->expected["reduce_input_to_hidden.linear.weight"] = lin_numel(m->r1);
+  m->expected["reduce_hidden_to_energy.linear.weight"] = lin_numel(m->r2);
+  const int nsc = cfg->species_wise_rescale ? cfg->n_species : 1;
+  m->expected["rescale_atomic_energy.shift"] = nsc;
+  m->expected["rescale_atomic_energy.scale"] = nsc;
+  m->expected["edge_embedding.basis_function.coeffs"] = cfg->edge.num_basis;
+  *out = m;
+  return B200_OK;
+}
+
+extern "C" int b200_model_set_param(B200Model* m, const char* name, const float* data_host, int64_t numel) {
+  B200_REQUIRE(m && name && data_host, "model_set_param: null argument");
+  auto it = m->expected.find(name);
+  B200_REQUIRE(it != m->expected.end(), "model_set_param: unknown parameter '%s'", name);
+  B200_REQUIRE(it->second == numel, "model_set_param: '%s' expects %lld values, got %lld", name, it->second,
+               (long long)numel);
+  auto& slot = m->params[name];
+  if (!slot.first) {
+    if (cudaMalloc(&slot.first, sizeof(float) * (size_t)numel) != cudaSuccess) {
+      set_error("model_set_param: cudaMalloc failed");
+      return B200_ERR_CUDA;
+    }
+    slot.second = numel;
+  }
+  if (cudaMemcpy(slot.first, data_host, sizeof(float) * (size_t)numel, cudaMemcpyHostToDevice) != cudaSuccess) {
+    set_error("model_set_param: cudaMemcpy failed");
+    return B200_ERR_CUDA;
+  }
+  const std::string nm(name);
+  const std::string suffix = "_convolution.denominator";
+  if (nm.size() > suffix.size() && nm.compare(nm.size() - suffix.size(), suffix.size(), suffix) == 0)
+    m->denom[std::stoi(nm)] = data_host[0];
+  return B200_OK;
+}
+
+extern "C" void b200_model_destroy(B200Model* m) {
+  if (!m) return;
+  for (auto& kv : m->params) cudaFree(kv.second.first);
+  delete m;
+}
+
+namespace {
+struct Plan {
+  size_t off = 0;
+  char* base = nullptr;
+  template <class T> T* take(size_t n) {
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += (n * sizeof(T) + 255) / 256 * 256;
+    return p;
+  }
+};
+struct Buffers {
+  float *Y, *emb, *dY, *demb, *dvec, *dw, *x[2], *conv_out, *g_x[2], *g_gin, *g_conv, *h, *s, *g_h, *g_s, *virial_atom;
+  std::vector<float*> w, xs, gin;
+  int *rrowptr, *eid;
+  void* tws;
+};
+void plan_buffers(const B200Model* m, int N, long long E, Plan& p, Buffers& b) {
+  int maxx = 0, maxg = 0, maxmsg = 0, maxwn = 0;
+  for (const Layer& L : m->layers) {
+    maxx = std::max(maxx, L.conv.xdim);
+    maxg = std::max(maxg, L.sc.out_dim);
+    maxmsg = std::max(maxmsg, L.conv.odim);
+    maxwn = std::max(maxwn, L.conv.wn);
+  }
+  maxx = std::max(maxx, m->r1.in_dim);
+  const int nb = m->cfg.edge.num_basis;
+  b.Y = p.take<float>((size_t)E * 9);
+  b.emb = p.take<float>((size_t)E * nb);
+  b.dY = p.take<float>((size_t)E * 9);
+  b.demb = p.take<float>((size_t)E * nb);
+  b.dvec = p.take<float>((size_t)E * 3);
+  b.dw = p.take<float>((size_t)E * maxwn);
+  for (int k = 0; k < 2; ++k) b.x[k] = p.take<float>((size_t)N * maxx);
+  for (int k = 0; k < 2; ++k) b.g_x[k] = p.take<float>((size_t)N * maxx);
+  b.conv_out = p.take<float>((size_t)N * maxmsg);
+  b.g_conv = p.take<float>((size_t)N * maxmsg);
+  b.g_gin = p.take<float>((size_t)N * maxg);
+  b.h = p.take<float>((size_t)N * m->r1.out_dim);
+  b.g_h = p.take<float>((size_t)N * m->r1.out_dim);
+  b.s = p.take<float>((size_t)N);
+  b.g_s = p.take<float>((size_t)N);
+  b.virial_atom = p.take<float>((size_t)N * 6);
+  b.w.clear(); b.xs.clear(); b.gin.clear();
+  for (const Layer& L : m->layers) {
+    b.w.push_back(p.take<float>((size_t)E * L.conv.wn));
+    b.xs.push_back(p.take<float>((size_t)N * L.conv.xdim));
+    b.gin.push_back(p.take<float>((size_t)N * L.sc.out_dim));
+  }
+  b.rrowptr = p.take<int>((size_t)N + 1);
+  b.eid = p.take<int>((size_t)E);
+  b.tws = p.take<char>(transpose_workspace_bytes(N, E));
+}
+
+__global__ void rescale_bwd_kernel(int n, const int* __restrict__ types, const float* __restrict__ scale, int species_wise,
+                                   float* __restrict__ g) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) g[i] = scale[species_wise ? types[i] : 0];
+}
+}  // namespace
+
+extern "C" size_t b200_model_workspace_bytes(const B200Model* m, int n_atoms, int64_t n_edges) {
+  Plan p;
+  Buffers b;
+  plan_buffers(m, n_atoms, n_edges, p, b);
+  return p.off + 256;
+}
+
+#define TRY(call)                 \
+  do {                            \
+    int rc_ = (call);             \
+    if (rc_ != B200_OK) return rc_; \
+  } while (0)
+
+extern "C" int b200_model_compute(B200Model* m, int N, int64_t E, const int32_t* types, const int32_t* rowptr,
+                                  const int32_t* src, const int32_t* dst, const float* edge_vec, void* workspace,
+                                  size_t workspace_bytes, float* energy, float* atomic_energy, float* force,
+                                  float* virial, void* stream) {
+  B200_REQUIRE(m, "model_compute: null model");
+  for (auto& kv : m->expected)
+    B200_REQUIRE(m->params.count(kv.first), "model_compute: parameter '%s' was never set", kv.first.c_str());
+  B200_REQUIRE(E < (1LL << 31), "model_compute: more than 2^31 edges per device");
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  p.base = (char*)(((uintptr_t)workspace + 255) / 256 * 256);
+  Buffers b;
+  plan_buffers(m, N, E, p, b);
+  B200_REQUIRE(p.off + 256 <= workspace_bytes, "model_compute: workspace too small (%zu needed)", p.off + 256);
+  const B200ModelConfig& c = m->cfg;
+  const float* coeffs = P(m, "edge_embedding.basis_function.coeffs");
+  const int nl = c.n_layers;
+
+  // ---------------- forward ----------------
+  TRY(edge_embed_fwd(c.edge, E, edge_vec, coeffs, nullptr, b.Y, b.emb, st));
+  TRY(csr_transpose(N, E, src, b.tws, b.rrowptr, b.eid, st));
+  float* x = b.x[0];
+  float* xn = b.x[1];
+  TRY(embed_fwd(N, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
+  const std::vector<float>& denom = m->denom;
+  for (int t = 0; t < nl; ++t) {
+    const Layer& L = m->layers[t];
+    const std::string s = std::to_string(t);
+    if (!lin_covers_output(L.sc)) cudaMemsetAsync(b.gin[t], 0, sizeof(float) * (size_t)N * L.sc.out_dim, st);
+    TRY(irreps_linear(L.sc, N, x, P(m, s + "_self_connection_intro.linear.weight"), b.gin[t], 0, 0, st));
+    TRY(irreps_linear(L.si1, N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+    TRY(radial_mlp_fwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
+                       P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
+                       b.w[t], st));
+    TRY(conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
+    TRY(irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
+    TRY(gate_fwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], xn, st));
+    std::swap(x, xn);
+  }
+  TRY(irreps_linear(m->r1, N, x, P(m, "reduce_input_to_hidden.linear.weight"), b.h, 0, 0, st));
+  TRY(irreps_linear(m->r2, N, b.h, P(m, "reduce_hidden_to_energy.linear.weight"), b.s, 0, 0, st));
+  TRY(rescale_fwd(N, types, b.s, P(m, "rescale_atomic_energy.scale"), P(m, "rescale_atomic_energy.shift"),
+                  c.species_wise_rescale, atomic_energy, st));
+  TRY(colsum(N, 1, atomic_energy, energy, st));
+
+  // ---------------- reverse pass: dE/d edge_vec ----------------
+  if (N > 0)
+    rescale_bwd_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, types, P(m, "rescale_atomic_energy.scale"),
+                                                        c.species_wise_rescale, b.g_s);
+  TRY(irreps_linear(m->r2, N, b.g_s, P(m, "reduce_hidden_to_energy.linear.weight"), b.g_h, 1, 0, st));
+  float* g = b.g_x[0];
+  float* gp = b.g_x[1];
+  TRY(irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
+  bool first_edge = true;
+  for (int t = nl - 1; t >= 0; --t) {
+    const Layer& L = m->layers[t];
+    const std::string s = std::to_string(t);
+    TRY(gate_bwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], g, b.g_gin, st));
+    TRY(irreps_linear(L.si2, N, b.g_gin, P(m, s + "_self_interaction_2.linear.weight"), b.g_conv, 1, 0, st));
+    TRY(conv_bwd_edge(L.conv, N, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw, b.dY,
+                      first_edge ? 0 : 1, st));
+    TRY(radial_mlp_bwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
+                       P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
+                       b.dw, b.demb, first_edge ? 0 : 1, st));
+    first_edge = false;
+    if (t > 0) {
+      // features entering layer t depend on the positions through layers < t
+      if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
+      TRY(irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
+      TRY(conv_bwd_x(L.conv, N, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
+      TRY(irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
+      std::swap(g, gp);
+    }
+  }
+  TRY(edge_embed_bwd(c.edge, E, edge_vec, coeffs, b.dY, b.demb, b.dvec, st));
+  TRY(force_virial(N, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
+  TRY(colsum(N, 6, b.virial_atom, virial, st));
+  return check_launch("model_compute");
+}

@@ -1,0 +1,123 @@
+// Node-side elementwise pieces: gate nonlinearity, species embedding gather, rescale, column sums.
+//
+// Reference: sevenn/nn/equivariant_gate.py:59-61 (e3nn Gate; frozen graph: c*silu on scalars and on
+// gates, gated[u,:] *= gate[u]); sevenn/nn/node_embedding.py:39-48 + nn/linear.py:37-44;
+// sevenn/nn/scale.py:35-38,67-73; sevenn/nn/linear.py:76-90 (AtomReduce).
+#include "common.cuh"
+
+namespace b200 {
+
+// in  row: [ns scalars | ng = m1+m2 gates | m1 x 3 | m2 x 5];  out row: [ns | m1 x 3 | m2 x 5]
+__global__ void gate_fwd_kernel(int ns, int m1, int m2, long long n_nodes, const float* __restrict__ in,
+                                float* __restrict__ out) {
+  const int din = ns + m1 + m2 + 3 * m1 + 5 * m2, dout = ns + 3 * m1 + 5 * m2;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= n_nodes * dout) return;
+  const long long n = idx / dout;
+  const int c = (int)(idx % dout);
+  const float* r = in + n * din;
+  float v;
+  if (c < ns) {
+    v = kSilu2Mom * silu_f(r[c]);
+  } else {
+    int u, off;
+    if (c < ns + 3 * m1) { u = (c - ns) / 3; off = c - ns; }
+    else { u = m1 + (c - ns - 3 * m1) / 5; off = c - ns; }
+    v = kSilu2Mom * silu_f(r[ns + u]) * r[ns + m1 + m2 + off];
+  }
+  out[idx] = v;
+}
+
+__global__ void gate_bwd_kernel(int ns, int m1, int m2, long long n_nodes, const float* __restrict__ in,
+                                const float* __restrict__ dout_, float* __restrict__ din_) {
+  const int ng = m1 + m2, din = ns + ng + 3 * m1 + 5 * m2, dout = ns + 3 * m1 + 5 * m2;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= n_nodes * din) return;
+  const long long n = idx / din;
+  const int c = (int)(idx % din);
+  const float* r = in + n * din;
+  const float* g = dout_ + n * dout;
+  float v, d;
+  if (c < ns) {
+    silu_vd(r[c], v, d);
+    din_[idx] = g[c] * d;
+  } else if (c < ns + ng) {
+    const int u = c - ns;
+    const int D = u < m1 ? 3 : 5;
+    const int off = u < m1 ? u * 3 : 3 * m1 + (u - m1) * 5;
+    float s = 0.f;
+    for (int m = 0; m < D; ++m) s = fmaf(g[ns + off + m], r[ns + ng + off + m], s);
+    silu_vd(r[c], v, d);
+    din_[idx] = s * d;
+  } else {
+    const int off = c - ns - ng;
+    const int u = off < 3 * m1 ? off / 3 : m1 + (off - 3 * m1) / 5;
+    din_[idx] = g[ns + off] * kSilu2Mom * silu_f(r[ns + u]);
+  }
+}
+
+__global__ void embed_fwd_kernel(long long n_nodes, int n_species, int dim, const int* __restrict__ types,
+                                 const float* __restrict__ W, float* __restrict__ x) {
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= n_nodes * dim) return;
+  const long long n = idx / dim;
+  const int c = (int)(idx % dim);
+  x[idx] = W[(size_t)types[n] * dim + c] * (1.0f / sqrtf((float)n_species));
+}
+
+__global__ void rescale_fwd_kernel(int n_nodes, const int* __restrict__ types, const float* __restrict__ scaled,
+                                   const float* __restrict__ scale, const float* __restrict__ shift, int species_wise,
+                                   float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= n_nodes) return;
+  const int t = species_wise ? types[n] : 0;
+  out[n] = scaled[n] * scale[t] + shift[t];
+}
+
+// one CTA per column, fp64 accumulation in a fixed order
+__global__ void colsum_kernel(int n_rows, int ncol, const float* __restrict__ in, float* __restrict__ out) {
+  __shared__ double sh[1024];
+  const int c = blockIdx.x;
+  double s = 0.0;
+  for (int r = threadIdx.x; r < n_rows; r += blockDim.x) s += (double)in[(size_t)r * ncol + c];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[c] = (float)sh[0];
+}
+
+static unsigned blocks_for(long long n, int t) { return (unsigned)((n + t - 1) / t); }
+
+int gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, cudaStream_t st) {
+  if (n_nodes == 0) return B200_OK;
+  const long long tot = (long long)n_nodes * (ns + 3 * m1 + 5 * m2);
+  gate_fwd_kernel<<<blocks_for(tot, 256), 256, 0, st>>>(ns, m1, m2, n_nodes, in, out);
+  return check_launch("gate_fwd");
+}
+int gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, float* din, cudaStream_t st) {
+  if (n_nodes == 0) return B200_OK;
+  const long long tot = (long long)n_nodes * (ns + m1 + m2 + 3 * m1 + 5 * m2);
+  gate_bwd_kernel<<<blocks_for(tot, 256), 256, 0, st>>>(ns, m1, m2, n_nodes, in, dout, din);
+  return check_launch("gate_bwd");
+}
+int embed_fwd(int n_nodes, int n_species, int dim, const int* types, const float* W, float* x, cudaStream_t st) {
+  if (n_nodes == 0) return B200_OK;
+  embed_fwd_kernel<<<blocks_for((long long)n_nodes * dim, 256), 256, 0, st>>>(n_nodes, n_species, dim, types, W, x);
+  return check_launch("embed_fwd");
+}
+int rescale_fwd(int n_nodes, const int* types, const float* scaled, const float* scale, const float* shift,
+                int species_wise, float* out, cudaStream_t st) {
+  if (n_nodes == 0) return B200_OK;
+  rescale_fwd_kernel<<<blocks_for(n_nodes, 256), 256, 0, st>>>(n_nodes, types, scaled, scale, shift, species_wise, out);
+  return check_launch("rescale_fwd");
+}
+int colsum(int n_rows, int ncol, const float* in, float* out, cudaStream_t st) {
+  B200_REQUIRE(ncol >= 1 && ncol <= 64, "colsum: ncol out of range");
+  colsum_kernel<<<ncol, 1024, 0, st>>>(n_rows, ncol, in, out);
+  return check_launch("colsum");
+}
+
+}  // namespace b200

@@ -1,0 +1,50 @@
+// Internal C++ launchers shared by the C-ABI (capi.cu) and the whole-model engine (engine.cu).
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+void fill_conv_desc(int m0, int m1, int m2, int lout, ConvDesc& d);
+
+int edge_embed_fwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, float* len, float* Y,
+                   float* emb, cudaStream_t st);
+int edge_embed_bwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
+                   const float* demb, float* dvec, cudaStream_t st);
+int force_virial(int n_atoms, const int* rowptr, const int* rrowptr, const int* eid_by_src, const float* vec,
+                 const float* dvec, float* force, float* virial_atom, cudaStream_t st);
+
+int radial_mlp_fwd(const MlpDesc& d, long long E, const float* emb, const float* W0, const float* W1, const float* W2,
+                   float* w, cudaStream_t st);
+int radial_mlp_bwd(const MlpDesc& d, long long E, const float* emb, const float* W0, const float* W1, const float* W2,
+                   const float* dw, float* demb, int accumulate, cudaStream_t st);
+
+int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+             const float* w, float denom, float* out, cudaStream_t st);
+int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst, const float* gout,
+               const float* Y, const float* w, float denom, float* dx, cudaStream_t st);
+int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x,
+                  const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                  cudaStream_t st);
+
+int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
+                  cudaStream_t st);
+int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const float* dy, float* dW, int accumulate,
+                        cudaStream_t st);
+
+int gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, cudaStream_t st);
+int gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, float* din, cudaStream_t st);
+int embed_fwd(int n_nodes, int n_species, int dim, const int* types, const float* W, float* x, cudaStream_t st);
+int rescale_fwd(int n_nodes, const int* types, const float* scaled, const float* scale, const float* shift,
+                int species_wise, float* out, cudaStream_t st);
+int colsum(int n_rows, int ncol, const float* in, float* out, cudaStream_t st);
+
+size_t graph_workspace_bytes(int n);
+int graph_count(int n, const double* pos, const double* cell_host, const int* pbc_host, double cutoff, void* ws,
+                int* rowptr, long long* n_edges_host, cudaStream_t st);
+int graph_fill(int n, const double* pos, const double* cell_host, const int* pbc_host, double cutoff, void* ws,
+               const int* rowptr, int* src, int* dst, int* shift, float* edge_vec, unsigned long long* tmp_key,
+               cudaStream_t st);
+size_t transpose_workspace_bytes(int n, long long E);
+int csr_transpose(int n, long long E, const int* src, void* ws, int* rrowptr, int* eid, cudaStream_t st);
+
+}  // namespace b200

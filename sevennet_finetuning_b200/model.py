@@ -1,0 +1,105 @@
+"""Whole-model energy/forces/stress through the C-ABI engine (b200_model_*).
+
+This is the call ``SevenNetCalculator.calculate`` (sevenn/sevennet_calculator.py:119-157) and
+``PairE3GNN::compute`` (sevenn/pair_e3gnn/pair_e3gnn.cpp:205-266) make into the model; the
+reverse pass is hand-written kernels (ForceStressOutputFromEdge semantics,
+sevenn/nn/force_output.py:158-215), so no autograd graph is built.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import ops
+from ._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, EdgeParams, ModelConfig, check, lib
+
+SEVENNET0_CONFIG = dict(
+    cutoff=5.0, num_species=89, lmax=2, num_convolution_layer=5,
+    irreps_manual=['128x0e', '128x0e+64x1e+32x2e', '128x0e+64x1e+32x2e', '128x0e+64x1e+32x2e',
+                   '128x0e+64x1e+32x2e', '128x0e'],
+    bessel_basis_num=8, cutoff_function=dict(name='XPLOR', cutoff_on=4.5),
+    weight_nn_hidden_neurons=[64, 64], use_species_wise_shift_scale=True, normalize_sph=True,
+)
+
+
+def edge_params_from_config(cfg):
+    cf = cfg['cutoff_function']
+    xpl = cf['name'].upper() == 'XPLOR'
+    return EdgeParams(int(cfg['bessel_basis_num']), B200_CUTOFF_XPLOR if xpl else B200_CUTOFF_POLY,
+                      int(bool(cfg.get('normalize_sph', True))), float(cfg['cutoff']),
+                      float(cf.get('cutoff_on', 0.0)), float(cf.get('poly_cut_p_value', 6)))
+
+
+class B200SevenNet:
+    """Device-resident SevenNet-style model (nequip interaction, linear self connection)."""
+
+    def __init__(self, config=None, state_dict=None, device='cuda:0'):
+        cfg = dict(SEVENNET0_CONFIG)
+        cfg.update(config or {})
+        self.config = cfg
+        self.device = torch.device(device)
+        mc = ModelConfig()
+        nl = cfg['num_convolution_layer']
+        mc.n_layers, mc.n_species, mc.lmax = nl, cfg['num_species'], cfg['lmax']
+        for t, ir in enumerate(cfg['irreps_manual']):
+            for l, m in enumerate(ops.muls_of(ir)):
+                mc.mul[t][l] = m
+        mc.hidden[0], mc.hidden[1] = cfg['weight_nn_hidden_neurons']
+        mc.readout_hidden = ops.muls_of(cfg['irreps_manual'][-1])[0] // 2
+        mc.edge = edge_params_from_config(cfg)
+        mc.species_wise_rescale = int(bool(cfg['use_species_wise_shift_scale']))
+        self._cfg_struct = mc
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib().b200_model_create(C.byref(mc), C.byref(self._h)), 'model_create')
+        self._ws = None
+        if state_dict is not None:
+            self.load_state_dict(state_dict)
+
+    def load_state_dict(self, sd):
+        """sd: reference parameter names (named_parameters of the sevenn model) -> array/tensor."""
+        with torch.cuda.device(self.device):
+            for k, v in sd.items():
+                a = np.ascontiguousarray(v.detach().cpu().numpy() if torch.is_tensor(v) else v, dtype=np.float32).reshape(-1)
+                check(lib().b200_model_set_param(self._h, k.encode(), a.ctypes.data_as(C.c_void_p), a.size),
+                      f'model_set_param({k})')
+
+    def __del__(self):
+        try:
+            if getattr(self, '_h', None) is not None and self._h.value:
+                lib().b200_model_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def workspace_bytes(self, n_atoms, n_edges):
+        return lib().b200_model_workspace_bytes(self._h, int(n_atoms), int(n_edges))
+
+    def compute(self, types, rowptr, src, dst, edge_vec):
+        """types int32[N]; CSR sorted by dst: rowptr int32[N+1], src/dst int32[E]; edge_vec f32[E,3].
+        Returns energy[1], atomic_energy[N], force[N,3], virial[6] (device tensors)."""
+        N, E = types.shape[0], src.shape[0]
+        need = self.workspace_bytes(N, E)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = None
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        dev = self.device
+        energy = torch.empty(1, dtype=torch.float32, device=dev)
+        ae = torch.empty(N, dtype=torch.float32, device=dev)
+        force = torch.empty(N, 3, dtype=torch.float32, device=dev)
+        virial = torch.empty(6, dtype=torch.float32, device=dev)
+        p = ops._p
+        check(lib().b200_model_compute(self._h, N, E, p(types), p(rowptr), p(src), p(dst), p(edge_vec), p(self._ws),
+                                       self._ws.numel(), p(energy), p(ae), p(force), p(virial), ops._stream()),
+              'model_compute')
+        return energy, ae, force, virial
+
+    def calculate(self, pos, cell, pbc, types):
+        """One MD force call: radius graph + E/F/S.  pos float64 [N,3] (device), cell 3x3 (host),
+        types int32 [N] (device).  stress = -virial/volume in the model's order [xx,yy,zz,xy,yz,zx]
+        (sevenn/nn/force_output.py:186-213)."""
+        g = ops.radius_graph(pos, cell, pbc, self.config['cutoff'])
+        e, ae, f, vir = self.compute(types, g['rowptr'], g['src'], g['dst'], g['edge_vec'])
+        vol = abs(float(np.linalg.det(np.asarray(cell, np.float64).reshape(3, 3))))
+        stress = -vir / vol if vol > 0 else None
+        return dict(energy=e, atomic_energy=ae, forces=f, virial=vir, stress=stress, graph=g)
