@@ -1,0 +1,272 @@
+#!/usr/bin/env python
+"""bench.py - SevenNet-0 energy+forces+stress atom-steps/s on B200 (BASELINE.json metric).
+
+Workload at N=1: config 3 of BASELINE.json - one MD force call (radius graph + E + F + virial) on a
+100,000-atom synthetic amorphous cell (~5M edges), SevenNet-0 weights, fp32.  A "step" is one full
+force call with the graph rebuilt.  N>1: the halo-exchange decomposition is not built yet, so every
+rank runs an independent replica of the same cell ("replicas", weak scaling, no collective).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--atoms A] [--impl reference]
+
+One JSON line on stdout (rank 0).  `value` = device-resident inputs; `e2e` = host buffers in, host
+results out, through the public API (B200SevenNet.calculate).  `--impl reference` times the
+reference's own frozen TorchScript graph (oracle/_ref/deployed_serial.pt) on the host CPU cores on a
+bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'SevenNet-0 E+F+S atom-steps/s'
+UNIT = 'atom-steps/s'
+CAT_NAMES = ['edge_embed+csr', 'radial_mlp_fwd', 'conv_fwd', 'node_linear_gate', 'radial_mlp_bwd', 'conv_bwd_edge',
+             'conv_bwd_x', 'force_virial']
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        return dict(hbm=float(p['hbm_gbs']), tf=float(p['bf16_tflops_sustained']), src='measured')
+    except Exception:
+        return dict(hbm=6650.0, tf=1400.0, src='fallback')
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.rows, self.stop, self.index = [], False, index
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+        while not self.stop:
+            try:
+                out = subprocess.run(['nvidia-smi', f'--id={self.index}', f'--query-gpu={q}', '--format=csv,noheader,nounits'],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([t.strip() for t in out.split(',')])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=['unavailable'])
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith('active') for r in self.rows)]
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=float(self.rows[0][1]), reasons=reasons, samples=len(sm))
+
+
+def make_cell(n_atoms, seed=0):
+    from sevennet_finetuning_b200.synthetic import SPECIES_INDEX, amorphous_cell
+    pos, cell, pbc, sym = amorphous_cell(n_atoms, seed=seed)
+    types = np.array([SPECIES_INDEX[s] for s in sym], np.int32)
+    return pos, cell, pbc, types
+
+
+def load_weights():
+    return dict(np.load(os.path.join(ROOT, 'tests', 'golden', 'sevennet0_weights.npz')))
+
+
+def reference_cpu_time(n_atoms, steps, warmup, seed=1):
+    """The reference's own PyTorch CPU path: its frozen TorchScript graph on the host cores."""
+    from oracle.graph import radius_graph
+    path = os.path.join(ROOT, 'oracle', '_ref', 'deployed_serial.pt')
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    pos, cell, pbc, types = make_cell(n_atoms, seed)
+    kind = 'reference'
+    if os.path.exists(path):
+        ts = torch.jit.load(path, map_location='cpu').eval()
+
+        def call():
+            ei, S, D = radius_graph(pos, cell, pbc, 5.0)
+            d = {'x': torch.tensor(types, dtype=torch.long), 'pos': torch.tensor(pos, dtype=torch.float32).requires_grad_(True),
+                 'edge_index': torch.tensor(ei), 'pbc_shift': torch.tensor(S, dtype=torch.float32),
+                 'cell_lattice_vectors': torch.tensor(cell, dtype=torch.float32),
+                 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
+                 'num_atoms': torch.tensor(len(pos)), 'batch': torch.zeros(0, dtype=torch.long)}
+            o = ts(d)
+            return float(o['inferred_total_energy']), ei.shape[1]
+    else:  # the restated oracle (port) when the frozen graph did not travel
+        kind = 'port'
+        from oracle.refmodel import build_model
+        w = load_weights()
+        m = build_model(dict(shift=w['rescale_atomic_energy.shift'].tolist(), scale=w['rescale_atomic_energy.scale'].tolist(),
+                             conv_denominator=float(w['0_convolution.denominator'][0])))
+        m.load_state_dict({k: torch.tensor(v) for k, v in w.items()})
+        m.eval()
+        m.set_is_batch_data(False)
+
+        def call():
+            ei, S, D = radius_graph(pos, cell, pbc, 5.0)
+            o = m({'x': torch.tensor(types, dtype=torch.long), 'edge_index': torch.tensor(ei),
+                   'edge_vec': torch.tensor(D, dtype=torch.float32).requires_grad_(True),
+                   'num_atoms': torch.tensor(len(pos)), 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
+                   'batch': torch.zeros(0, dtype=torch.long)})
+            return float(o['inferred_total_energy']), ei.shape[1]
+    for _ in range(warmup):
+        call()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        _, ne = call()
+    dt = (time.perf_counter() - t0) / steps
+    return dict(value=n_atoms / dt, unit=UNIT, cores=cores, kind=kind,
+                sample=f'{n_atoms}-atom amorphous cell of the same generator, {ne} edges, {steps} timed calls '
+                       f'({dt:.2f} s/call), graph via the numpy restatement'), dt
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--atoms', type=int, default=100_000)
+    ap.add_argument('--impl', default='b200')
+    ap.add_argument('--cpu-atoms', type=int, default=600)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    a = ap.parse_args()
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    warmup = max(a.warmup, 3) if a.impl != 'reference' else a.warmup
+    cfg = {'workload': f'config 3: SevenNet-0 single-structure MD force call, {a.atoms}-atom synthetic amorphous cell '
+                       '(Si:O 1:2, ~50 edges/atom, 5 A cutoff), graph rebuilt every step',
+           'parallelism': 'replicas' if world > 1 else 'single', 'l2': 'inputs larger than L2'}
+
+    if a.impl == 'reference':
+        if rank != 0:
+            return
+        steps = max(1, min(a.steps, 3))
+        cb, dt = reference_cpu_time(a.cpu_atoms, steps, min(a.warmup, 1))
+        line = dict(metric=METRIC, value=cb['value'], unit=UNIT, n_gpus=a.gpus, steps=steps, warmup=min(a.warmup, 1),
+                    ms_per_step=dt * 1e3, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32',
+                    data='synthetic', config=cfg, impl='reference', cpu_baseline=cb,
+                    e2e=dict(value=cb['value'], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+        print(json.dumps(line))
+        return
+
+    import torch.distributed as dist
+    from sevennet_finetuning_b200 import _lib, ops
+    from sevennet_finetuning_b200.model import B200SevenNet
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    L = _lib.lib()
+    model = B200SevenNet(state_dict=load_weights(), device=dev)
+    pos, cell, pbc, types = make_cell(a.atoms, seed=rank)
+    pos_d = torch.tensor(pos, dtype=torch.float64, device=dev)
+    types_d = torch.tensor(types, dtype=torch.int32, device=dev)
+    pos_pin = torch.tensor(pos, dtype=torch.float64).pin_memory()
+    types_pin = torch.tensor(types, dtype=torch.int32).pin_memory()
+
+    def step_resident():
+        return model.calculate(pos_d, cell, pbc, types_d)
+
+    def step_e2e():
+        p = pos_pin.to(dev, non_blocking=True)
+        t = types_pin.to(dev, non_blocking=True)
+        o = model.calculate(p, cell, pbc, t)
+        return o['energy'].cpu(), o['forces'].cpu(), o['stress'].cpu()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = e0.elapsed_time(e1)
+        # host-synchronous pieces (edge count readback, D2H) sit between the events as well; use the larger
+        t = torch.tensor([max(ms * 1e-3, wall if fn is step_e2e else ms * 1e-3)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), out
+
+    for _ in range(warmup):
+        out = step_resident()
+    n_edges = int(out['graph']['src'].shape[0])
+    launches0 = L.b200_launch_count()
+    with ClockSampler(local) as cs:
+        L.b200_model_set_timing(model._h, 1)
+        t_res, out = timed(step_resident, a.steps)
+        cat = (C.c_float * 8)()
+        L.b200_model_get_timing(model._h, cat, 8)
+        L.b200_model_set_timing(model._h, 0)
+        launches = L.b200_launch_count() - launches0
+        for _ in range(2):
+            step_e2e()
+        t_e2e, _ = timed(step_e2e, a.steps)
+    clocks = cs.summary()
+    N, E = a.atoms, n_edges
+    value = world * N * a.steps / t_res
+    e2e_v = world * N * a.steps / t_e2e
+    pk = peaks()
+    cat_ms = {n: float(cat[k]) / a.steps for k, n in enumerate(CAT_NAMES)}
+    step_ms = t_res / a.steps * 1e3
+    # dominant kernel category -> roofline (algorithmic bytes/flops per step: SURVEY 8d)
+    conv_bytes = {'conv_fwd': 8292.0 * E + 43136.0 * N,
+                  'conv_bwd_edge': (16092.0 - 4 * 1920.0) * E + 43136.0 * N,  # x[src] read + weights; dOut read once per node
+                  'conv_bwd_x': 4 * 1920.0 * E}
+    mlp_flops = {'radial_mlp_fwd': 2.0 * (29184 + 3 * 66048 + 18944) * E, 'radial_mlp_bwd': 2.0 * (29184 + 3 * 66048 + 18944) * E}
+    dom = max(cat_ms, key=cat_ms.get)
+    if dom in mlp_flops:
+        ach = mlp_flops[dom] / (cat_ms[dom] * 1e-3) / 1e12
+        roof = dict(kernel=dom, bound='tensor', achieved=ach, peak=pk['tf'], unit='TFLOP/s', frac=ach / pk['tf'], traffic=None)
+    else:
+        byt = conv_bytes.get(dom, 24384.0 * E + 86272.0 * N)
+        ach = byt / (cat_ms[dom] * 1e-3) / 1e9
+        roof = dict(kernel=dom, bound='hbm', achieved=ach, peak=pk['hbm'], unit='GB/s', frac=ach / pk['hbm'], traffic=None)
+    roof['peak_source'] = pk['src']
+    roof['ms_per_step'] = cat_ms[dom]
+    step_bytes = 24384.0 * E + 86272.0 * N
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=a.steps, warmup=warmup, ms_per_step=step_ms,
+                higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32', data='synthetic', config=cfg,
+                n_atoms=N, n_edges=E,
+                e2e=dict(value=e2e_v, unit=UNIT, h2d_bytes_per_step=int(pos_pin.numel() * 8 + types_pin.numel() * 4),
+                         d2h_bytes_per_step=int(4 + N * 12 + 24), ms_per_step=t_e2e / a.steps * 1e3),
+                gpu_launches=int(launches), roofline=roof,
+                step_roofline=dict(bound='hbm', algorithmic_bytes=step_bytes, achieved=step_bytes / (step_ms * 1e-3) / 1e9,
+                                   peak=pk['hbm'], unit='GB/s', frac=step_bytes / (step_ms * 1e-3) / 1e9 / pk['hbm']),
+                kernel_ms_per_step=cat_ms, clocks=clocks)
+    if rank == 0:
+        if not a.no_cpu_baseline and world == 1:
+            line['cpu_baseline'], _ = reference_cpu_time(a.cpu_atoms, 2, 1)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -31,6 +31,8 @@ extern "C" {
 
 const char* b200_last_error(void);
 int b200_version(void);
+/* number of CUDA kernels this library has launched in this process (bench.py's gpu_launches) */
+long long b200_launch_count(void);
 
 /* ---- edge embedding: sevenn/nn/edge_embedding.py:202-230 (EdgeEmbedding.forward) ------------------ */
 typedef struct EdgeParams {
@@ -153,6 +155,13 @@ int b200_model_compute(B200Model* m, int n_atoms, int64_t n_edges, const int32_t
                        const int32_t* src, const int32_t* dst, const float* edge_vec, void* workspace,
                        size_t workspace_bytes, float* energy, float* atomic_energy, float* force, float* virial,
                        void* stream);
+
+/* optional per-category device timing of b200_model_compute (CUDA events on the compute stream).
+ * categories: 0 edge embedding+CSR, 1 radial MLP fwd, 2 conv fwd, 3 node linears/gate/readout,
+ * 4 radial MLP bwd, 5 conv bwd (weights, harmonics), 6 conv bwd (x), 7 force/virial */
+#define B200_TIMING_CATEGORIES 8
+int b200_model_set_timing(B200Model* m, int enable);
+int b200_model_get_timing(B200Model* m, float* ms_out, int n_out);
 
 #ifdef __cplusplus
 }

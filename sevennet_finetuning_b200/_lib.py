@@ -43,6 +43,7 @@ _P = C.POINTER
 SIGNATURES = {
     'b200_last_error': (C.c_char_p, []),
     'b200_version': (_i, []),
+    'b200_launch_count': (C.c_longlong, []),
     'b200_edge_embed_fwd': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_edge_embed_bwd': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_radial_mlp_fwd': (_i, [_P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
@@ -68,6 +69,8 @@ SIGNATURES = {
     'b200_model_set_param': (_i, [_vp, C.c_char_p, _vp, _i64]),
     'b200_model_destroy': (None, [_vp]),
     'b200_model_workspace_bytes': (_sz, [_vp, _i, _i64]),
+    'b200_model_set_timing': (_i, [_vp, _i]),
+    'b200_model_get_timing': (_i, [_vp, _vp, _i]),
     'b200_model_compute': (_i, [_vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
 }
 

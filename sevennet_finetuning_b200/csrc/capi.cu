@@ -1,5 +1,7 @@
 // extern "C" surface of libsevennet_b200.so (declared in include/sevennet_b200.h).
 #include <stdarg.h>
+
+#include <atomic>
 #include <string.h>
 
 #include "ops.h"
@@ -12,7 +14,9 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
-int check_launch(const char* what) {
+static std::atomic<long long> g_launches{0};
+int check_launch(const char* what, int n_launched) {
+  g_launches += n_launched;
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));
@@ -29,6 +33,7 @@ extern "C" {
 
 const char* b200_last_error(void) { return g_err; }
 int b200_version(void) { return 1; }
+long long b200_launch_count(void) { return g_launches.load(); }
 
 int b200_edge_embed_fwd(const EdgeParams* p, int64_t E, const float* vec, const float* coeffs, float* len, float* Y,
                         float* emb, void* stream) {

@@ -10,7 +10,7 @@ namespace b200 {
 
 // error channel of the C-ABI (SURVEY 8b "Errors": status code + b200_last_error()).
 void set_error(const char* fmt, ...);
-int check_launch(const char* what);
+int check_launch(const char* what, int n_launched = 1);  // also counts kernels for b200_launch_count()
 
 #define B200_REQUIRE(cond, ...)            \
   do {                                     \

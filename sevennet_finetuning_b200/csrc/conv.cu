@@ -584,7 +584,7 @@ int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, co
     launch_fwd<1, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
     launch_fwd<2, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
   }
-  return check_launch("conv_fwd");
+  return check_launch("conv_fwd", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
 }
 
 int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst, const float* gout,
@@ -600,7 +600,7 @@ int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid,
     launch_bwdx<1, 0>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
     launch_bwdx<2, 0>(d, n_src, rrowptr, eid, dst, gout, Y, w, inv, dx, st);
   }
-  return check_launch("conv_bwd_x");
+  return check_launch("conv_bwd_x", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
 }
 
 int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x, const float* Y,
@@ -621,7 +621,7 @@ int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, 
     if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
     if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
   }
-  return check_launch("conv_bwd_edge");
+  return check_launch("conv_bwd_edge", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
 }
 
 }  // namespace b200

@@ -95,7 +95,56 @@ struct B200Model {
   std::map<std::string, std::pair<float*, long long>> params;  // name -> (device ptr, numel)
   std::map<std::string, long long> expected;
   std::vector<float> denom;  // host copies of {t}_convolution.denominator
+  // optional per-category device timing (CUDA events on the compute stream)
+  bool timing = false;
+  std::vector<cudaEvent_t> ev;
+  std::vector<int> ev_cat;
+  size_t ev_used = 0;
 };
+
+enum { CAT_EDGE = 0, CAT_MLP_FWD, CAT_CONV_FWD, CAT_NODE, CAT_MLP_BWD, CAT_CONV_BWD_EDGE, CAT_CONV_BWD_X, CAT_FORCE, CAT_COUNT };
+
+static void tick(B200Model* m, int cat, cudaStream_t st) {
+  if (!m->timing) return;
+  if (m->ev_used + 2 > m->ev.size()) {
+    for (int k = 0; k < 64; ++k) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      m->ev.push_back(e);
+      m->ev_cat.push_back(-1);
+    }
+  }
+  m->ev_cat[m->ev_used] = cat;
+  cudaEventRecord(m->ev[m->ev_used++], st);
+}
+// OP(cat, call): run one launcher, bracketed by events when timing is on
+#define OP(cat, call)                 \
+  do {                                \
+    tick(m, cat, st);                 \
+    int rc_ = (call);                 \
+    tick(m, -1, st);                  \
+    if (rc_ != B200_OK) return rc_;   \
+  } while (0)
+
+extern "C" int b200_model_set_timing(B200Model* m, int enable) {
+  B200_REQUIRE(m, "model_set_timing: null model");
+  m->timing = enable != 0;
+  m->ev_used = 0;
+  return B200_OK;
+}
+// accumulated device milliseconds per category since set_timing(1); synchronises the device
+extern "C" int b200_model_get_timing(B200Model* m, float* ms_out, int n_out) {
+  B200_REQUIRE(m && ms_out && n_out >= CAT_COUNT, "model_get_timing: need %d output slots", (int)CAT_COUNT);
+  cudaDeviceSynchronize();
+  for (int k = 0; k < n_out; ++k) ms_out[k] = 0.f;
+  for (size_t k = 0; k + 1 < m->ev_used; k += 2) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, m->ev[k], m->ev[k + 1]);
+    ms_out[m->ev_cat[k]] += ms;
+  }
+  m->ev_used = 0;
+  return B200_OK;
+}
 
 static float* P(B200Model* m, const std::string& name) {
   auto it = m->params.find(name);
@@ -177,6 +226,7 @@ extern "C" int b200_model_set_param(B200Model* m, const char* name, const float*
 extern "C" void b200_model_destroy(B200Model* m) {
   if (!m) return;
   for (auto& kv : m->params) cudaFree(kv.second.first);
+  for (auto e : m->ev) cudaEventDestroy(e);
   delete m;
 }
 
@@ -272,63 +322,63 @@ extern "C" int b200_model_compute(B200Model* m, int N, int64_t E, const int32_t*
   const int nl = c.n_layers;
 
   // ---------------- forward ----------------
-  TRY(edge_embed_fwd(c.edge, E, edge_vec, coeffs, nullptr, b.Y, b.emb, st));
-  TRY(csr_transpose(N, E, src, b.tws, b.rrowptr, b.eid, st));
+  OP(CAT_EDGE, edge_embed_fwd(c.edge, E, edge_vec, coeffs, nullptr, b.Y, b.emb, st));
+  OP(CAT_EDGE, csr_transpose(N, E, src, b.tws, b.rrowptr, b.eid, st));
   float* x = b.x[0];
   float* xn = b.x[1];
-  TRY(embed_fwd(N, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
+  OP(CAT_NODE, embed_fwd(N, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
   const std::vector<float>& denom = m->denom;
   for (int t = 0; t < nl; ++t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
     if (!lin_covers_output(L.sc)) cudaMemsetAsync(b.gin[t], 0, sizeof(float) * (size_t)N * L.sc.out_dim, st);
-    TRY(irreps_linear(L.sc, N, x, P(m, s + "_self_connection_intro.linear.weight"), b.gin[t], 0, 0, st));
-    TRY(irreps_linear(L.si1, N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
-    TRY(radial_mlp_fwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
+    OP(CAT_NODE, irreps_linear(L.sc, N, x, P(m, s + "_self_connection_intro.linear.weight"), b.gin[t], 0, 0, st));
+    OP(CAT_NODE, irreps_linear(L.si1, N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+    OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
                        P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
                        b.w[t], st));
-    TRY(conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
-    TRY(irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
-    TRY(gate_fwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], xn, st));
+    OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
+    OP(CAT_NODE, irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
+    OP(CAT_NODE, gate_fwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], xn, st));
     std::swap(x, xn);
   }
-  TRY(irreps_linear(m->r1, N, x, P(m, "reduce_input_to_hidden.linear.weight"), b.h, 0, 0, st));
-  TRY(irreps_linear(m->r2, N, b.h, P(m, "reduce_hidden_to_energy.linear.weight"), b.s, 0, 0, st));
-  TRY(rescale_fwd(N, types, b.s, P(m, "rescale_atomic_energy.scale"), P(m, "rescale_atomic_energy.shift"),
+  OP(CAT_NODE, irreps_linear(m->r1, N, x, P(m, "reduce_input_to_hidden.linear.weight"), b.h, 0, 0, st));
+  OP(CAT_NODE, irreps_linear(m->r2, N, b.h, P(m, "reduce_hidden_to_energy.linear.weight"), b.s, 0, 0, st));
+  OP(CAT_NODE, rescale_fwd(N, types, b.s, P(m, "rescale_atomic_energy.scale"), P(m, "rescale_atomic_energy.shift"),
                   c.species_wise_rescale, atomic_energy, st));
-  TRY(colsum(N, 1, atomic_energy, energy, st));
+  OP(CAT_NODE, colsum(N, 1, atomic_energy, energy, st));
 
   // ---------------- reverse pass: dE/d edge_vec ----------------
   if (N > 0)
     rescale_bwd_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, types, P(m, "rescale_atomic_energy.scale"),
                                                         c.species_wise_rescale, b.g_s);
-  TRY(irreps_linear(m->r2, N, b.g_s, P(m, "reduce_hidden_to_energy.linear.weight"), b.g_h, 1, 0, st));
+  OP(CAT_NODE, irreps_linear(m->r2, N, b.g_s, P(m, "reduce_hidden_to_energy.linear.weight"), b.g_h, 1, 0, st));
   float* g = b.g_x[0];
   float* gp = b.g_x[1];
-  TRY(irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
+  OP(CAT_NODE, irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
   bool first_edge = true;
   for (int t = nl - 1; t >= 0; --t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
-    TRY(gate_bwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], g, b.g_gin, st));
-    TRY(irreps_linear(L.si2, N, b.g_gin, P(m, s + "_self_interaction_2.linear.weight"), b.g_conv, 1, 0, st));
-    TRY(conv_bwd_edge(L.conv, N, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw, b.dY,
+    OP(CAT_NODE, gate_bwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], g, b.g_gin, st));
+    OP(CAT_NODE, irreps_linear(L.si2, N, b.g_gin, P(m, s + "_self_interaction_2.linear.weight"), b.g_conv, 1, 0, st));
+    OP(CAT_CONV_BWD_EDGE, conv_bwd_edge(L.conv, N, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw, b.dY,
                       first_edge ? 0 : 1, st));
-    TRY(radial_mlp_bwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
+    OP(CAT_MLP_BWD, radial_mlp_bwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
                        P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
                        b.dw, b.demb, first_edge ? 0 : 1, st));
     first_edge = false;
     if (t > 0) {
       // features entering layer t depend on the positions through layers < t
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
-      TRY(irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
-      TRY(conv_bwd_x(L.conv, N, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
-      TRY(irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
+      OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
+      OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, N, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
+      OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
       std::swap(g, gp);
     }
   }
-  TRY(edge_embed_bwd(c.edge, E, edge_vec, coeffs, b.dY, b.demb, b.dvec, st));
-  TRY(force_virial(N, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
-  TRY(colsum(N, 6, b.virial_atom, virial, st));
-  return check_launch("model_compute");
+  OP(CAT_EDGE, edge_embed_bwd(c.edge, E, edge_vec, coeffs, b.dY, b.demb, b.dvec, st));
+  OP(CAT_FORCE, force_virial(N, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
+  OP(CAT_NODE, colsum(N, 6, b.virial_atom, virial, st));
+  return check_launch("model_compute", N > 0 ? 1 : 0);
 }

@@ -347,7 +347,7 @@ int graph_count(int n, const double* pos, const double* cell_host, const int* pb
   cudaMemcpyAsync(&total, rowptr + n, sizeof(int), cudaMemcpyDeviceToHost, st);
   cudaStreamSynchronize(st);
   *n_edges_host = total;
-  return check_launch("graph_count");
+  return check_launch("graph_count", 6);
 }
 
 int graph_fill(int n, const double* pos, const double* cell_host, const int* pbc_host, double cutoff, void* ws,
@@ -420,7 +420,7 @@ int csr_transpose(int n, long long E, const int* src, void* ws, int* rrowptr, in
     scatter_by_key_kernel<<<(unsigned)((E + 255) / 256), 256, 0, st>>>(E, src, rrowptr, cursor, eid);
     sort_rows_kernel<<<(unsigned)(((long long)n * 32 + 255) / 256), 256, 0, st>>>(n, rrowptr, eid);
   }
-  return check_launch("csr_transpose");
+  return check_launch("csr_transpose", E > 0 ? 4 : 1);
 }
 
 }  // namespace b200
