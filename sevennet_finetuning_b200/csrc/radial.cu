@@ -6,6 +6,8 @@
 //
 // CUDA-core SGEMM version (fp32 FFMA, 64-edge tiles, 4x4 register micro-tiles).  The hidden
 // activations never leave shared memory; only the [E, wn] weights are written.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200 {
@@ -208,6 +210,18 @@ radial_mlp_bwd_kernel(MlpDesc d, long long E, const float* __restrict__ emb, con
   }
 }
 
+// tensor-core (tcgen05, 3xTF32) versions live in radial_tc.cu; the FFMA kernels above serve the shapes they do
+// not cover (hidden widths != 64).  B200_RADIAL_FFMA=1 forces the FFMA kernels (A/B measurements, tests).
+bool radial_tc_supported(const MlpDesc& d);
+int radial_mlp_fwd_tc(const MlpDesc& d, long long E, const float* emb, const float* W0, const float* W1, const float* W2,
+                      float* w, cudaStream_t st);
+int radial_mlp_bwd_tc(const MlpDesc& d, long long E, const float* emb, const float* W0, const float* W1, const float* W2,
+                      const float* dw, float* demb, int accumulate, cudaStream_t st);
+static bool use_tc(const MlpDesc& d) {
+  const char* e = getenv("B200_RADIAL_FFMA");
+  return radial_tc_supported(d) && !(e && e[0] == '1');
+}
+
 static bool mlp_ok(const MlpDesc& d) {
   return d.nb >= 1 && d.nb <= RT_H && d.h1 >= 1 && d.h1 <= RT_H && d.h2 >= 1 && d.h2 <= RT_H && d.wn >= 1;
 }
@@ -216,6 +230,7 @@ int radial_mlp_fwd(const MlpDesc& d, long long E, const float* emb, const float*
                    float* w, cudaStream_t st) {
   B200_REQUIRE(mlp_ok(d), "radial_mlp_fwd: supported shape is [nb<=64, H1<=64, H2<=64, wn]");
   if (E == 0) return B200_OK;
+  if (use_tc(d)) return radial_mlp_fwd_tc(d, E, emb, W0, W1, W2, w, st);
   cudaFuncSetAttribute(radial_mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MlpSmem));
   radial_mlp_fwd_kernel<<<(unsigned)((E + RT_M - 1) / RT_M), RT_T, sizeof(MlpSmem), st>>>(d, E, emb, W0, W1, W2, w);
   return check_launch("radial_mlp_fwd");
@@ -225,6 +240,7 @@ int radial_mlp_bwd(const MlpDesc& d, long long E, const float* emb, const float*
                    const float* dw, float* demb, int accumulate, cudaStream_t st) {
   B200_REQUIRE(mlp_ok(d), "radial_mlp_bwd: supported shape is [nb<=64, H1<=64, H2<=64, wn]");
   if (E == 0) return B200_OK;
+  if (use_tc(d)) return radial_mlp_bwd_tc(d, E, emb, W0, W1, W2, dw, demb, accumulate, st);
   cudaFuncSetAttribute(radial_mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(MlpSmemBwd));
   radial_mlp_bwd_kernel<<<(unsigned)((E + RT_M - 1) / RT_M), RT_T, sizeof(MlpSmemBwd), st>>>(d, E, emb, W0, W1, W2, dw,
                                                                                               demb, accumulate);

@@ -123,10 +123,13 @@ def test_edge_embedding_fwd_bwd(dev, kind):
     assert _rel(ops.edge_embed_bwd(p, vec32, c32, gY32, gE32), gv_Y + gv_E) < 1e-5
 
 
-@pytest.mark.parametrize('wn,E', [(960, 1000), (384, 130), (224, 64), (100, 77)])
-def test_radial_mlp_fwd_bwd(dev, wn, E):
+@pytest.mark.parametrize('path', ['tcgen05', 'ffma'])
+@pytest.mark.parametrize('wn,E', [(960, 1000), (384, 130), (224, 64), (100, 77), (960, 128), (960, 129)])
+def test_radial_mlp_fwd_bwd(dev, wn, E, path, monkeypatch):
+    """both implementations of the radial MLP: tcgen05 3xTF32 (default) and the FFMA kernels"""
     from oracle import refnn
     from sevennet_finetuning_b200 import ops
+    monkeypatch.setenv('B200_RADIAL_FFMA', '1' if path == 'ffma' else '0')
     torch.manual_seed(0)
     net = refnn.FullyConnectedNet([8, 64, 64, wn], 'silu').double()
     emb = (torch.randn(E, 8, dtype=torch.float64) * 0.3).requires_grad_(True)
