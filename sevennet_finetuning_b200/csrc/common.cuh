@@ -22,10 +22,10 @@ int check_launch(const char* what, int n_launched = 1);  // also counts kernels 
 
 constexpr float kSilu2Mom = 1.6791767923989418f;  // e3nn normalize2mom(silu), frozen-graph constant c5
 
-__device__ __forceinline__ float silu_f(float z) { return z / (1.0f + __expf(-z)); }
+__device__ __forceinline__ float silu_f(float z) { return __fdividef(z, 1.0f + __expf(-z)); }
 // value and derivative of c*silu(z)
 __device__ __forceinline__ void silu_vd(float z, float& v, float& d) {
-  float s = 1.0f / (1.0f + __expf(-z));
+  float s = __fdividef(1.0f, 1.0f + __expf(-z));
   v = kSilu2Mom * z * s;
   d = kSilu2Mom * s * (1.0f + z * (1.0f - s));
 }

@@ -5,9 +5,9 @@
 // lives at (k/4) * (R*16) + r*16 + (k%4)*4 bytes, i.e. core matrices of 8 rows x 16 B are contiguous,
 // SBO (next 8-row group) = 128 B and LBO (next 16-byte K chunk) = R*16 B.  One MMA consumes K = 8.
 //
-// fp32 accuracy on tf32 tensor cores: every operand is split x = hi + lo with hi = x & 0xffffe000
-// (exactly representable in tf32) and lo = x - hi; D += lo_a*hi_b + hi_a*lo_b + hi_a*hi_b ("3xTF32"),
-// relative error of a product ~2^-21, accumulation in fp32 in TMEM.
+// fp32 accuracy on tf32 tensor cores: every operand is split x ~= hi + lo with hi = rna_tf32(x) and
+// lo = rna_tf32(x - hi); D += lo_a*hi_b + hi_a*lo_b + hi_a*hi_b ("3xTF32"), relative error of a product
+// ~2^-21 and unbiased, accumulation in fp32 in TMEM.
 #pragma once
 #include <stdint.h>
 
@@ -34,6 +34,18 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (done) break;
     if (clock64() - t0 > (1LL << 31)) __trap();
   }
+}
+
+// one thread: announce `bytes` of async-copy traffic on the barrier and arrive (barrier count 1)
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// one thread: bulk async copy global -> shared (TMA engine, no tensor map), completion counted on `bar`
+__device__ __forceinline__ void bulk_copy_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -94,10 +106,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-// x = hi + lo, hi exactly representable in tf32
+// x ~= hi + lo with both parts representable in tf32 (round-to-nearest): |x - hi - lo| <= 2^-22 |x|
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
 __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
-  hi = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
-  lo = x - hi;
+  hi = to_tf32(x);
+  lo = to_tf32(x - hi);
 }
 __device__ __forceinline__ void split4(const float4& v, float4& hi, float4& lo) {
   split_tf32(v.x, hi.x, lo.x);
