@@ -3,8 +3,10 @@
 
 Workload at N=1: config 3 of BASELINE.json - one MD force call (radius graph + E + F + virial) on a
 100,000-atom synthetic amorphous cell (~5M edges), SevenNet-0 weights, fp32.  A "step" is one full
-force call with the graph rebuilt.  N>1: the halo-exchange decomposition is not built yet, so every
-rank runs an independent replica of the same cell ("replicas", weak scaling, no collective).
+force call with the graph rebuilt.  N>1: config 4 - ONE cell of N x 131,072 atoms (1,048,576 at N=8) cut
+into N bricks (2x1x1 / 2x2x1 / 2x2x2), one rank per brick, ghost features exchanged per interaction layer
+over NCCL (sevennet_finetuning_b200/parallel.py); weak scaling (fixed atoms per GPU), value = atoms of the
+whole cell x steps / max-over-ranks time.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--atoms A] [--impl reference]
 
@@ -31,7 +33,7 @@ sys.path.insert(0, ROOT)
 METRIC = 'SevenNet-0 E+F+S atom-steps/s'
 UNIT = 'atom-steps/s'
 CAT_NAMES = ['edge_embed+csr', 'radial_mlp_fwd', 'conv_fwd', 'node_linear_gate', 'radial_mlp_bwd', 'conv_bwd_edge',
-             'conv_bwd_x', 'force_virial']
+             'conv_bwd_x', 'force_virial', 'halo_exchange']
 
 
 def peaks():
@@ -144,6 +146,7 @@ def main():
     ap.add_argument('--steps', type=int, default=5)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--atoms', type=int, default=100_000)
+    ap.add_argument('--atoms-per-gpu', type=int, default=131_072, help='N>1: the cell holds N x this many atoms')
     ap.add_argument('--impl', default='b200')
     ap.add_argument('--cpu-atoms', type=int, default=600)
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -152,9 +155,17 @@ def main():
     world = int(os.environ.get('WORLD_SIZE', 1))
     local = int(os.environ.get('LOCAL_RANK', 0))
     warmup = max(a.warmup, 3) if a.impl != 'reference' else a.warmup
-    cfg = {'workload': f'config 3: SevenNet-0 single-structure MD force call, {a.atoms}-atom synthetic amorphous cell '
-                       '(Si:O 1:2, ~50 edges/atom, 5 A cutoff), graph rebuilt every step',
-           'parallelism': 'replicas' if world > 1 else 'single', 'l2': 'inputs larger than L2'}
+    n_total = a.atoms if world == 1 else a.atoms_per_gpu * world
+    if world == 1:
+        cfg = {'workload': f'config 3: SevenNet-0 single-structure MD force call, {a.atoms}-atom synthetic amorphous cell '
+                           '(Si:O 1:2, ~50 edges/atom, 5 A cutoff), graph rebuilt every step',
+               'parallelism': 'single', 'l2': 'inputs larger than L2'}
+    else:
+        from sevennet_finetuning_b200.parallel import brick_grid
+        cfg = {'workload': f'config 4: SevenNet-0 spatially decomposed MD force call, one {n_total}-atom synthetic amorphous '
+                           f'cell (Si:O 1:2, ~50 edges/atom, 5 A cutoff) in {"x".join(map(str, brick_grid(world)))} bricks, '
+                           'ghost shell of one cutoff, per-layer halo exchange over NCCL, partition + graph rebuilt every step',
+               'parallelism': f'spatial{world}', 'l2': 'inputs larger than L2'}
 
     if a.impl == 'reference':
         if rank != 0:
@@ -177,19 +188,25 @@ def main():
         dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
     model = B200SevenNet(state_dict=load_weights(), device=dev)
-    pos, cell, pbc, types = make_cell(a.atoms, seed=rank)
+    pos, cell, pbc, types = make_cell(n_total, seed=0)
+    par = None
+    if world > 1:
+        from sevennet_finetuning_b200.parallel import ParallelSevenNet
+        par = ParallelSevenNet(model)
     pos_d = torch.tensor(pos, dtype=torch.float64, device=dev)
     types_d = torch.tensor(types, dtype=torch.int32, device=dev)
     pos_pin = torch.tensor(pos, dtype=torch.float64).pin_memory()
     types_pin = torch.tensor(types, dtype=torch.int32).pin_memory()
 
+    calc = model.calculate if par is None else par.calculate
+
     def step_resident():
-        return model.calculate(pos_d, cell, pbc, types_d)
+        return calc(pos_d, cell, pbc, types_d)
 
     def step_e2e():
         p = pos_pin.to(dev, non_blocking=True)
         t = types_pin.to(dev, non_blocking=True)
-        o = model.calculate(p, cell, pbc, t)
+        o = calc(p, cell, pbc, t)
         return o['energy'].cpu(), o['forces'].cpu(), o['stress'].cpu()
 
     def barrier():
@@ -216,36 +233,46 @@ def main():
 
     for _ in range(warmup):
         out = step_resident()
-    n_edges = int(out['graph']['src'].shape[0])
+    if par is None:
+        n_edges, n_own = int(out['graph']['src'].shape[0]), n_total
+    else:
+        cnt = torch.tensor([out['n_edges'], out['n_local'], out['n_ghost']], dtype=torch.int64, device=dev)
+        per_rank = [torch.zeros_like(cnt) for _ in range(world)]
+        dist.all_gather(per_rank, cnt)
+        per_rank = torch.stack(per_rank).cpu().numpy()
+        n_edges, n_own = int(per_rank[:, 0].sum()), int(out['n_local'])
+        cfg['per_rank'] = {'edges': per_rank[:, 0].tolist(), 'local': per_rank[:, 1].tolist(), 'ghost': per_rank[:, 2].tolist()}
     launches0 = L.b200_launch_count()
     with ClockSampler(local) as cs:
         L.b200_model_set_timing(model._h, 1)
         t_res, out = timed(step_resident, a.steps)
-        cat = (C.c_float * 8)()
-        L.b200_model_get_timing(model._h, cat, 8)
+        cat = (C.c_float * 9)()
+        L.b200_model_get_timing(model._h, cat, 9)
         L.b200_model_set_timing(model._h, 0)
         launches = L.b200_launch_count() - launches0
         for _ in range(2):
             step_e2e()
         t_e2e, _ = timed(step_e2e, a.steps)
     clocks = cs.summary()
-    N, E = a.atoms, n_edges
-    value = world * N * a.steps / t_res
-    e2e_v = world * N * a.steps / t_e2e
+    N, E = n_total, n_edges
+    value = N * a.steps / t_res
+    e2e_v = N * a.steps / t_e2e
     pk = peaks()
     cat_ms = {n: float(cat[k]) / a.steps for k, n in enumerate(CAT_NAMES)}
     step_ms = t_res / a.steps * 1e3
     # dominant kernel category -> roofline (algorithmic bytes/flops per step: SURVEY 8d)
-    conv_bytes = {'conv_fwd': 8292.0 * E + 43136.0 * N,
-                  'conv_bwd_edge': (16092.0 - 4 * 1920.0) * E + 43136.0 * N,  # x[src] read + weights; dOut read once per node
-                  'conv_bwd_x': 4 * 1920.0 * E}
-    mlp_flops = {'radial_mlp_fwd': 2.0 * (29184 + 3 * 66048 + 18944) * E, 'radial_mlp_bwd': 2.0 * (29184 + 3 * 66048 + 18944) * E}
-    dom = max(cat_ms, key=cat_ms.get)
+    # per-kernel figures are rank 0's (its own edges / atoms); the step figure is the whole job over N x peak
+    Ek, Nk = (E, N) if par is None else (int(out['n_edges']), int(out['n_local']))
+    conv_bytes = {'conv_fwd': 8292.0 * Ek + 43136.0 * Nk,
+                  'conv_bwd_edge': (16092.0 - 4 * 1920.0) * Ek + 43136.0 * Nk,  # x[src] read + weights; dOut read once per node
+                  'conv_bwd_x': 4 * 1920.0 * Ek}
+    mlp_flops = {'radial_mlp_fwd': 2.0 * (29184 + 3 * 66048 + 18944) * Ek, 'radial_mlp_bwd': 2.0 * (29184 + 3 * 66048 + 18944) * Ek}
+    dom = max((k for k in cat_ms if k != 'halo_exchange'), key=cat_ms.get)
     if dom in mlp_flops:
         ach = mlp_flops[dom] / (cat_ms[dom] * 1e-3) / 1e12
         roof = dict(kernel=dom, bound='tensor', achieved=ach, peak=pk['tf'], unit='TFLOP/s', frac=ach / pk['tf'], traffic=None)
     else:
-        byt = conv_bytes.get(dom, 24384.0 * E + 86272.0 * N)
+        byt = conv_bytes.get(dom, 24384.0 * Ek + 86272.0 * Nk)
         ach = byt / (cat_ms[dom] * 1e-3) / 1e9
         roof = dict(kernel=dom, bound='hbm', achieved=ach, peak=pk['hbm'], unit='GB/s', frac=ach / pk['hbm'], traffic=None)
     roof['peak_source'] = pk['src']
@@ -255,10 +282,11 @@ def main():
                 higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32', data='synthetic', config=cfg,
                 n_atoms=N, n_edges=E,
                 e2e=dict(value=e2e_v, unit=UNIT, h2d_bytes_per_step=int(pos_pin.numel() * 8 + types_pin.numel() * 4),
-                         d2h_bytes_per_step=int(4 + N * 12 + 24), ms_per_step=t_e2e / a.steps * 1e3),
+                         d2h_bytes_per_step=int(4 + n_own * 12 + 24), ms_per_step=t_e2e / a.steps * 1e3),
                 gpu_launches=int(launches), roofline=roof,
                 step_roofline=dict(bound='hbm', algorithmic_bytes=step_bytes, achieved=step_bytes / (step_ms * 1e-3) / 1e9,
-                                   peak=pk['hbm'], unit='GB/s', frac=step_bytes / (step_ms * 1e-3) / 1e9 / pk['hbm']),
+                                   peak=pk['hbm'] * world, unit='GB/s',
+                                   frac=step_bytes / (step_ms * 1e-3) / 1e9 / (pk['hbm'] * world)),
                 kernel_ms_per_step=cat_ms, clocks=clocks)
     if rank == 0:
         if not a.no_cpu_baseline and world == 1:

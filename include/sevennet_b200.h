@@ -156,10 +156,29 @@ int b200_model_compute(B200Model* m, int n_atoms, int64_t n_edges, const int32_t
                        size_t workspace_bytes, float* energy, float* atomic_energy, float* force, float* virial,
                        void* stream);
 
+/* ---- spatially decomposed force call: PairE3GNNParallel::compute (pair_e3gnn_parallel.cpp:347-454) ----------
+ * A rank owns n_local atoms and sees n_ghost ghosts (rows n_local .. n_local+n_ghost-1 of `types`, targets of
+ * `src` only; every edge's centre `dst` is local, as pair_e3gnn_parallel.cpp:277-314 builds them).
+ * rowptr has n_local+n_ghost+1 entries (ghost rows empty).  `halo` is called on the calling thread, between
+ * kernels enqueued on `stream`, where the reference does its LAMMPS comm (:397-400 forward, :446-453 reverse):
+ *   B200_HALO_FWD_X  rows[n_local+n_ghost, width]: fill the ghost rows from their owners   (layers >= 1)
+ *   B200_HALO_BWD_X  rows[...]: add each ghost row into its owner's local row               (layers >= 1)
+ *   B200_HALO_FORCE  rows = force[n_local+n_ghost, 3]: add ghost rows into the owners' rows (LAMMPS reverse_comm)
+ * The hook must enqueue its work stream-ordered with `stream` and return 0.  force has n_local+n_ghost rows. */
+#define B200_HALO_FWD_X 0
+#define B200_HALO_BWD_X 1
+#define B200_HALO_FORCE 2
+typedef int (*b200_halo_fn)(void* user, int phase, int layer, float* rows, int width);
+size_t b200_model_workspace_bytes_halo(const B200Model* m, int n_local, int n_ghost, int64_t n_edges);
+int b200_model_compute_halo(B200Model* m, int n_local, int n_ghost, int64_t n_edges, const int32_t* types,
+                            const int32_t* rowptr, const int32_t* src, const int32_t* dst, const float* edge_vec,
+                            void* workspace, size_t workspace_bytes, float* energy, float* atomic_energy, float* force,
+                            float* virial, b200_halo_fn halo, void* halo_user, void* stream);
+
 /* optional per-category device timing of b200_model_compute (CUDA events on the compute stream).
  * categories: 0 edge embedding+CSR, 1 radial MLP fwd, 2 conv fwd, 3 node linears/gate/readout,
- * 4 radial MLP bwd, 5 conv bwd (weights, harmonics), 6 conv bwd (x), 7 force/virial */
-#define B200_TIMING_CATEGORIES 8
+ * 4 radial MLP bwd, 5 conv bwd (weights, harmonics), 6 conv bwd (x), 7 force/virial, 8 halo exchange */
+#define B200_TIMING_CATEGORIES 9
 int b200_model_set_timing(B200Model* m, int enable);
 int b200_model_get_timing(B200Model* m, float* ms_out, int n_out);
 

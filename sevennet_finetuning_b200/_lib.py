@@ -38,6 +38,9 @@ class ModelConfig(C.Structure):
 
 _vp, _i, _i64, _f, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 _P = C.POINTER
+HALO_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int)
+B200_HALO_FWD_X, B200_HALO_BWD_X, B200_HALO_FORCE = 0, 1, 2
+B200_TIMING_CATEGORIES = 9
 
 # name -> (restype, argtypes); must list every symbol include/sevennet_b200.h declares
 SIGNATURES = {
@@ -71,6 +74,9 @@ SIGNATURES = {
     'b200_model_workspace_bytes': (_sz, [_vp, _i, _i64]),
     'b200_model_set_timing': (_i, [_vp, _i]),
     'b200_model_get_timing': (_i, [_vp, _vp, _i]),
+    'b200_model_workspace_bytes_halo': (_sz, [_vp, _i, _i, _i64]),
+    'b200_model_compute_halo': (_i, [_vp, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp,
+                                     _vp]),
     'b200_model_compute': (_i, [_vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp, _vp, _vp]),
 }
 

@@ -102,7 +102,7 @@ struct B200Model {
   size_t ev_used = 0;
 };
 
-enum { CAT_EDGE = 0, CAT_MLP_FWD, CAT_CONV_FWD, CAT_NODE, CAT_MLP_BWD, CAT_CONV_BWD_EDGE, CAT_CONV_BWD_X, CAT_FORCE, CAT_COUNT };
+enum { CAT_EDGE = 0, CAT_MLP_FWD, CAT_CONV_FWD, CAT_NODE, CAT_MLP_BWD, CAT_CONV_BWD_EDGE, CAT_CONV_BWD_X, CAT_FORCE, CAT_HALO, CAT_COUNT };
 
 static void tick(B200Model* m, int cat, cudaStream_t st) {
   if (!m->timing) return;
@@ -246,7 +246,8 @@ struct Buffers {
   int *rrowptr, *eid;
   void* tws;
 };
-void plan_buffers(const B200Model* m, int N, long long E, Plan& p, Buffers& b) {
+void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buffers& b) {
+  const int N = NL;
   int maxx = 0, maxg = 0, maxmsg = 0, maxwn = 0;
   for (const Layer& L : m->layers) {
     maxx = std::max(maxx, L.conv.xdim);
@@ -262,25 +263,25 @@ void plan_buffers(const B200Model* m, int N, long long E, Plan& p, Buffers& b) {
   b.demb = p.take<float>((size_t)E * nb);
   b.dvec = p.take<float>((size_t)E * 3);
   b.dw = p.take<float>((size_t)E * maxwn);
-  for (int k = 0; k < 2; ++k) b.x[k] = p.take<float>((size_t)N * maxx);
+  for (int k = 0; k < 2; ++k) b.x[k] = p.take<float>((size_t)NA * maxx);
   for (int k = 0; k < 2; ++k) b.g_x[k] = p.take<float>((size_t)N * maxx);
-  b.conv_out = p.take<float>((size_t)N * maxmsg);
+  b.conv_out = p.take<float>((size_t)NA * maxmsg);
   b.g_conv = p.take<float>((size_t)N * maxmsg);
   b.g_gin = p.take<float>((size_t)N * maxg);
   b.h = p.take<float>((size_t)N * m->r1.out_dim);
   b.g_h = p.take<float>((size_t)N * m->r1.out_dim);
   b.s = p.take<float>((size_t)N);
   b.g_s = p.take<float>((size_t)N);
-  b.virial_atom = p.take<float>((size_t)N * 6);
+  b.virial_atom = p.take<float>((size_t)NA * 6);
   b.w.clear(); b.xs.clear(); b.gin.clear();
   for (const Layer& L : m->layers) {
     b.w.push_back(p.take<float>((size_t)E * L.conv.wn));
-    b.xs.push_back(p.take<float>((size_t)N * L.conv.xdim));
+    b.xs.push_back(p.take<float>((size_t)NA * L.conv.xdim));
     b.gin.push_back(p.take<float>((size_t)N * L.sc.out_dim));
   }
-  b.rrowptr = p.take<int>((size_t)N + 1);
+  b.rrowptr = p.take<int>((size_t)NA + 1);
   b.eid = p.take<int>((size_t)E);
-  b.tws = p.take<char>(transpose_workspace_bytes(N, E));
+  b.tws = p.take<char>(transpose_workspace_bytes(NA, E));
 }
 
 __global__ void rescale_bwd_kernel(int n, const int* __restrict__ types, const float* __restrict__ scale, int species_wise,
@@ -290,11 +291,14 @@ __global__ void rescale_bwd_kernel(int n, const int* __restrict__ types, const f
 }
 }  // namespace
 
-extern "C" size_t b200_model_workspace_bytes(const B200Model* m, int n_atoms, int64_t n_edges) {
+extern "C" size_t b200_model_workspace_bytes_halo(const B200Model* m, int n_local, int n_ghost, int64_t n_edges) {
   Plan p;
   Buffers b;
-  plan_buffers(m, n_atoms, n_edges, p, b);
+  plan_buffers(m, n_local, n_local + n_ghost, n_edges, p, b);
   return p.off + 256;
+}
+extern "C" size_t b200_model_workspace_bytes(const B200Model* m, int n_atoms, int64_t n_edges) {
+  return b200_model_workspace_bytes_halo(m, n_atoms, 0, n_edges);
 }
 
 #define TRY(call)                 \
@@ -303,19 +307,36 @@ extern "C" size_t b200_model_workspace_bytes(const B200Model* m, int n_atoms, in
     if (rc_ != B200_OK) return rc_; \
   } while (0)
 
-extern "C" int b200_model_compute(B200Model* m, int N, int64_t E, const int32_t* types, const int32_t* rowptr,
-                                  const int32_t* src, const int32_t* dst, const float* edge_vec, void* workspace,
-                                  size_t workspace_bytes, float* energy, float* atomic_energy, float* force,
-                                  float* virial, void* stream) {
+// halo hook: called on the compute stream's host thread at the exchange points (see header)
+#define HALO(phase, layer, rows, width)                                                   \
+  do {                                                                                    \
+    if (halo) {                                                                           \
+      tick(m, CAT_HALO, st);                                                              \
+      int rc_ = halo(halo_user, phase, layer, rows, width);                               \
+      tick(m, -1, st);                                                                    \
+      if (rc_ != 0) {                                                                     \
+        set_error("model_compute: halo callback failed (phase %d, layer %d)", phase, layer); \
+        return B200_ERR_INVALID;                                                          \
+      }                                                                                   \
+    }                                                                                     \
+  } while (0)
+
+extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t E, const int32_t* types,
+                                       const int32_t* rowptr, const int32_t* src, const int32_t* dst,
+                                       const float* edge_vec, void* workspace, size_t workspace_bytes, float* energy,
+                                       float* atomic_energy, float* force, float* virial, b200_halo_fn halo,
+                                       void* halo_user, void* stream) {
   B200_REQUIRE(m, "model_compute: null model");
+  B200_REQUIRE(N >= 0 && n_ghost >= 0 && (n_ghost == 0 || halo), "model_compute: ghosts need a halo callback");
   for (auto& kv : m->expected)
     B200_REQUIRE(m->params.count(kv.first), "model_compute: parameter '%s' was never set", kv.first.c_str());
   B200_REQUIRE(E < (1LL << 31), "model_compute: more than 2^31 edges per device");
   cudaStream_t st = (cudaStream_t)stream;
+  const int NA = N + n_ghost;   // rows that can be edge sources: local atoms then ghosts
   Plan p;
   p.base = (char*)(((uintptr_t)workspace + 255) / 256 * 256);
   Buffers b;
-  plan_buffers(m, N, E, p, b);
+  plan_buffers(m, N, NA, E, p, b);
   B200_REQUIRE(p.off + 256 <= workspace_bytes, "model_compute: workspace too small (%zu needed)", p.off + 256);
   const B200ModelConfig& c = m->cfg;
   const float* coeffs = P(m, "edge_embedding.basis_function.coeffs");
@@ -323,17 +344,20 @@ extern "C" int b200_model_compute(B200Model* m, int N, int64_t E, const int32_t*
 
   // ---------------- forward ----------------
   OP(CAT_EDGE, edge_embed_fwd(c.edge, E, edge_vec, coeffs, nullptr, b.Y, b.emb, st));
-  OP(CAT_EDGE, csr_transpose(N, E, src, b.tws, b.rrowptr, b.eid, st));
+  OP(CAT_EDGE, csr_transpose(NA, E, src, b.tws, b.rrowptr, b.eid, st));
   float* x = b.x[0];
   float* xn = b.x[1];
-  OP(CAT_NODE, embed_fwd(N, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
+  OP(CAT_NODE, embed_fwd(NA, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
   const std::vector<float>& denom = m->denom;
   for (int t = 0; t < nl; ++t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
     if (!lin_covers_output(L.sc)) cudaMemsetAsync(b.gin[t], 0, sizeof(float) * (size_t)N * L.sc.out_dim, st);
     OP(CAT_NODE, irreps_linear(L.sc, N, x, P(m, s + "_self_connection_intro.linear.weight"), b.gin[t], 0, 0, st));
-    OP(CAT_NODE, irreps_linear(L.si1, N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+    // layer 0: ghost rows are recomputed from their types (model_build.py:134-172 "ghost_" modules);
+    // later layers: the owners' rows are fetched through the halo hook
+    OP(CAT_NODE, irreps_linear(L.si1, t == 0 ? NA : N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+    if (t > 0) HALO(B200_HALO_FWD_X, t, b.xs[t], L.conv.xdim);
     OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
                        P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
                        b.w[t], st));
@@ -372,13 +396,23 @@ extern "C" int b200_model_compute(B200Model* m, int N, int64_t E, const int32_t*
       // features entering layer t depend on the positions through layers < t
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
       OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
-      OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, N, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
+      OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
+      HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
       OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
       std::swap(g, gp);
     }
   }
   OP(CAT_EDGE, edge_embed_bwd(c.edge, E, edge_vec, coeffs, b.dY, b.demb, b.dvec, st));
-  OP(CAT_FORCE, force_virial(N, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
-  OP(CAT_NODE, colsum(N, 6, b.virial_atom, virial, st));
+  OP(CAT_FORCE, force_virial(NA, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
+  HALO(B200_HALO_FORCE, -1, force, 3);
+  OP(CAT_NODE, colsum(NA, 6, b.virial_atom, virial, st));   // per-source rows (force_output.py:186-213): ghosts included
   return check_launch("model_compute", N > 0 ? 1 : 0);
+}
+
+extern "C" int b200_model_compute(B200Model* m, int N, int64_t E, const int32_t* types, const int32_t* rowptr,
+                                  const int32_t* src, const int32_t* dst, const float* edge_vec, void* workspace,
+                                  size_t workspace_bytes, float* energy, float* atomic_energy, float* force,
+                                  float* virial, void* stream) {
+  return b200_model_compute_halo(m, N, 0, E, types, rowptr, src, dst, edge_vec, workspace, workspace_bytes, energy,
+                                 atomic_energy, force, virial, nullptr, nullptr, stream);
 }

@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import ops
-from ._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, EdgeParams, ModelConfig, check, lib
+from ._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, HALO_FN, EdgeParams, ModelConfig, check, lib
 
 SEVENNET0_CONFIG = dict(
     cutoff=5.0, num_species=89, lmax=2, num_convolution_layer=5,
@@ -28,6 +28,13 @@ def edge_params_from_config(cfg):
     return EdgeParams(int(cfg['bessel_basis_num']), B200_CUTOFF_XPLOR if xpl else B200_CUTOFF_POLY,
                       int(bool(cfg.get('normalize_sph', True))), float(cfg['cutoff']),
                       float(cf.get('cutoff_on', 0.0)), float(cf.get('poly_cut_p_value', 6)))
+
+
+def _wrap_rows(ptr, n_rows, width, dev):
+    """Zero-copy fp32 [n_rows, width] view of engine workspace memory handed to the halo hook."""
+    class _Arr:
+        __cuda_array_interface__ = dict(shape=(n_rows, width), typestr='<f4', data=(int(ptr), False), version=2)
+    return torch.as_tensor(_Arr(), device=dev)
 
 
 class B200SevenNet:
@@ -72,26 +79,43 @@ class B200SevenNet:
         except Exception:
             pass
 
-    def workspace_bytes(self, n_atoms, n_edges):
-        return lib().b200_model_workspace_bytes(self._h, int(n_atoms), int(n_edges))
+    def workspace_bytes(self, n_atoms, n_edges, n_ghost=0):
+        return lib().b200_model_workspace_bytes_halo(self._h, int(n_atoms), int(n_ghost), int(n_edges))
 
-    def compute(self, types, rowptr, src, dst, edge_vec):
-        """types int32[N]; CSR sorted by dst: rowptr int32[N+1], src/dst int32[E]; edge_vec f32[E,3].
-        Returns energy[1], atomic_energy[N], force[N,3], virial[6] (device tensors)."""
-        N, E = types.shape[0], src.shape[0]
-        need = self.workspace_bytes(N, E)
+    def compute(self, types, rowptr, src, dst, edge_vec, n_ghost=0, halo=None):
+        """types int32[N+n_ghost]; CSR sorted by dst: rowptr int32[N+n_ghost+1], src/dst int32[E]; edge_vec f32[E,3].
+        halo(phase, layer, rows) is the exchange hook of the spatially decomposed call (parallel.py).
+        Returns energy[1], atomic_energy[N], force[N+n_ghost,3], virial[6] (device tensors)."""
+        NA, E = types.shape[0], src.shape[0]
+        N = NA - int(n_ghost)
+        need = self.workspace_bytes(N, E, n_ghost)
         if self._ws is None or self._ws.numel() < need:
             self._ws = None
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         dev = self.device
         energy = torch.empty(1, dtype=torch.float32, device=dev)
         ae = torch.empty(N, dtype=torch.float32, device=dev)
-        force = torch.empty(N, 3, dtype=torch.float32, device=dev)
+        force = torch.empty(NA, 3, dtype=torch.float32, device=dev)
         virial = torch.empty(6, dtype=torch.float32, device=dev)
         p = ops._p
-        check(lib().b200_model_compute(self._h, N, E, p(types), p(rowptr), p(src), p(dst), p(edge_vec), p(self._ws),
-                                       self._ws.numel(), p(energy), p(ae), p(force), p(virial), ops._stream()),
-              'model_compute')
+        err = []
+        cb = None
+        if halo is not None:
+            def _hook(user, phase, layer, rows_ptr, width):
+                try:
+                    rows = _wrap_rows(rows_ptr, NA, width, dev)
+                    halo(phase, layer, rows)
+                    return 0
+                except Exception as ex:  # never unwind through the C frame
+                    err.append(ex)
+                    return 1
+            cb = HALO_FN(_hook)
+        rc = lib().b200_model_compute_halo(self._h, N, int(n_ghost), E, p(types), p(rowptr), p(src), p(dst), p(edge_vec),
+                                           p(self._ws), self._ws.numel(), p(energy), p(ae), p(force), p(virial),
+                                           C.cast(cb, C.c_void_p) if cb is not None else None, None, ops._stream())
+        if err:
+            raise err[0]
+        check(rc, 'model_compute')
         return energy, ae, force, virial
 
     def calculate(self, pos, cell, pbc, types):
