@@ -61,12 +61,17 @@ __global__ void edge_embed_fwd_kernel(EdgeParams p, long long E, const float* __
 // dvec = dE/d edge_vec from dE/dY (components 1..8; component 0 is the constant 1) and dE/d emb
 __global__ void edge_embed_bwd_kernel(EdgeParams p, long long E, const float* __restrict__ vec,
                                       const float* __restrict__ coeffs, const float* __restrict__ dY,
-                                      const float* __restrict__ demb, float* __restrict__ dvec) {
+                                      const float* __restrict__ demb, const float* __restrict__ dr_in,
+                                      float* __restrict__ dvec) {
   const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (e >= E) return;
   const float vx = vec[e * 3], vy = vec[e * 3 + 1], vz = vec[e * 3 + 2];
   const float r = sqrtf(vx * vx + vy * vy + vz * vz);
   float gx = 0.f, gy = 0.f, gz = 0.f;
+  if (dr_in) {   // dE/dr given directly (fused convolution backward)
+    const float t = dr_in[e] / r;
+    gx = t * vx; gy = t * vy; gz = t * vz;
+  }
   if (demb) {
     float f, df;
     cutoff_vd(p, r, f, df);
@@ -81,7 +86,7 @@ __global__ void edge_embed_bwd_kernel(EdgeParams p, long long E, const float* __
       dr += demb[e * p.num_basis + n] * (db * f + b * df);
     }
     const float ir = 1.0f / r;
-    gx = dr * vx * ir; gy = dr * vy * ir; gz = dr * vz * ir;
+    gx += dr * vx * ir; gy += dr * vy * ir; gz += dr * vz * ir;
   }
   if (dY) {
     const float* g = dY + e * 9;
@@ -153,8 +158,15 @@ int edge_embed_fwd(const EdgeParams& p, long long E, const float* vec, const flo
 int edge_embed_bwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
                    const float* demb, float* dvec, cudaStream_t st) {
   if (E == 0) return B200_OK;
-  edge_embed_bwd_kernel<<<(unsigned)((E + 255) / 256), 256, 0, st>>>(p, E, vec, coeffs, dY, demb, dvec);
+  edge_embed_bwd_kernel<<<(unsigned)((E + 255) / 256), 256, 0, st>>>(p, E, vec, coeffs, dY, demb, nullptr, dvec);
   return check_launch("edge_embed_bwd");
+}
+
+int edge_embed_bwd_r(const EdgeParams& p, long long E, const float* vec, const float* dY, const float* dr, float* dvec,
+                     cudaStream_t st) {
+  if (E == 0) return B200_OK;
+  edge_embed_bwd_kernel<<<(unsigned)((E + 255) / 256), 256, 0, st>>>(p, E, vec, nullptr, dY, nullptr, dr, dvec);
+  return check_launch("edge_embed_bwd_r");
 }
 
 int force_virial(int n_atoms, const int* rowptr, const int* rrowptr, const int* eid_by_src, const float* vec,

@@ -10,6 +10,8 @@ int edge_embed_fwd(const EdgeParams& p, long long E, const float* vec, const flo
                    float* emb, cudaStream_t st);
 int edge_embed_bwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
                    const float* demb, float* dvec, cudaStream_t st);
+int edge_embed_bwd_r(const EdgeParams& p, long long E, const float* vec, const float* dY, const float* dr, float* dvec,
+                     cudaStream_t st);
 int force_virial(int n_atoms, const int* rowptr, const int* rrowptr, const int* eid_by_src, const float* vec,
                  const float* dvec, float* force, float* virial_atom, cudaStream_t st);
 
@@ -25,6 +27,17 @@ int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid,
 int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x,
                   const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
                   cudaStream_t st);
+
+// fused path (fused.cu): radial operand tiles, then convolution forward / backward with the weights kept in TMEM
+bool fused_supported(const ConvDesc& d, const MlpDesc& m);
+size_t fused_radial_bytes(long long E);
+int fused_radial(const EdgeParams& ep, const MlpDesc& m, long long E, const float* vec, const float* coeffs, const float* W0,
+                 const float* W1, float* tiles, cudaStream_t st);
+int fused_conv_fwd(const ConvDesc& d, int n_dst, long long E, const int* dst, const int* src, const float* x, const float* Y,
+                   const float* tiles, const float* W2, float denom, float* out, cudaStream_t st);
+int fused_conv_bwd(const ConvDesc& d, int n_src, long long E, const int* dst, const int* src, const float* x, const float* Y,
+                   const float* tiles, const float* W2, const float* gout, float denom, float* dx, float* dY, float* dr,
+                   int accumulate, cudaStream_t st);
 
 int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
                   cudaStream_t st);

@@ -246,3 +246,45 @@ def colsum(x):
     out = torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
     check(lib().b200_colsum(x.shape[0], x.shape[1], _p(x), _p(out), _stream()), 'colsum')
     return out
+
+
+# ---- fused convolution (radial MLP output layer on tcgen05 inside the convolution kernels) -----------------------------
+def fused_supported(muls, lout, nb, h1, h2, wn):
+    return bool(lib().b200_fused_supported(*muls, lout, C.byref(MlpDesc(nb, h1, h2, wn))))
+
+
+def fused_radial(params, vec, coeffs, W0, W1):
+    """Hidden activations of weight_nn (and their d/dr tangents) for every edge, as tcgen05 operand tiles."""
+    E = vec.shape[0]
+    d = MlpDesc(W0.shape[0], W0.shape[1], W1.shape[1], 0)
+    buf = torch.empty(lib().b200_fused_radial_bytes(E) // 4, dtype=torch.float32, device=vec.device)
+    check(lib().b200_fused_radial(C.byref(params), C.byref(d), E, _p(vec), _p(coeffs), _p(W0), _p(W1), _p(buf), _stream()),
+          'fused_radial')
+    return buf
+
+
+def fused_conv_fwd(muls, lout, n_dst, dst, src, x, Y, radial, W2, denom):
+    _, od = conv_dims(*muls, lout)
+    out = torch.empty(n_dst, od, dtype=torch.float32, device=x.device)
+    check(lib().b200_fused_conv_fwd(*muls, lout, n_dst, src.shape[0], _p(dst), _p(src), _p(x), _p(Y), _p(radial), _p(W2),
+                                    float(denom), _p(out), _stream()), 'fused_conv_fwd')
+    return out
+
+
+def fused_conv_bwd(muls, lout, dst, src, x, Y, radial, W2, gout, denom, dY=None, dr=None):
+    E = src.shape[0]
+    acc = dY is not None
+    if dY is None:
+        dY = torch.zeros(E, 9, dtype=torch.float32, device=x.device)
+        dr = torch.empty(E, dtype=torch.float32, device=x.device)
+    dx = torch.empty_like(x)
+    check(lib().b200_fused_conv_bwd(*muls, lout, x.shape[0], E, _p(dst), _p(src), _p(x), _p(Y), _p(radial), _p(W2), _p(gout),
+                                    float(denom), _p(dx), _p(dY), _p(dr), int(acc), _stream()), 'fused_conv_bwd')
+    return dx, dY, dr
+
+
+def edge_embed_bwd_r(params, vec, dY, dr):
+    E = vec.shape[0]
+    dvec = torch.empty(E, 3, dtype=torch.float32, device=vec.device)
+    check(lib().b200_edge_embed_bwd_r(C.byref(params), E, _p(vec), _p(dY), _p(dr), _p(dvec), _stream()), 'edge_embed_bwd_r')
+    return dvec
