@@ -87,7 +87,7 @@ int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* 
  *      Edges sorted by dst (= edge_index[0]); `radial` is the buffer b200_fused_radial fills once per layer and
  *      graph (hidden activations of weight_nn and their d/dr tangents, b200_fused_radial_bytes(E) bytes).
  *      Forward:  out[n_dst, out_dim] (zeroed inside) = scatter_sum(TP(x[src], Y, weight_nn(r))) / denominator.
- *      Backward: d_x[n_src, x_dim] (zeroed inside), d_Y[E,9] (component 0 untouched) and d_r[E] = dE/d|edge_vec|
+ *      Backward: d_x[n_src, x_dim] (zeroed inside; NULL = not wanted), d_Y[E,9] (component 0 untouched) and d_r[E] = dE/d|edge_vec|
  *      through the radial MLP (accumulate=1 adds to d_Y, d_r).  Needs multiplicities that are multiples of 32
  *      (<= 128x0e, 64x1e, 32x2e) and a [nb<=16, 64, 64, wn] weight_nn: b200_fused_supported() tells. */
 int b200_fused_supported(int m0, int m1, int m2, int lout, const MlpDesc* mlp);

@@ -163,7 +163,7 @@ int b200_fused_conv_bwd(int m0, int m1, int m2, int lout, int n_src, int64_t E, 
                         const float* x, const float* Y, const float* radial, const float* W2, const float* d_out,
                         float denom, float* d_x, float* d_Y, float* d_r, int accumulate, void* stream) {
   B200_REQUIRE(lout == 0 || lout == 2, "fused_conv_bwd: lout must be 0 or 2");
-  B200_REQUIRE(W2 && d_x && (E == 0 || (dst && src && x && Y && radial && d_out && d_Y && d_r)), "fused_conv_bwd: null argument");
+  B200_REQUIRE(W2 && (E == 0 || (dst && src && x && Y && radial && d_out && d_Y && d_r)), "fused_conv_bwd: null argument");
   ConvDesc d;
   fill_conv_desc(m0, m1, m2, lout, d);
   return fused_conv_bwd(d, n_src, E, dst, src, x, Y, radial, W2, d_out, denom, d_x, d_Y, d_r, accumulate, ST(stream));

@@ -162,6 +162,13 @@ int edge_embed_bwd(const EdgeParams& p, long long E, const float* vec, const flo
   return check_launch("edge_embed_bwd");
 }
 
+int edge_embed_bwd_full(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
+                        const float* demb, const float* dr, float* dvec, cudaStream_t st) {
+  if (E == 0) return B200_OK;
+  edge_embed_bwd_kernel<<<(unsigned)((E + 255) / 256), 256, 0, st>>>(p, E, vec, coeffs, dY, demb, dr, dvec);
+  return check_launch("edge_embed_bwd");
+}
+
 int edge_embed_bwd_r(const EdgeParams& p, long long E, const float* vec, const float* dY, const float* dr, float* dvec,
                      cudaStream_t st) {
   if (E == 0) return B200_OK;

@@ -5,6 +5,8 @@
 // Layer order follows sevenn/model_build.py:219-437 and nn/interaction_blocks.py:49-84:
 //   edge_embedding -> onehot embedding -> for t: sc_intro | self_interaction_1 -> convolution ->
 //   self_interaction_2 -> (+ self connection) -> gate;  readout 2 linears -> rescale -> sum.
+#include <stdlib.h>
+
 #include <map>
 #include <string>
 #include <vector>
@@ -82,6 +84,7 @@ struct Layer {
   MlpDesc mlp;
   LinDesc sc, si1, si2;
   int lout;
+  bool fused;   // radial layer + convolution run as the fused tcgen05 kernels (fused.cu)
 };
 
 }  // namespace b200
@@ -173,6 +176,7 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.sc = make_linear(L.in, L.gin);
     L.si1 = make_linear(L.in, L.in);
     L.si2 = make_linear(L.msg, L.gin);
+    L.fused = fused_supported(L.conv, L.mlp) && !getenv("B200_NO_FUSED");
     m->layers.push_back(L);
     const std::string s = std::to_string(t);
     m->expected[s + "_self_connection_intro.linear.weight"] = lin_numel(L.sc);
@@ -241,8 +245,8 @@ struct Plan {
   }
 };
 struct Buffers {
-  float *Y, *emb, *dY, *demb, *dvec, *dw, *x[2], *conv_out, *g_x[2], *g_gin, *g_conv, *h, *s, *g_h, *g_s, *virial_atom;
-  std::vector<float*> w, xs, gin;
+  float *Y, *emb, *dY, *demb, *ddr, *dvec, *dw, *x[2], *conv_out, *g_x[2], *g_gin, *g_conv, *h, *s, *g_h, *g_s, *virial_atom;
+  std::vector<float*> w, xs, gin, rad;
   int *rrowptr, *eid;
   void* tws;
 };
@@ -253,7 +257,7 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
     maxx = std::max(maxx, L.conv.xdim);
     maxg = std::max(maxg, L.sc.out_dim);
     maxmsg = std::max(maxmsg, L.conv.odim);
-    maxwn = std::max(maxwn, L.conv.wn);
+    if (!L.fused) maxwn = std::max(maxwn, L.conv.wn);   // un-fused layers materialise [E, wn] weights and their gradient
   }
   maxx = std::max(maxx, m->r1.in_dim);
   const int nb = m->cfg.edge.num_basis;
@@ -261,6 +265,7 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
   b.emb = p.take<float>((size_t)E * nb);
   b.dY = p.take<float>((size_t)E * 9);
   b.demb = p.take<float>((size_t)E * nb);
+  b.ddr = p.take<float>((size_t)E);
   b.dvec = p.take<float>((size_t)E * 3);
   b.dw = p.take<float>((size_t)E * maxwn);
   for (int k = 0; k < 2; ++k) b.x[k] = p.take<float>((size_t)NA * maxx);
@@ -273,9 +278,10 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
   b.s = p.take<float>((size_t)N);
   b.g_s = p.take<float>((size_t)N);
   b.virial_atom = p.take<float>((size_t)NA * 6);
-  b.w.clear(); b.xs.clear(); b.gin.clear();
+  b.w.clear(); b.xs.clear(); b.gin.clear(); b.rad.clear();
   for (const Layer& L : m->layers) {
-    b.w.push_back(p.take<float>((size_t)E * L.conv.wn));
+    b.w.push_back(p.take<float>(L.fused ? 0 : (size_t)E * L.conv.wn));
+    b.rad.push_back(reinterpret_cast<float*>(p.take<char>(L.fused ? fused_radial_bytes(E) : 0)));
     b.xs.push_back(p.take<float>((size_t)NA * L.conv.xdim));
     b.gin.push_back(p.take<float>((size_t)N * L.sc.out_dim));
   }
@@ -358,10 +364,16 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     // later layers: the owners' rows are fetched through the halo hook
     OP(CAT_NODE, irreps_linear(L.si1, t == 0 ? NA : N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
     if (t > 0) HALO(B200_HALO_FWD_X, t, b.xs[t], L.conv.xdim);
-    OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
-                       P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
-                       b.w[t], st));
-    OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
+    const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
+    const float* W1 = P(m, s + "_convolution.weight_nn.layer1.weight");
+    const float* W2 = P(m, s + "_convolution.weight_nn.layer2.weight");
+    if (L.fused) {
+      OP(CAT_MLP_FWD, fused_radial(c.edge, L.mlp, E, edge_vec, coeffs, W0, W1, b.rad[t], st));
+      OP(CAT_CONV_FWD, fused_conv_fwd(L.conv, N, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, denom[t], b.conv_out, st));
+    } else {
+      OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, W0, W1, W2, b.w[t], st));
+      OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
+    }
     OP(CAT_NODE, irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
     OP(CAT_NODE, gate_fwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], xn, st));
     std::swap(x, xn);
@@ -380,29 +392,39 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   float* g = b.g_x[0];
   float* gp = b.g_x[1];
   OP(CAT_NODE, irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
-  bool first_edge = true;
+  bool any_fused = false, any_plain = false;
   for (int t = nl - 1; t >= 0; --t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
     OP(CAT_NODE, gate_bwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], g, b.g_gin, st));
     OP(CAT_NODE, irreps_linear(L.si2, N, b.g_gin, P(m, s + "_self_interaction_2.linear.weight"), b.g_conv, 1, 0, st));
-    OP(CAT_CONV_BWD_EDGE, conv_bwd_edge(L.conv, N, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw, b.dY,
-                      first_edge ? 0 : 1, st));
-    OP(CAT_MLP_BWD, radial_mlp_bwd(L.mlp, E, b.emb, P(m, s + "_convolution.weight_nn.layer0.weight"),
-                       P(m, s + "_convolution.weight_nn.layer1.weight"), P(m, s + "_convolution.weight_nn.layer2.weight"),
-                       b.dw, b.demb, first_edge ? 0 : 1, st));
-    first_edge = false;
+    const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
+    const float* W1 = P(m, s + "_convolution.weight_nn.layer1.weight");
+    const float* W2 = P(m, s + "_convolution.weight_nn.layer2.weight");
+    // features entering layer t > 0 depend on the positions through the earlier layers: d x is needed there
+    float* dxs = t > 0 ? b.conv_out : nullptr;
+    if (L.fused) {
+      OP(CAT_CONV_BWD_EDGE, fused_conv_bwd(L.conv, NA, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, b.g_conv, denom[t], dxs, b.dY,
+                                           b.ddr, any_fused ? 1 : 0, st));
+      any_fused = true;
+    } else {
+      OP(CAT_CONV_BWD_EDGE, conv_bwd_edge(L.conv, N, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw, b.dY,
+                                          (any_fused || any_plain) ? 1 : 0, st));
+      OP(CAT_MLP_BWD, radial_mlp_bwd(L.mlp, E, b.emb, W0, W1, W2, b.dw, b.demb, any_plain ? 1 : 0, st));
+      any_plain = true;
+    }
     if (t > 0) {
-      // features entering layer t depend on the positions through layers < t
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
       OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
-      OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
+      if (!L.fused)
+        OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
       OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
       std::swap(g, gp);
     }
   }
-  OP(CAT_EDGE, edge_embed_bwd(c.edge, E, edge_vec, coeffs, b.dY, b.demb, b.dvec, st));
+  OP(CAT_EDGE, edge_embed_bwd_full(c.edge, E, edge_vec, coeffs, b.dY, any_plain ? b.demb : nullptr,
+                                   any_fused ? b.ddr : nullptr, b.dvec, st));
   OP(CAT_FORCE, force_virial(NA, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
   HALO(B200_HALO_FORCE, -1, force, 3);
   OP(CAT_NODE, colsum(NA, 6, b.virial_atom, virial, st));   // per-source rows (force_output.py:186-213): ghosts included

@@ -37,7 +37,7 @@ constexpr int F_BPART = (FH / 4) * F_BCH;   // 16 KB: one part of a B tile
 constexpr int F_TILE_FLOATS = 4 * F_BPART / 4;   // h2 hi | h2 lo | h2' hi | h2' lo
 constexpr int F_MAXSLAB = 12;
 constexpr int F_EPI_WARPS = 16;
-constexpr int F_THREADS = (F_EPI_WARPS + 1) * 32;
+constexpr int F_THREADS = F_EPI_WARPS * 32;
 
 struct FusedPlan {
   int nslab;
@@ -284,19 +284,53 @@ __device__ __forceinline__ int conv_xoff(const ConvDesc& d, int l1) { return l1 
   }
 
 // ================================================ forward ======================================================
+// whole warp: 4 consecutive fp32 columns of this warp's 32 TMEM lanes
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
+  uint32_t r[4];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// the harmonics a path needs, from the padded shared-memory record (compile-time indices only)
+template <int L2> __device__ __forceinline__ void load_Y(const float* rec, float* Y) {
+  if constexpr (L2 == 1) {
+    const float4 v = *reinterpret_cast<const float4*>(rec);
+    Y[1] = v.y; Y[2] = v.z; Y[3] = v.w;
+  } else if constexpr (L2 == 2) {
+    const float4 v = *reinterpret_cast<const float4*>(rec + 4);
+    Y[4] = v.x; Y[5] = v.y; Y[6] = v.z; Y[7] = v.w;
+    Y[8] = rec[8];
+  }
+}
+
+// bit j: edge e_lo + j starts a new destination row within this warp's range (bit 0 always set)
+__device__ __forceinline__ unsigned break_mask(const int* dst, int e_lo, int e_hi) {
+  const int lane = threadIdx.x & 31, e = e_lo + lane;
+  const bool b = e < e_hi && (lane == 0 || dst[e] != dst[e - 1]);
+  return __ballot_sync(0xffffffffu, b);
+}
+
 struct FusedFwdSmem {
   uint8_t A[2][2 * F_APART];     // two stages of W2^T slabs (hi | lo)
   uint8_t B[2][2 * F_BPART];     // two 64-edge operand tiles (h2 hi | h2 lo)
   float Y[2 * FT][12];
-  int src[2 * FT], dst[2 * FT];
+  const float* xrow[2 * FT];     // x + src * xdim
+  int dst[2 * FT];
   uint64_t full_a[2], full_b, mma_done[2], tmem_free[2];
   uint32_t tmem_base;
 };
 
 template <int PID>
-__device__ __forceinline__ void fwd_unit(const ConvDesc& d, const FusedFwdSmem& s, uint32_t taddr, int e_lo, int ne, int ubase,
-                                         const float* __restrict__ x, float inv_denom, float* __restrict__ out) {
+__device__ __forceinline__ void fwd_unit(const ConvDesc& d, const FusedFwdSmem& s, uint32_t taddr, int e_lo, int e_hi,
+                                         unsigned brk, int ubase, float inv_denom, float* __restrict__ out) {
   using C = CgD<PID>;
+  if (e_lo >= e_hi) return;
   const int lane = threadIdx.x & 31;
   const int u = ubase + lane;
   const int xo = conv_xoff(d, C::L1) + u * C::D1;
@@ -304,38 +338,50 @@ __device__ __forceinline__ void fwd_unit(const ConvDesc& d, const FusedFwdSmem& 
   float acc[C::D3];
 #pragma unroll
   for (int c = 0; c < C::D3; ++c) acc[c] = 0.f;
-  int cur = e_lo < ne ? s.dst[e_lo] : -1;
-  for (int jb = 0; jb < 4; ++jb) {
-    const int eb = e_lo + 8 * jb;
-    if (eb >= ne) break;
-    float w8[8];
-    tmem_ld8(taddr + 8 * jb, w8);
-    const int nj = min(8, ne - eb);
-#pragma unroll 1
-    for (int jj = 0; jj < nj; ++jj) {
-      const int e = eb + jj;
-      const float w = w8[0];
+  int cur = -1;
+  float xq[4][C::D1];   // gathers run 4 edges ahead of the arithmetic: slot jj is refilled as soon as it is consumed
+  auto load_x = [&](float (&xq)[4][C::D1], int eb) {
 #pragma unroll
-      for (int i = 0; i < 7; ++i) w8[i] = w8[i + 1];
-      const int dd = s.dst[e];
-      if (dd != cur) {
-        float* o = out + (size_t)cur * d.odim + oo;
+    for (int jj = 0; jj < 4; ++jj) {
+      const float* xr = s.xrow[min(eb + jj, e_hi - 1)] + xo;
 #pragma unroll
-        for (int c = 0; c < C::D3; ++c) { atomicAdd(o + c, acc[c] * inv_denom); acc[c] = 0.f; }
-        cur = dd;
-      }
-      const float* xr = x + (size_t)s.src[e] * d.xdim + xo;
-      float X[C::D1];
-#pragma unroll
-      for (int a = 0; a < C::D1; ++a) X[a] = w * __ldg(xr + a);
-      C::fwd(X, s.Y[e], acc);
+      for (int a = 0; a < C::D1; ++a) xq[jj][a] = __ldg(xr + a);
     }
-  }
-  if (cur >= 0) {
+  };
+  auto flush = [&]() {
     float* o = out + (size_t)cur * d.odim + oo;
 #pragma unroll
-    for (int c = 0; c < C::D3; ++c) atomicAdd(o + c, acc[c] * inv_denom);
-  }
+    for (int c = 0; c < C::D3; ++c) { atomicAdd(o + c, acc[c] * inv_denom); acc[c] = 0.f; }
+  };
+  auto compute = [&](int eb) {
+    float w4[4];
+    tmem_ld4(taddr + (uint32_t)(eb - e_lo), w4);
+    const unsigned bm = brk >> (eb - e_lo);
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const int e = eb + jj;
+      if (e < e_hi) {
+        if ((bm >> jj) & 1u) {
+          if (cur >= 0) flush();
+          cur = s.dst[e];
+        }
+        float Yl[12], X[C::D1];
+        load_Y<C::L2>(s.Y[e], Yl);
+#pragma unroll
+        for (int a = 0; a < C::D1; ++a) X[a] = w4[jj] * xq[jj][a];
+        {
+          const float* xr = s.xrow[min(e + 4, e_hi - 1)] + xo;
+#pragma unroll
+          for (int a = 0; a < C::D1; ++a) xq[jj][a] = __ldg(xr + a);
+        }
+        C::fwd(X, Yl, acc);
+      }
+    }
+  };
+  load_x(xq, e_lo);
+#pragma unroll 1
+  for (int eb = e_lo; eb < e_hi; eb += 4) compute(eb);
+  flush();
 }
 
 __global__ void __launch_bounds__(F_THREADS, 1)
@@ -351,7 +397,7 @@ fused_conv_fwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
   const int NS = pl.nslab;
   constexpr uint32_t SLAB = 2 * F_APART;
 
-  if (warp == F_EPI_WARPS) {
+  if (warp == 0) {
     tmem_alloc(&s.tmem_base, 256);
     if (lane == 0) {
       mbar_init(&s.full_a[0], 1); mbar_init(&s.full_a[1], 1); mbar_init(&s.full_b, 1);
@@ -361,7 +407,7 @@ fused_conv_fwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
     }
   }
   for (int i = threadIdx.x; i < ne; i += F_THREADS) {
-    s.src[i] = srcv[e0 + i];
+    s.xrow[i] = x + (size_t)srcv[e0 + i] * d.xdim;
     s.dst[i] = dstv[e0 + i];
   }
   for (int i = threadIdx.x; i < ne * 9; i += F_THREADS) s.Y[i / 9][i % 9] = Yg[e0 * 9 + i];
@@ -370,50 +416,57 @@ fused_conv_fwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
   tc_fence_after();
   const uint32_t tmem = s.tmem_base;
 
-  if (warp == F_EPI_WARPS) {
-    if (lane == 0) {
-      mbar_expect_tx(&s.full_b, (uint32_t)nsub * 2 * F_BPART);
-      for (int j = 0; j < nsub; ++j)
-        bulk_copy_g2s(s.B[j], tiles + (size_t)(2 * blockIdx.x + j) * F_TILE_FLOATS, 2 * F_BPART, &s.full_b);
-      for (int k = 0; k < 2 && k < NS; ++k) {
-        mbar_expect_tx(&s.full_a[k], SLAB);
-        bulk_copy_g2s(s.A[k], pack + (size_t)k * (SLAB / 4), SLAB, &s.full_a[k]);
-      }
-      mbar_wait(&s.full_b, 0);
-      for (int sl = 0; sl < NS; ++sl) {
-        const int st = sl & 1;
-        mbar_wait(&s.full_a[st], (sl >> 1) & 1);
-        if (sl >= 2) mbar_wait(&s.tmem_free[st], ((sl - 2) >> 1) & 1);
-        tc_fence_after();
-        for (int j = 0; j < nsub; ++j) issue_slab_mma(tmem + (uint32_t)(st * 128 + j * FT), s.A[st], s.B[j]);
-        mma_commit(&s.mma_done[st]);
-        if (sl + 2 < NS) {
-          mbar_wait(&s.mma_done[st], (sl >> 1) & 1);   // the slab's MMAs have consumed A[st]
+  // slab sl + 1 is launched (operand refill + MMA issue) by warp (sl + 1) % 16 at the start of its iteration sl
+  auto launch_slab = [&](int sl) {   // one thread; sl < NS
+    const int st = sl & 1;
+    mbar_wait(&s.full_a[st], (sl >> 1) & 1);
+    if (sl >= 2) mbar_wait(&s.tmem_free[st], ((sl - 2) >> 1) & 1);
+    tc_fence_after();
+    for (int j = 0; j < nsub; ++j) issue_slab_mma(tmem + (uint32_t)(st * 128 + j * FT), s.A[st], s.B[j]);
+    mma_commit(&s.mma_done[st]);
+  };
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(&s.full_b, (uint32_t)nsub * 2 * F_BPART);
+    for (int j = 0; j < nsub; ++j)
+      bulk_copy_g2s(s.B[j], tiles + (size_t)(2 * blockIdx.x + j) * F_TILE_FLOATS, 2 * F_BPART, &s.full_b);
+    for (int k = 0; k < 2 && k < NS; ++k) {
+      mbar_expect_tx(&s.full_a[k], SLAB);
+      bulk_copy_g2s(s.A[k], pack + (size_t)k * (SLAB / 4), SLAB, &s.full_a[k]);
+    }
+    mbar_wait(&s.full_b, 0);
+    launch_slab(0);
+  }
+  __syncwarp();
+  const int q = warp & 3, cg = warp >> 2;
+  const int e_lo = 32 * cg, e_hi = min(32 * cg + 32, ne);
+  const unsigned brk = break_mask(s.dst, e_lo, e_hi);
+  for (int sl = 0; sl < NS; ++sl) {
+    const int st = sl & 1;
+    mbar_wait(&s.mma_done[st], (sl >> 1) & 1);
+    if (warp == ((sl + 1) & (F_EPI_WARPS - 1)) && sl + 1 < NS) {
+      if (lane == 0) {
+        if (sl + 2 < NS) {   // MMA(sl) has consumed A[st]: refill it with slab sl + 2
           mbar_expect_tx(&s.full_a[st], SLAB);
           bulk_copy_g2s(s.A[st], pack + (size_t)(sl + 2) * (SLAB / 4), SLAB, &s.full_a[st]);
         }
+        launch_slab(sl + 1);
       }
-    }
-  } else {
-    const int q = warp & 3, cg = warp >> 2;
-    for (int sl = 0; sl < NS; ++sl) {
-      const int st = sl & 1;
-      mbar_wait(&s.mma_done[st], (sl >> 1) & 1);
-      tc_fence_after();
-      const int p = pl.path[sl][q];
-      const int ub = pl.ubase[sl][q];
-      const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(st * 128 + 32 * cg);
-#define F_CALL(PID) fwd_unit<PID>(d, s, taddr, 32 * cg, ne, ub, x, inv_denom, out)
-      F_DISPATCH_PATH(p, F_CALL)
-#undef F_CALL
-      tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&s.tmem_free[st]);
     }
+    tc_fence_after();
+    const int p = pl.path[sl][q];
+    const int ub = pl.ubase[sl][q];
+    const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(st * 128 + e_lo);
+#define F_CALL(PID) fwd_unit<PID>(d, s, taddr, e_lo, e_hi, brk, ub, inv_denom, out)
+    F_DISPATCH_PATH(p, F_CALL)
+#undef F_CALL
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s.tmem_free[st]);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == F_EPI_WARPS) tmem_dealloc(tmem, 256);
+  if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
 // ================================================ backward =====================================================
@@ -422,13 +475,14 @@ struct FusedBwdSmem {
   uint8_t B[4 * F_BPART];        // one 64-edge operand tile: h2 hi | h2 lo | h2' hi | h2' lo
   float Y[FT][12];
   float acc[FT][12];             // per edge: [0] d r, [1..8] d Y
+  const float* xrow[FT + 1];     // x + src * xdim; [FT] = x
   int src[FT], dst[FT];
   uint64_t full_a, full_b, mma_done[2], tmem_free[2];
   uint32_t tmem_base;
   float stage[1];                // [FT][stage_width] thread-private d x staging (dynamic tail)
 };
 
-// sum over the warp of N values per lane; lane L ends with component slot(L) (see callers), others hold garbage
+// sums over the warp; the lane named in the comment ends with the component, the others hold garbage
 __device__ __forceinline__ float warp_sum1(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -474,77 +528,93 @@ __device__ __forceinline__ float warp_sum8(float* v, int lane) {
 }
 
 template <int PID>
-__device__ __forceinline__ void bwd_unit(const ConvDesc& d, FusedBwdSmem& s, int stage_width, uint32_t taddr, int e_lo, int ne,
-                                         int ubase, const float* __restrict__ x, const float* __restrict__ gout,
-                                         float inv_denom, float* __restrict__ dxo) {
+__device__ __forceinline__ void bwd_unit(const ConvDesc& d, FusedBwdSmem& s, int stage_width, uint32_t taddr, int e_lo, int e_hi,
+                                         unsigned brk, int ubase, const float* __restrict__ gout, float inv_denom,
+                                         float* __restrict__ dxo) {
   using C = CgD<PID>;
+  if (e_lo >= e_hi) return;
   const int lane = threadIdx.x & 31;
   const int u = ubase + lane;
   const int xo = conv_xoff(d, C::L1) + u * C::D1;
   const size_t oo = (size_t)d.ooff[PID] + (size_t)u * C::D3;
   const int so = (C::L1 == 1 ? 0 : 3 * d.m1) + u * C::D1;   // staging column (roles 1, 2)
   float g[C::D3];
-  int cur = -1;
-  for (int jb = 0; jb < 2; ++jb) {
-    const int eb = e_lo + 8 * jb;
-    if (eb >= ne) break;
-    float w8[8], wp8[8];
-    tmem_ld8(taddr + 8 * jb, w8);
-    tmem_ld8(taddr + FT + 8 * jb, wp8);
-    const int nj = min(8, ne - eb);
-#pragma unroll 1
-    for (int jj = 0; jj < nj; ++jj) {
+  float xq[4][C::D1];
+  auto load_x = [&](float (&xq)[4][C::D1], int eb) {
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const float* xr = s.xrow[min(eb + jj, e_hi - 1)] + xo;
+#pragma unroll
+      for (int a = 0; a < C::D1; ++a) xq[jj][a] = __ldg(xr + a);
+    }
+  };
+  auto compute = [&](int eb) {
+    float w4[4], wp4[4];
+    tmem_ld4(taddr + (uint32_t)(eb - e_lo), w4);
+    tmem_ld4(taddr + (uint32_t)(FT + eb - e_lo), wp4);
+    const unsigned bm = brk >> (eb - e_lo);
+    float r0[4];   // d r of the 4 edges (reduced together when the path has no harmonics to differentiate)
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
       const int e = eb + jj;
-      const float w = w8[0], wp = wp8[0];
+      r0[jj] = 0.f;
+      if (e < e_hi) {
+        if ((bm >> jj) & 1u) {
+          const float* gr = gout + (size_t)s.dst[e] * d.odim + oo;
 #pragma unroll
-      for (int i = 0; i < 7; ++i) { w8[i] = w8[i + 1]; wp8[i] = wp8[i + 1]; }
-      const int dd = s.dst[e];
-      if (dd != cur) {
-        const float* gr = gout + (size_t)dd * d.odim + oo;
+          for (int c = 0; c < C::D3; ++c) g[c] = __ldg(gr + c) * inv_denom;
+        }
+        const float w = w4[jj], wp = wp4[jj];
+        float Yl[12], T[C::D2];
+        load_Y<C::L2>(s.Y[e], Yl);
+        C::tvec(xq[jj], g, T);
+        {
+          const float* xr = s.xrow[min(e + 4, e_hi - 1)] + xo;
 #pragma unroll
-        for (int c = 0; c < C::D3; ++c) g[c] = __ldg(gr + c) * inv_denom;
-        cur = dd;
-      }
-      const int sj = s.src[e];
-      const float* xr = x + (size_t)sj * d.xdim + xo;
-      float xv[C::D1];
+          for (int a = 0; a < C::D1; ++a) xq[jj][a] = __ldg(xr + a);
+        }
+        float dwv = 0.f;
+        if constexpr (C::L2 == 0) {
+          dwv = T[0];
+        } else {
 #pragma unroll
-      for (int a = 0; a < C::D1; ++a) xv[a] = __ldg(xr + a);
-      const float* Y = s.Y[e];
-      float T[C::D2];
-      C::tvec(xv, g, T);
-      float dwv = 0.f;
-      if constexpr (C::L2 == 0) {
-        dwv = T[0];
-      } else {
+          for (int b = 0; b < C::D2; ++b) dwv = fmaf(Yl[C::YO + b], T[b], dwv);
+        }
+        if (dxo) {   // not needed for the first layer: its input depends on the species only
+          float dx[C::D1];
+          C::dxv(Yl, g, dx);
+          if constexpr (C::L1 == 0) {
+            atomicAdd(dxo + (s.xrow[e] - s.xrow[FT]) + xo, w * dx[0]);
+          } else {
+            float* sp = s.stage + e * stage_width + so;
 #pragma unroll
-        for (int b = 0; b < C::D2; ++b) dwv = fmaf(Y[C::YO + b], T[b], dwv);
-      }
-      float dx[C::D1];
-      C::dxv(Y, g, dx);
-      if constexpr (C::L1 == 0) {
-        atomicAdd(dxo + (size_t)sj * d.xdim + xo, w * dx[0]);
-      } else {
-        float* sp = s.stage + e * stage_width + so;
-#pragma unroll
-        for (int a = 0; a < C::D1; ++a) sp[a] = fmaf(w, dx[a], sp[a]);
-      }
-      // warp reduction over the 32 channels of the unit: d r and d Y of this edge
-      if constexpr (C::L2 == 0) {
-        const float r = warp_sum1(dwv * wp);
-        if (lane == 0) atomicAdd(&s.acc[e][0], r);
-      } else if constexpr (C::L2 == 1) {
-        float v[4] = {dwv * wp, w * T[0], w * T[1], w * T[2]};
-        const float r = warp_sum4(v, lane);
-        if ((lane & 7) == 0) atomicAdd(&s.acc[e][((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)], r);
-      } else {
-        float v[8] = {dwv * wp, w * T[0], w * T[1], w * T[2], w * T[3], w * T[4], 0.f, 0.f};
-        const float r = warp_sum8(v, lane);
-        const int m = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-        if ((lane & 3) == 0 && m < 6) atomicAdd(&s.acc[e][m == 0 ? 0 : 3 + m], r);
+            for (int a = 0; a < C::D1; ++a) sp[a] = fmaf(w, dx[a], sp[a]);
+          }
+        }
+        // reduction over the 32 channels of the unit: d r and d Y of this edge
+        if constexpr (C::L2 == 0) {
+          r0[jj] = dwv * wp;
+        } else if constexpr (C::L2 == 1) {
+          float v[4] = {dwv * wp, w * T[0], w * T[1], w * T[2]};
+          const float r = warp_sum4(v, lane);
+          if ((lane & 7) == 0) atomicAdd(&s.acc[e][((lane >> 4) & 1) * 2 + ((lane >> 3) & 1)], r);
+        } else {
+          float v[8] = {dwv * wp, w * T[0], w * T[1], w * T[2], w * T[3], w * T[4], 0.f, 0.f};
+          const float r = warp_sum8(v, lane);
+          const int m = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+          if ((lane & 3) == 0 && m < 6) atomicAdd(&s.acc[e][m == 0 ? 0 : 3 + m], r);
+        }
       }
     }
-  }
+    if constexpr (C::L2 == 0) {
+      const float r = warp_sum4(r0, lane);
+      const int jj = ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1);
+      if ((lane & 7) == 0 && eb + jj < e_hi) atomicAdd(&s.acc[eb + jj][0], r);
+    }
+  };
+  load_x(xq, e_lo);
+#pragma unroll 1
+  for (int eb = e_lo; eb < e_hi; eb += 4) compute(eb);
 }
 
 __global__ void __launch_bounds__(F_THREADS, 1)
@@ -560,7 +630,7 @@ fused_conv_bwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
   const int NS = pl.nslab, SW = pl.stage_width;
   constexpr uint32_t SLAB = 2 * F_APART;
 
-  if (warp == F_EPI_WARPS) {
+  if (warp == 0) {
     tmem_alloc(&s.tmem_base, 256);
     if (lane == 0) {
       mbar_init(&s.full_a, 1); mbar_init(&s.full_b, 1);
@@ -570,9 +640,12 @@ fused_conv_bwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
     }
   }
   for (int i = threadIdx.x; i < ne; i += F_THREADS) {
-    s.src[i] = srcv[e0 + i];
+    const int sj = srcv[e0 + i];
+    s.src[i] = sj;
+    s.xrow[i] = x + (size_t)sj * d.xdim;
     s.dst[i] = dstv[e0 + i];
   }
+  if (threadIdx.x == 0) s.xrow[FT] = x;   // base, to turn a row pointer back into an offset
   for (int i = threadIdx.x; i < ne * 9; i += F_THREADS) s.Y[i / 9][i % 9] = Yg[e0 * 9 + i];
   for (int i = threadIdx.x; i < FT * 12; i += F_THREADS) (&s.acc[0][0])[i] = 0.f;
   for (int i = threadIdx.x; i < FT * SW; i += F_THREADS) s.stage[i] = 0.f;
@@ -581,48 +654,52 @@ fused_conv_bwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
   tc_fence_after();
   const uint32_t tmem = s.tmem_base;
 
-  if (warp == F_EPI_WARPS) {
-    if (lane == 0) {
-      mbar_expect_tx(&s.full_b, 4 * F_BPART);
-      bulk_copy_g2s(s.B, tiles + (size_t)blockIdx.x * F_TILE_FLOATS, 4 * F_BPART, &s.full_b);
-      mbar_expect_tx(&s.full_a, SLAB);
-      bulk_copy_g2s(s.A, pack, SLAB, &s.full_a);
-      mbar_wait(&s.full_b, 0);
-      for (int sl = 0; sl < NS; ++sl) {
-        const int st = sl & 1;
-        mbar_wait(&s.full_a, sl & 1);
-        if (sl >= 2) mbar_wait(&s.tmem_free[st], ((sl - 2) >> 1) & 1);
-        tc_fence_after();
-        issue_slab_mma(tmem + (uint32_t)(st * 128), s.A, s.B);                      // w  = W2^T . h2
-        issue_slab_mma(tmem + (uint32_t)(st * 128 + FT), s.A, s.B + 2 * F_BPART);   // w' = W2^T . h2'
-        mma_commit(&s.mma_done[st]);
-        if (sl + 1 < NS) {
-          mbar_wait(&s.mma_done[st], (sl >> 1) & 1);
-          mbar_expect_tx(&s.full_a, SLAB);
-          bulk_copy_g2s(s.A, pack + (size_t)(sl + 1) * (SLAB / 4), SLAB, &s.full_a);
-        }
+  auto launch_slab = [&](int sl) {   // one thread: A(sl) must have been requested
+    const int st = sl & 1;
+    mbar_wait(&s.full_a, sl & 1);
+    if (sl >= 2) mbar_wait(&s.tmem_free[st], ((sl - 2) >> 1) & 1);
+    tc_fence_after();
+    issue_slab_mma(tmem + (uint32_t)(st * 128), s.A, s.B);                      // w  = W2^T . h2
+    issue_slab_mma(tmem + (uint32_t)(st * 128 + FT), s.A, s.B + 2 * F_BPART);   // w' = W2^T . h2'
+    mma_commit(&s.mma_done[st]);
+  };
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(&s.full_b, 4 * F_BPART);
+    bulk_copy_g2s(s.B, tiles + (size_t)blockIdx.x * F_TILE_FLOATS, 4 * F_BPART, &s.full_b);
+    mbar_expect_tx(&s.full_a, SLAB);
+    bulk_copy_g2s(s.A, pack, SLAB, &s.full_a);
+    mbar_wait(&s.full_b, 0);
+    launch_slab(0);
+  }
+  __syncwarp();
+  const int q = warp & 3, cg = warp >> 2;
+  const int e_lo = 16 * cg, e_hi = min(16 * cg + 16, ne);
+  const unsigned brk = break_mask(s.dst, e_lo, e_hi);
+  for (int sl = 0; sl < NS; ++sl) {
+    const int st = sl & 1;
+    mbar_wait(&s.mma_done[st], (sl >> 1) & 1);
+    if (warp == ((sl + 1) & (F_EPI_WARPS - 1)) && sl + 1 < NS) {
+      if (lane == 0) {   // MMA(sl) has consumed the single A stage: stream slab sl + 1 and issue it
+        mbar_expect_tx(&s.full_a, SLAB);
+        bulk_copy_g2s(s.A, pack + (size_t)(sl + 1) * (SLAB / 4), SLAB, &s.full_a);
+        launch_slab(sl + 1);
       }
-    }
-  } else {
-    const int q = warp & 3, cg = warp >> 2;
-    for (int sl = 0; sl < NS; ++sl) {
-      const int st = sl & 1;
-      mbar_wait(&s.mma_done[st], (sl >> 1) & 1);
-      tc_fence_after();
-      const int p = pl.path[sl][q];
-      const int ub = pl.ubase[sl][q];
-      const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(st * 128 + 16 * cg);
-#define F_CALL(PID) bwd_unit<PID>(d, s, SW, taddr, 16 * cg, ne, ub, x, gout, inv_denom, dxo)
-      F_DISPATCH_PATH(p, F_CALL)
-#undef F_CALL
-      tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&s.tmem_free[st]);
     }
+    tc_fence_after();
+    const int p = pl.path[sl][q];
+    const int ub = pl.ubase[sl][q];
+    const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(st * 128 + e_lo);
+#define F_CALL(PID) bwd_unit<PID>(d, s, SW, taddr, e_lo, e_hi, brk, ub, gout, inv_denom, dxo)
+    F_DISPATCH_PATH(p, F_CALL)
+#undef F_CALL
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s.tmem_free[st]);
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == F_EPI_WARPS) tmem_dealloc(tmem, 256);
+  if (warp == 0) tmem_dealloc(tmem, 256);
   // per-edge results: d r, d Y (each edge belongs to exactly one CTA: plain read-modify-write)
   for (int i = threadIdx.x; i < ne * 9; i += F_THREADS) {
     const int e = i / 9, b = i % 9;
@@ -635,8 +712,8 @@ fused_conv_bwd_kernel(FusedPlan pl, ConvDesc d, long long E, const int* __restri
     }
   }
   // staged d x rows (roles 1 and 2): one coalesced RED row per edge
-  if (SW > 0) {
-    for (int e = warp; e < ne; e += F_EPI_WARPS + 1) {
+  if (SW > 0 && dxo) {
+    for (int e = warp; e < ne; e += F_EPI_WARPS) {
       float* row = dxo + (size_t)s.src[e] * d.xdim + d.m0;
       for (int c = lane; c < SW; c += 32) atomicAdd(row + c, s.stage[e * SW + c]);
     }
@@ -691,7 +768,7 @@ int fused_conv_bwd(const ConvDesc& d, int n_src, long long E, const int* dst, co
                    int accumulate, cudaStream_t st) {
   FusedPlan pl;
   B200_REQUIRE(build_plan(d, pl), "fused_conv_bwd: unsupported irreps (multiplicities must be multiples of 32, <= 128/64/32)");
-  cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)n_src * d.xdim, st);
+  if (dx) cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)n_src * d.xdim, st);
   if (E == 0) return B200_OK;
   float* pack;
   if (int rc = make_pack(pl, d, W2, st, &pack)) return rc;

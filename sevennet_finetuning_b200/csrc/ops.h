@@ -10,6 +10,8 @@ int edge_embed_fwd(const EdgeParams& p, long long E, const float* vec, const flo
                    float* emb, cudaStream_t st);
 int edge_embed_bwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
                    const float* demb, float* dvec, cudaStream_t st);
+int edge_embed_bwd_full(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
+                        const float* demb, const float* dr, float* dvec, cudaStream_t st);
 int edge_embed_bwd_r(const EdgeParams& p, long long E, const float* vec, const float* dY, const float* dr, float* dvec,
                      cudaStream_t st);
 int force_virial(int n_atoms, const int* rowptr, const int* rrowptr, const int* eid_by_src, const float* vec,
