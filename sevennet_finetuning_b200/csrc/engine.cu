@@ -176,7 +176,7 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.sc = make_linear(L.in, L.gin);
     L.si1 = make_linear(L.in, L.in);
     L.si2 = make_linear(L.msg, L.gin);
-    L.fused = fused_supported(L.conv, L.mlp) && !getenv("B200_NO_FUSED");
+    L.fused = fused_supported(L.conv, L.mlp) && getenv("B200_FUSED") && atoi(getenv("B200_FUSED")) != 0;   // opt-in
     m->layers.push_back(L);
     const std::string s = std::to_string(t);
     m->expected[s + "_self_connection_intro.linear.weight"] = lin_numel(L.sc);
