@@ -43,6 +43,9 @@ int fused_conv_bwd(const ConvDesc& d, int n_src, long long E, const int* dst, co
 
 int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
                   cudaStream_t st);
+bool irreps_linear_tc_supported(const LinDesc& d, int transpose);
+int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
+                     cudaStream_t st);
 int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const float* dy, float* dW, int accumulate,
                         cudaStream_t st);
 
