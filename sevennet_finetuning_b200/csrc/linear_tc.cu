@@ -22,6 +22,7 @@ constexpr int L_APART = (LK / 4) * L_ACH;   // 8 KB (hi or lo)
 constexpr int L_MAXN = 64;             // output columns per pass
 constexpr int L_BPART = (LK / 4) * L_MAXN * 16;   // 4 KB (hi or lo)
 constexpr int L_T = 256;
+constexpr int L_GPT = (128 * LK + L_T - 1) / L_T;   // gather slots per thread
 
 struct LinTcBlock {
   int D, K, N, Npad;          // 2l+1, contraction length, real / padded (multiple of 16) output columns of this pass
@@ -115,6 +116,28 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
     tc_fence_before();
   };
 
+  // per-thread gather slots (fixed over the chunks): element it = tid + j * L_T of the [TN][16][D] chunk
+  const int span = LK * D;
+  int gnl[L_GPT];            // node of the slot, -1: unused
+  uint32_t goff[L_GPT];      // byte offset of the element in the operand tile
+  const float* gptr[L_GPT];  // its address in chunk 0
+  int gk[L_GPT];
+#pragma unroll
+  for (int j = 0; j < L_GPT; ++j) {
+    const int it = threadIdx.x + j * L_T;
+    const int nl = it / span, km = it % span, k = km / D, m = km % D;
+    gnl[j] = it < TN * span ? nl : -1;
+    gk[j] = k;
+    goff[j] = (uint32_t)(k >> 2) * L_ACH + (uint32_t)(nl * D + m) * 16 + (uint32_t)(k & 3) * 4;
+    gptr[j] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + km;
+  }
+  auto gload = [&](int c, int j) -> float {
+    return (gnl[j] >= 0 && gnl[j] < nn && c * LK + gk[j] < b.K) ? __ldg(gptr[j] + (size_t)c * span) : 0.f;
+  };
+  float gv[L_GPT];
+#pragma unroll
+  for (int j = 0; j < L_GPT; ++j) gv[j] = gload(0, j);
+
   for (int c = 0; c < b.nchunk; ++c) {
     const int st = c & 1;
     if (c >= 2) {   // the MMAs of chunk c-2 have consumed the operand stage and filled its two accumulators
@@ -128,17 +151,18 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
       bulk_copy_g2s(s.B[st], src, bpart, &s.full_b[st]);
       bulk_copy_g2s(s.B[st] + L_BPART, src + bpart / 4, bpart, &s.full_b[st]);
     }
-    // gather the A chunk: element (node nl, k, m) -> row nl*D+m, column k; lanes run along the contiguous (k, m) index
-    const int span = LK * D;
-    for (int it = threadIdx.x; it < TN * span; it += L_T) {
-      const int nl = it / span, km = it % span, k = km / D, m = km % D;
-      float v = 0.f;
-      if (nl < nn && c * LK + k < b.K) v = __ldg(x + (size_t)(n0 + nl) * pl.ldx + b.xoff + (size_t)c * span + km);
-      float hi, lo;
-      split_tf32(v, hi, lo);
-      const uint32_t off = (uint32_t)(k >> 2) * L_ACH + (uint32_t)(nl * D + m) * 16 + (uint32_t)(k & 3) * 4;
-      *reinterpret_cast<float*>(s.A[st] + off) = hi;
-      *reinterpret_cast<float*>(s.A[st] + L_APART + off) = lo;
+    // gather the A chunk: element (node nl, k, m) -> row nl*D+m, column k; lanes run along the contiguous (k, m) index.
+    // The values of the NEXT chunk are requested before this chunk's are split and stored (one round trip hidden).
+#pragma unroll
+    for (int j = 0; j < L_GPT; ++j) {
+      const float v = gv[j];
+      if (c + 1 < b.nchunk) gv[j] = gload(c + 1, j);
+      if (gnl[j] >= 0) {
+        float hi, lo;
+        split_tf32(v, hi, lo);
+        *reinterpret_cast<float*>(s.A[st] + goff[j]) = hi;
+        *reinterpret_cast<float*>(s.A[st] + L_APART + goff[j]) = lo;
+      }
     }
     if (TN * D < 128) {   // rows of the tile that belong to no node (128 is not a multiple of 2l+1)
       for (int it = threadIdx.x; it < (128 - TN * D) * LK; it += L_T) {
