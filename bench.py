@@ -185,6 +185,8 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
+        if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
+            os.environ['NCCL_DEBUG'] = 'WARN'   # keep stdout to the one JSON line (NCCL prints its version banner there)
         dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
     model = B200SevenNet(state_dict=load_weights(), device=dev)

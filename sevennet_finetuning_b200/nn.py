@@ -1,0 +1,595 @@
+"""Drop-in twins of the reference's ``sevenn.nn`` modules on the B200 kernels.
+
+Same class names, constructor arguments, parameter names/shapes and the same
+``forward(data: Dict[str, Tensor]) -> Dict[str, Tensor]`` contract as the reference
+(``sevenn/nn/*.py``, keys from ``sevenn/_keys.py:26-81``), so ``AtomGraphSequential.replace_module``
+(``sevenn/nn/sequential.py:61-62``) can swap them in and ``load_state_dict`` of a reference checkpoint works
+unchanged.  Every forward and every first-order backward is a kernel of libsevennet_b200.so reached through
+``torch.autograd.Function``; per-edge intermediates (weights, messages) are recomputed in backward instead of
+saved.  There is no CPU path: a CPU tensor raises.
+
+Scope of autograd: first order, including parameter gradients (energy-type losses train exactly).  Second order
+(``create_graph=True`` through the force output, ``sevenn/nn/force_output.py:168``, needed by force-matching
+losses) is not implemented in the kernels yet: ``ForceStressOutputFromEdge`` raises in training mode instead of
+silently returning non-differentiable forces.
+"""
+import math
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from ._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, EdgeParams
+
+C_SILU = 1.6791767923989418   # e3nn normalize2mom(silu)
+
+
+# ---- graph cache: the kernels want edges sorted by destination (edge_index[0], convolution.py:112-113) ----------------
+def _graph_of(data):
+    ei = data['edge_index']
+    g = data.get('_b200_graph')
+    if g is not None and g['key'] == (ei.data_ptr(), ei.shape[1]):
+        return g
+    dst64, src64 = ei[0], ei[1]
+    n = data['x'].shape[0] if data['x'].dim() > 0 else int(data['num_atoms'])
+    if 'x_ghost' in data and data['x_ghost'].dim() > 0:
+        n_src = n + data['x_ghost'].shape[0]
+    else:
+        n_src = n
+    E = ei.shape[1]
+    perm = None
+    if E > 1 and bool((dst64[1:] < dst64[:-1]).any()):
+        perm = torch.argsort(dst64, stable=True)
+        dst64, src64 = dst64[perm], src64[perm]
+    dst, src = dst64.to(torch.int32).contiguous(), src64.to(torch.int32).contiguous()
+    rowptr = torch.zeros(n_src + 1, dtype=torch.int32, device=ei.device)
+    if E:
+        rowptr[1:] = torch.cumsum(torch.bincount(dst64, minlength=n_src), 0).to(torch.int32)
+    rrowptr, eid = ops.csr_transpose(n_src, src)
+    g = dict(key=(ei.data_ptr(), ei.shape[1]), perm=perm, dst=dst, src=src, rowptr=rowptr, rrowptr=rrowptr, eid=eid,
+             n_dst=n, n_src=n_src)
+    data['_b200_graph'] = g
+    return g
+
+
+# ---- autograd functions ---------------------------------------------------------------------------------------------
+class _EdgeEmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, vec, coeffs, params):
+        v = ops._f32(vec)
+        ln, Y, emb = ops.edge_embed_fwd(params, v, ops._f32(coeffs))
+        ctx.save_for_backward(v, coeffs.detach())
+        ctx.params = params
+        return ln, Y, emb
+
+    @staticmethod
+    def backward(ctx, g_len, gY, gemb):
+        v, coeffs = ctx.saved_tensors
+        p = ctx.params
+        gY = None if gY is None else ops._f32(gY)
+        gemb = None if gemb is None else ops._f32(gemb)
+        dvec = None
+        if ctx.needs_input_grad[0]:
+            dvec = ops.edge_embed_bwd(p, v, ops._f32(coeffs), gY, gemb)
+            if g_len is not None:
+                dvec = dvec + g_len.unsqueeze(-1) * v / torch.linalg.norm(v, dim=-1, keepdim=True)
+        dco = None
+        if ctx.needs_input_grad[1] and gemb is not None:
+            # d emb[e, n] / d k_n = (2 / r_c) cos(k_n r) f_cut(r)   (edge_embedding.py:114-116)
+            r = torch.linalg.norm(v, dim=-1, keepdim=True)
+            dco = (gemb * (2.0 / p.r_cut) * torch.cos(coeffs * r) * _cutoff_torch(p, r)).sum(0)
+        return dvec, dco, None
+
+
+def _cutoff_torch(p, r):
+    if p.cutoff_kind == B200_CUTOFF_XPLOR:
+        rc2, ron2, r2 = p.r_cut ** 2, p.r_on ** 2, r * r
+        f = (rc2 - r2) ** 2 * (rc2 + 2 * r2 - 3 * ron2) / (rc2 - ron2) ** 3
+        return torch.where(r < p.r_on, torch.ones_like(r), f)
+    x, pp = r / p.r_cut, p.poly_p
+    return 1 - (pp + 1) * (pp + 2) / 2 * x ** pp + pp * (pp + 2) * x ** (pp + 1) - pp * (pp + 1) / 2 * x ** (pp + 2)
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, W, desc, numel):
+        x32, W32 = ops._f32(x), ops._f32(W)
+        ctx.save_for_backward(x32, W32)
+        ctx.desc, ctx.numel = desc, numel
+        return ops.irreps_linear(desc, x32, W32)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, W = ctx.saved_tensors
+        gy = ops._f32(gy)
+        dx = ops.irreps_linear(ctx.desc, gy, W, transpose=True) if ctx.needs_input_grad[0] else None
+        dW = ops.irreps_linear_wgrad(ctx.desc, x, gy, ctx.numel) if ctx.needs_input_grad[1] else None
+        return dx, dW, None, None
+
+
+class _EmbedFn(torch.autograd.Function):
+    """one_hot(type) . W / sqrt(n_species) as a row gather (node_embedding.py:39-48 + linear.py:37-44)."""
+
+    @staticmethod
+    def forward(ctx, types, W, n_species, dim):
+        t32 = ops._i32(types)
+        ctx.save_for_backward(t32)
+        ctx.n_species, ctx.dim = n_species, dim
+        return ops.embed_fwd(t32, ops._f32(W).view(n_species, dim), n_species)
+
+    @staticmethod
+    def backward(ctx, g):
+        (t,) = ctx.saved_tensors
+        dW = torch.zeros(ctx.n_species, ctx.dim, dtype=torch.float32, device=g.device)
+        dW.index_add_(0, t.long(), ops._f32(g) / math.sqrt(ctx.n_species))
+        return None, dW.reshape(-1), None, None
+
+
+class _GateFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, ns, m1, m2):
+        x32 = ops._f32(x)
+        ctx.save_for_backward(x32)
+        ctx.dims = (ns, m1, m2)
+        return ops.gate_fwd(ns, m1, m2, x32)
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        return ops.gate_bwd(*ctx.dims, x, ops._f32(g)), None, None, None
+
+
+class _ConvFn(torch.autograd.Function):
+    """weight_nn + uvu tensor product + scatter / denominator (convolution.py:105-121); edges sorted by dst."""
+
+    @staticmethod
+    def forward(ctx, x, Y, emb, W0, W1, W2, denom, graph, muls, lout):
+        x32, Y32, e32 = ops._f32(x), ops._f32(Y), ops._f32(emb)
+        Ws = [ops._f32(W) for W in (W0, W1, W2)]
+        w = ops.radial_mlp_fwd(e32, *Ws)
+        d = float(denom)
+        out = ops.conv_fwd(muls, lout, graph['rowptr'][:graph['n_dst'] + 1].contiguous(), graph['src'], x32, Y32, w, d)
+        ctx.save_for_backward(x32, Y32, e32, *Ws, out)
+        ctx.graph, ctx.muls, ctx.lout, ctx.denom = graph, muls, lout, d
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, Y, emb, W0, W1, W2, out = ctx.saved_tensors
+        g, muls, lout, d = ctx.graph, ctx.muls, ctx.lout, ctx.denom
+        gout = ops._f32(gout)
+        rowptr = g['rowptr'][:g['n_dst'] + 1].contiguous()
+        w = ops.radial_mlp_fwd(emb, W0, W1, W2)                       # recomputed, never saved
+        dw, dY = ops.conv_bwd_edge(muls, lout, rowptr, g['src'], x, Y, w, gout, d)
+        dY[:, 0] = 0.0
+        dx = ops.conv_bwd_x(muls, lout, x.shape[0], g['rrowptr'], g['eid'], g['dst'], gout, Y, w, d) \
+            if ctx.needs_input_grad[0] else None
+        demb = ops.radial_mlp_bwd(emb, W0, W1, W2, dw) if ctx.needs_input_grad[2] else None
+        dW0 = dW1 = dW2 = None
+        if any(ctx.needs_input_grad[3:6]):
+            # parameter gradients of the radial MLP: small dense GEMMs over the edge axis (library GEMMs)
+            nb, h = W0.shape[0], W1.shape[0]
+            z1 = emb @ W0 / math.sqrt(nb)
+            s1 = torch.sigmoid(z1)
+            h1 = C_SILU * z1 * s1
+            z2 = h1 @ W1 / math.sqrt(h)
+            s2 = torch.sigmoid(z2)
+            h2 = C_SILU * z2 * s2
+            k2 = 1.0 / math.sqrt(W2.shape[0])
+            dW2 = h2.t() @ dw * k2
+            dz2 = (dw @ W2.t() * k2) * (C_SILU * s2 * (1 + z2 * (1 - s2)))
+            dW1 = h1.t() @ dz2 / math.sqrt(h)
+            dz1 = (dz2 @ W1.t() / math.sqrt(h)) * (C_SILU * s1 * (1 + z1 * (1 - s1)))
+            dW0 = emb.t() @ dz1 / math.sqrt(nb)
+        dden = -(out * gout).sum().reshape(1) / d if ctx.needs_input_grad[6] else None
+        return dx, dY, demb, dW0, dW1, dW2, dden, None, None, None
+
+
+# ---- modules ----------------------------------------------------------------------------------------------------------
+class BesselBasis(nn.Module):
+    """sevenn/nn/edge_embedding.py:80-116 (parameters only; evaluated inside the edge kernel)."""
+
+    def __init__(self, cutoff_length, bessel_basis_num=8, trainable_coeff=True):
+        super().__init__()
+        self.num_basis, self.cutoff_length = bessel_basis_num, cutoff_length
+        c = torch.tensor([n * math.pi / cutoff_length for n in range(1, bessel_basis_num + 1)], dtype=torch.float32)
+        if trainable_coeff:
+            self.coeffs = nn.Parameter(c)
+        else:
+            self.register_buffer('coeffs', c)
+
+
+class PolynomialCutoff(nn.Module):
+    """sevenn/nn/edge_embedding.py:119-145."""
+
+    def __init__(self, cutoff_length, poly_cut_p_value=6):
+        super().__init__()
+        self.cutoff_length, self.p = cutoff_length, poly_cut_p_value
+
+
+class XPLORCutoff(nn.Module):
+    """sevenn/nn/edge_embedding.py:148-173."""
+
+    def __init__(self, cutoff_length, cutoff_on):
+        super().__init__()
+        self.cutoff_length, self.cutoff_on = cutoff_length, cutoff_on
+
+
+class SphericalEncoding(nn.Module):
+    """sevenn/nn/edge_embedding.py:177-198 (lmax 2, component normalisation)."""
+
+    def __init__(self, lmax, parity=-1, normalization='component', normalize=True):
+        super().__init__()
+        if lmax != 2 or normalization != 'component':
+            raise ValueError('B200 path: lmax = 2 with component normalisation only')
+        self.lmax, self.normalize = lmax, normalize
+
+
+class EdgeEmbedding(nn.Module):
+    """sevenn/nn/edge_embedding.py:202-230."""
+
+    def __init__(self, basis_module, cutoff_module, spherical_module):
+        super().__init__()
+        self.basis_function, self.cutoff_function, self.spherical = basis_module, cutoff_module, spherical_module
+
+    def _params(self):
+        c, b = self.cutoff_function, self.basis_function
+        if isinstance(c, XPLORCutoff):
+            return EdgeParams(b.num_basis, B200_CUTOFF_XPLOR, int(self.spherical.normalize), float(c.cutoff_length),
+                              float(c.cutoff_on), 6.0)
+        return EdgeParams(b.num_basis, B200_CUTOFF_POLY, int(self.spherical.normalize), float(c.cutoff_length), 0.0, float(c.p))
+
+    def forward(self, data):
+        ln, Y, emb = _EdgeEmbedFn.apply(data['edge_vec'], self.basis_function.coeffs, self._params())
+        data['edge_length'], data['edge_attr'], data['edge_embedding'] = ln, Y, emb
+        return data
+
+
+class OnehotEmbedding(nn.Module):
+    """sevenn/nn/node_embedding.py:15-48: x (species index) -> one-hot x, node_attr, atom_type."""
+
+    def __init__(self, num_classes, data_key_x='x', data_key_save='atom_type', data_key_additional='node_attr'):
+        super().__init__()
+        self.num_classes = num_classes
+        self.key_x, self.key_save, self.key_additional_output = data_key_x, data_key_save, data_key_additional
+
+    def forward(self, data):
+        idx = data[self.key_x]
+        if not idx.is_cuda:
+            raise RuntimeError('sevennet_b200: CPU tensor passed to a CUDA-only module')
+        data[self.key_save] = idx
+        onehot = torch.nn.functional.one_hot(idx.long(), self.num_classes).to(torch.float32)
+        data[self.key_x] = onehot
+        if self.key_additional_output is not None:
+            data[self.key_additional_output] = onehot
+        return data
+
+
+class IrrepsLinear(nn.Module):
+    """sevenn/nn/linear.py:14-49; parameter ``linear.weight`` is the flat e3nn weight vector."""
+
+    class _Holder(nn.Module):
+        def __init__(self, numel):
+            super().__init__()
+            self.weight = nn.Parameter(torch.randn(numel))
+
+    def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, is_embed=False, **e3nn_linear_params):
+        super().__init__()
+        self.key_input = data_key_in
+        self.key_output = data_key_in if data_key_out is None else data_key_out
+        self.irreps_in, self.irreps_out, self.is_embed = irreps_in, irreps_out, is_embed
+        self.desc, self.numel = ops.make_lin_desc(irreps_in, irreps_out)
+        self.linear = IrrepsLinear._Holder(self.numel)
+        if is_embed:   # the reference pre-divides the initial weight by the path weight (linear.py:37-44)
+            with torch.no_grad():
+                self.linear.weight.div_(1.0 / math.sqrt(ops.muls_of(irreps_in)[0]))
+
+    def forward(self, data):
+        x = data[self.key_input]
+        if self.is_embed and 'atom_type' in data:
+            # one-hot input: a row gather of W / sqrt(n_species) instead of a dense product with 89x wasted work
+            nsp, dim = ops.muls_of(self.irreps_in)[0], ops.muls_of(self.irreps_out)[0]
+            data[self.key_output] = _EmbedFn.apply(data['atom_type'], self.linear.weight, nsp, dim)
+        else:
+            data[self.key_output] = _LinearFn.apply(x, self.linear.weight, self.desc, self.numel)
+        return data
+
+
+class SelfConnectionLinearIntro(nn.Module):
+    """sevenn/nn/self_connection.py:42-62."""
+
+    def __init__(self, irreps_x, irreps_out, data_key_x='x', **kwargs):
+        super().__init__()
+        self.irreps_x, self.irreps_out, self.key_x = irreps_x, irreps_out, data_key_x
+        self.desc, self.numel = ops.make_lin_desc(irreps_x, irreps_out)
+        self.linear = IrrepsLinear._Holder(self.numel)
+
+    def forward(self, data):
+        data['self_cont_tmp'] = _LinearFn.apply(data[self.key_x], self.linear.weight, self.desc, self.numel)
+        return data
+
+
+class SelfConnectionOutro(nn.Module):
+    """sevenn/nn/self_connection.py:93-109."""
+
+    def __init__(self, data_key_x='x'):
+        super().__init__()
+        self.key_x = data_key_x
+
+    def forward(self, data):
+        data[self.key_x] = data[self.key_x] + data['self_cont_tmp']
+        del data['self_cont_tmp']
+        return data
+
+
+class _RadialNet(nn.Module):
+    """parameter holder with e3nn FullyConnectedNet's names: layer{k}.weight [in, out]."""
+
+    class _Layer(nn.Module):
+        def __init__(self, a, b):
+            super().__init__()
+            self.weight = nn.Parameter(torch.randn(a, b))
+
+    def __init__(self, hs):
+        super().__init__()
+        for k, (a, b) in enumerate(zip(hs[:-1], hs[1:])):
+            setattr(self, f'layer{k}', _RadialNet._Layer(a, b))
+
+
+class IrrepsConvolution(nn.Module):
+    """sevenn/nn/convolution.py:36-123 (silu radial activation, 3-layer weight_nn, filter 0e+1e+2e)."""
+
+    def __init__(self, irreps_x, irreps_filter, irreps_out, weight_layer_input_to_hidden, weight_layer_act='silu',
+                 denominator=1.0, weight_shift=0.0, weight_scale=1.0, train_denominator=False, data_key_x='x',
+                 data_key_filter='edge_attr', data_key_weight_input='edge_embedding', data_key_edge_idx='edge_index',
+                 is_parallel=False):
+        super().__init__()
+        if weight_shift != 0.0 or weight_scale != 1.0:
+            raise ValueError('B200 path: weight_shift / weight_scale other than 0 / 1 are not supported')
+        if len(weight_layer_input_to_hidden) != 3:
+            raise ValueError('B200 path: weight_nn with two hidden layers')
+        self.muls = ops.muls_of(irreps_x)
+        louts = [l for _, l in ops.parse_irreps(irreps_out)]
+        self.lout = max(louts)
+        self.weight_numel, self.out_dim = ops.conv_dims(*self.muls, self.lout)
+        self.denominator = nn.Parameter(torch.tensor([float(denominator)]), requires_grad=train_denominator)
+        self.weight_nn = _RadialNet(list(weight_layer_input_to_hidden) + [self.weight_numel])
+        self.key_x, self.key_filter, self.key_weight_input, self.key_edge_idx = (
+            data_key_x, data_key_filter, data_key_weight_input, data_key_edge_idx)
+        self.is_parallel = is_parallel
+        self._comm_size = self.muls[0] + 3 * self.muls[1] + 5 * self.muls[2]   # convolution.py:102
+
+    def forward(self, data):
+        g = _graph_of(data)
+        x = data[self.key_x]
+        if self.is_parallel:
+            x = torch.cat([x, data['x_ghost']])
+        Y, emb = data[self.key_filter], data[self.key_weight_input]
+        if g['perm'] is not None:
+            Y, emb = Y.index_select(0, g['perm']), emb.index_select(0, g['perm'])
+        nn_ = self.weight_nn
+        out = _ConvFn.apply(x, Y, emb, nn_.layer0.weight, nn_.layer1.weight, nn_.layer2.weight, self.denominator, g,
+                            self.muls, self.lout)
+        data[self.key_x] = out   # rows of the local atoms only (convolution.py:119-121)
+        return data
+
+
+class EquivariantGate(nn.Module):
+    """sevenn/nn/equivariant_gate.py:13-61 (silu on scalars and gates, even parity)."""
+
+    def __init__(self, irreps_x, act_scalar_dict=None, act_gate_dict=None, data_key_x='x'):
+        super().__init__()
+        self.key_x = data_key_x
+        self.muls = ops.muls_of(irreps_x)
+        self.irreps_out = irreps_x
+
+    def get_gate_irreps_in(self):
+        m0, m1, m2 = self.muls
+        parts = [f'{m0 + m1 + m2}x0e'] + ([f'{m1}x1e'] if m1 else []) + ([f'{m2}x2e'] if m2 else [])
+        return '+'.join(parts)
+
+    def forward(self, data):
+        data[self.key_x] = _GateFn.apply(data[self.key_x], *self.muls)
+        return data
+
+
+class Rescale(nn.Module):
+    """sevenn/nn/scale.py:12-38."""
+
+    def __init__(self, shift, scale, data_key_in='scaled_atomic_energy', data_key_out='atomic_energy',
+                 train_shift_scale=False, **kwargs):
+        super().__init__()
+        self.shift = nn.Parameter(torch.tensor([float(shift)]), requires_grad=train_shift_scale)
+        self.scale = nn.Parameter(torch.tensor([float(scale)]), requires_grad=train_shift_scale)
+        self.key_input, self.key_output = data_key_in, data_key_out
+
+    def forward(self, data):
+        data[self.key_output] = data[self.key_input] * self.scale + self.shift
+        return data
+
+
+class SpeciesWiseRescale(nn.Module):
+    """sevenn/nn/scale.py:42-73."""
+
+    def __init__(self, shift, scale, data_key_in='scaled_atomic_energy', data_key_out='atomic_energy',
+                 data_key_indices='atom_type', train_shift_scale=False):
+        super().__init__()
+        self.shift = nn.Parameter(torch.tensor(shift, dtype=torch.float32), requires_grad=train_shift_scale)
+        self.scale = nn.Parameter(torch.tensor(scale, dtype=torch.float32), requires_grad=train_shift_scale)
+        self.key_input, self.key_output, self.key_indices = data_key_in, data_key_out, data_key_indices
+
+    def forward(self, data):
+        idx = data[self.key_indices].long()
+        data[self.key_output] = data[self.key_input] * self.scale[idx].view(-1, 1) + self.shift[idx].view(-1, 1)
+        return data
+
+
+class AtomReduce(nn.Module):
+    """sevenn/nn/linear.py:53-90."""
+
+    def __init__(self, data_key_in, data_key_out, reduce='sum', constant=1.0):
+        super().__init__()
+        self.key_input, self.key_output, self.constant = data_key_in, data_key_out, constant
+        self._is_batch_data = True
+
+    def forward(self, data):
+        src = data[self.key_input].squeeze(1)
+        if self._is_batch_data:
+            size = int(data['batch'].max()) + 1
+            out = torch.zeros(size, dtype=src.dtype, device=src.device)
+            out.scatter_reduce_(0, data['batch'], src, reduce='sum')
+            data[self.key_output] = out * self.constant
+        else:
+            data[self.key_output] = torch.sum(src) * self.constant
+        return data
+
+
+class ForceStressOutputFromEdge(nn.Module):
+    """sevenn/nn/force_output.py:133-215: forces and stress from dE/d edge_vec."""
+
+    def __init__(self, data_key_edge='edge_vec', data_key_edge_idx='edge_index', data_key_energy='inferred_total_energy',
+                 data_key_force='inferred_force', data_key_stress='inferred_stress', data_key_cell_volume='cell_volume'):
+        super().__init__()
+        self.key_edge, self.key_edge_idx, self.key_energy = data_key_edge, data_key_edge_idx, data_key_energy
+        self.key_force, self.key_stress, self.key_cell_volume = data_key_force, data_key_stress, data_key_cell_volume
+        self._is_batch_data = True
+
+    def forward(self, data):
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError(
+                'sevennet_b200: force output with create_graph=True (force/stress-matching loss) needs the second-order '
+                'kernels, which are not built yet; train on the energy or call .eval() for inference')
+        energy = data[self.key_energy]
+        rij = data[self.key_edge]
+        (fij,) = torch.autograd.grad([energy.sum()], [rij], create_graph=False, allow_unused=True)
+        g = _graph_of(data)
+        n = g['n_src']
+        if fij is None:
+            fij = torch.zeros_like(rij)
+        ei = data[self.key_edge_idx]
+        force = torch.zeros(n, 3, dtype=fij.dtype, device=fij.device)
+        force.index_add_(0, ei[0], fij)
+        force.index_add_(0, ei[1], -fij)
+        data[self.key_force] = force
+        diag = rij * fij
+        s12 = rij[:, 0] * fij[:, 1]
+        s23 = rij[:, 1] * fij[:, 2]
+        s31 = rij[:, 2] * fij[:, 0]
+        vir = torch.cat([diag, s12.unsqueeze(-1), s23.unsqueeze(-1), s31.unsqueeze(-1)], dim=-1)
+        if self._is_batch_data:
+            batch = data['batch']
+            nb = int(batch.max()) + 1
+            per = torch.zeros(nb, 6, dtype=vir.dtype, device=vir.device)
+            per.index_add_(0, batch[ei[1]], vir)
+            data[self.key_stress] = -per / data[self.key_cell_volume].view(-1, 1)
+        else:
+            data[self.key_stress] = -vir.sum(0) / data[self.key_cell_volume]
+        return data
+
+
+class AtomGraphSequential(nn.Sequential):
+    """sevenn/nn/sequential.py:15-90."""
+
+    def __init__(self, modules, cutoff=0.0, type_map=None):
+        if not isinstance(modules, OrderedDict):
+            modules = OrderedDict(modules)
+        super().__init__(modules)
+        self.cutoff, self.type_map = cutoff, type_map
+        self._is_batch_data = True
+
+    def set_is_batch_data(self, flag):
+        for m in self:
+            if hasattr(m, '_is_batch_data'):
+                m._is_batch_data = flag
+        self._is_batch_data = flag
+
+    def prepand_module(self, key, module):
+        self._modules.update({key: module})
+        self._modules.move_to_end(key, last=False)
+
+    def replace_module(self, key, module):
+        self._modules.update({key: module})
+
+    def delete_module_by_key(self, key):
+        if key in self._modules:
+            del self._modules[key]
+
+    def forward(self, data):
+        for m in self:
+            data = m(data)
+        data.pop('_b200_graph', None)
+        return data
+
+
+def build_E3_equivariant_model(config=None):
+    """The module chain of ``sevenn/model_build.py:186-445`` ('nequip' interaction, 'linear' self connection,
+    ``irreps_manual``) with the reference's module names, built from the B200 twins."""
+    from .model import SEVENNET0_CONFIG
+    cfg = dict(SEVENNET0_CONFIG)
+    cfg.update(config or {})
+    cutoff, nsp = cfg['cutoff'], cfg['num_species']
+    man = cfg['irreps_manual']
+    nconv = cfg['num_convolution_layer']
+    cf = cfg['cutoff_function']
+    env = (XPLORCutoff(cutoff, cf['cutoff_on']) if cf['name'].upper() == 'XPLOR'
+           else PolynomialCutoff(cutoff, cf.get('poly_cut_p_value', 6)))
+    L = OrderedDict()
+    L['edge_embedding'] = EdgeEmbedding(BesselBasis(cutoff, cfg['bessel_basis_num']), env,
+                                        SphericalEncoding(cfg['lmax'], 1, normalize=cfg.get('normalize_sph', True)))
+    L['onehot_idx_to_onehot'] = OnehotEmbedding(nsp)
+    irreps_x = man[0]
+    L['onehot_to_feature_x'] = IrrepsLinear(f'{nsp}x0e', irreps_x, 'x', is_embed=True)
+    den = cfg.get('conv_denominator', 1.0)
+    den = den if isinstance(den, (list, tuple)) else [den] * nconv
+    for t in range(nconv):
+        irreps_out = man[t + 1]
+        lmax_node = 0 if t == nconv - 1 else cfg['lmax']
+        tp_out = '+'.join(f'1x{l}e' for l in range(lmax_node + 1))
+        gate = EquivariantGate(irreps_out)
+        gin = gate.get_gate_irreps_in()
+        L[f'{t}_self_connection_intro'] = SelfConnectionLinearIntro(irreps_x, gin)
+        L[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, 'x')
+        conv = IrrepsConvolution(irreps_x, '1x0e+1x1e+1x2e', tp_out,
+                                 [cfg['bessel_basis_num']] + list(cfg['weight_nn_hidden_neurons']), 'silu', den[t])
+        L[f'{t}_convolution'] = conv
+        m = ops.muls_of(irreps_x)
+        msg = {0: [0, 0, 0]}[0]
+        for (l1, l2, l3) in [(a, b, c) for a in range(3) for b in range(3) for c in range(abs(a - b), min(a + b, lmax_node) + 1)]:
+            if m[l1] > 0:
+                msg[l3] += m[l1]
+        irreps_msg = '+'.join(f'{msg[l]}x{l}e' for l in range(3) if msg[l] > 0)
+        L[f'{t}_self_interaction_2'] = IrrepsLinear(irreps_msg, gin, 'x')
+        L[f'{t}_self_connection_outro'] = SelfConnectionOutro()
+        L[f'{t}_equivariant_gate'] = gate
+        irreps_x = irreps_out
+    mid = ops.muls_of(man[-1])[0]
+    L['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, f'{mid // 2}x0e', 'x')
+    L['reduce_hidden_to_energy'] = IrrepsLinear(f'{mid // 2}x0e', '1x0e', 'x', 'scaled_atomic_energy')
+    shift, scale = cfg.get('shift', 0.0), cfg.get('scale', 1.0)
+    if cfg['use_species_wise_shift_scale']:
+        shift = shift if isinstance(shift, (list, tuple)) else [float(shift)] * nsp
+        scale = scale if isinstance(scale, (list, tuple)) else [float(scale)] * nsp
+        L['rescale_atomic_energy'] = SpeciesWiseRescale(list(shift), list(scale))
+    else:
+        L['rescale_atomic_energy'] = Rescale(shift, scale)
+    L['reduce_total_enegy'] = AtomReduce('atomic_energy', 'inferred_total_energy')
+    L['force_output'] = ForceStressOutputFromEdge()
+    return AtomGraphSequential(L, cutoff)
+
+
+_TWINS = ('EdgeEmbedding', 'OnehotEmbedding', 'IrrepsLinear', 'SelfConnectionLinearIntro', 'SelfConnectionOutro',
+          'IrrepsConvolution', 'EquivariantGate', 'Rescale', 'SpeciesWiseRescale', 'AtomReduce', 'ForceStressOutputFromEdge')
+
+
+def substitute(model, config=None):
+    """Replace the hot-path modules of a reference ``AtomGraphSequential`` by their B200 twins, key by key
+    (``replace_module``, ``sevenn/nn/sequential.py:61-62``), and copy the parameters (names and shapes are identical)."""
+    twin = build_E3_equivariant_model(config)
+    ref_sd = model.state_dict()
+    twin.load_state_dict({k: v for k, v in ref_sd.items() if k in twin.state_dict()}, strict=False)
+    dev = next(model.parameters()).device
+    for key, mod in twin._modules.items():
+        if key in model._modules and type(model._modules[key]).__name__ in _TWINS:
+            model.replace_module(key, mod.to(dev))
+    return model
