@@ -263,9 +263,6 @@ fused_radial_kernel(EdgeParams ep, int nb, long long E, const float* __restrict_
 }
 
 // ---- shared pieces of the two convolution kernels ---------------------------------------------------------------
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 // whole warp: 8 consecutive fp32 columns of this warp's 32 TMEM lanes
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
   uint32_t r[8];

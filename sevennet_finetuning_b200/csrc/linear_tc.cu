@@ -73,8 +73,10 @@ __global__ void linear_prepack_kernel(LinTcPlan pl, const float* __restrict__ W,
 // The tensor core adds into its fp32 accumulator with truncation: the bias grows with the number of MMAs an
 // accumulator receives (measured: -2.4e-8 relative per MMA).  So every K=8 step of the main product (hi*hi) gets a
 // fresh TMEM accumulator (two per chunk, ping-pong over chunks) that the threads drain into fp32 registers with
-// round-to-nearest adds, and the two small cross products (lo*hi, hi*lo) go to a fifth accumulator of their own.
-__global__ void __launch_bounds__(L_T, 1)
+// round-to-nearest adds; the two small cross products (lo*hi, hi*lo) of the step are issued first into the same
+// accumulator, so the large product is added (one truncation) to a sum that is 2^-11 of its size.  Four accumulators
+// of 64 columns = 256 TMEM columns per CTA: two CTAs share an SM and hide each other's gather and drain latency.
+__global__ void __launch_bounds__(L_T, 2)
 irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, const float* __restrict__ pack,
                         float* __restrict__ y, int accumulate) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -88,7 +90,7 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
   const int q = warp & 3, half = warp >> 2;      // TMEM lane quarter, 32-column half of the pass
   const uint32_t bpart = (uint32_t)(LK / 4) * b.Npad * 16;   // bytes of one part (hi or lo) of a B chunk
 
-  if (warp == 0) tmem_alloc(&s.tmem_base, 512);
+  if (warp == 0) tmem_alloc(&s.tmem_base, 256);
   if (threadIdx.x == 32) {
     for (int k = 0; k < 2; ++k) { mbar_init(&s.full_b[k], 1); mbar_init(&s.mma_done[k], 1); }
     fence_mbar_init();
@@ -145,7 +147,7 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
       tc_fence_after();
       drain(c - 2);
     }
-    if (threadIdx.x == 0) {
+    if (warp == 0 && elect_one()) {
       mbar_expect_tx(&s.full_b[st], 2 * bpart);
       const float* src = pack + b.pack_off + (size_t)c * (2 * bpart / 4);
       bulk_copy_g2s(s.B[st], src, bpart, &s.full_b[st]);
@@ -175,35 +177,28 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (warp == 0 && elect_one()) {
       mbar_wait(&s.full_b[st], (c >> 1) & 1);
       tc_fence_after();
       const uint32_t ah = smem_u32(s.A[st]), al = ah + L_APART, bh = smem_u32(s.B[st]), bl = bh + L_BPART;
       const uint32_t bch = (uint32_t)b.Npad * 16;
-      const uint32_t dmain = tmem + (uint32_t)(2 * (c & 1) * L_MAXN), dcross = tmem + 4 * L_MAXN;
+      const uint32_t dmain = tmem + (uint32_t)(2 * (c & 1) * L_MAXN);
 #pragma unroll
       for (int kk = 0; kk < LK / 8; ++kk) {
         const uint64_t dah = make_desc(ah + kk * 2 * L_ACH, L_ACH, 128), dal = make_desc(al + kk * 2 * L_ACH, L_ACH, 128);
         const uint64_t dbh = make_desc(bh + kk * 2 * bch, bch, 128), dbl = make_desc(bl + kk * 2 * bch, bch, 128);
-        mma_tf32(dcross, dal, dbh, idesc, (c > 0 || kk > 0) ? 1u : 0u);
-        mma_tf32(dcross, dah, dbl, idesc, 1);
-        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbh, idesc, 0u);
+        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dal, dbh, idesc, 0u);
+        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbl, idesc, 1u);
+        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbh, idesc, 1u);
       }
       mma_commit(&s.mma_done[st]);
     }
   }
-  // the last two chunks, then the cross terms (MMAs retire in order)
+  // the last two chunks (MMAs retire in order)
   for (int c = max(0, b.nchunk - 2); c < b.nchunk; ++c) {
     mbar_wait(&s.mma_done[c & 1], (c >> 1) & 1);
     tc_fence_after();
     drain(c);
-  }
-  tc_fence_after();
-  if (have_cols) {
-    float v[32];
-    tmem_ld32(tlane + 4 * L_MAXN, v);
-#pragma unroll
-    for (int j = 0; j < 32; ++j) acc[j] += v[j];
   }
   // transpose the warp's 32x32 block so that the stores run along the output channels of one (node, m) row
   float (*T)[33] = s.T[warp];
@@ -222,7 +217,7 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 512);
+  if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
 // plan: one pass per (block, <=256 output columns); returns false when a block is too small for the tensor-core path

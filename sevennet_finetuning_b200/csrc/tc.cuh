@@ -16,6 +16,14 @@ namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// whole (converged) warp: true in exactly one lane.  Branching on this instead of `lane == 0` lets ptxas keep the
+// tcgen05 / bulk-copy instructions of the elected thread on the uniform datapath without per-instruction elect loops.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
@@ -23,8 +31,7 @@ __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier
 // spin on the phase parity; traps (instead of hanging the GPU) if the barrier never flips
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
-  const long long t0 = clock64();
-  for (;;) {
+  for (uint32_t spins = 0;; ++spins) {
     uint32_t done;
     asm volatile(
         "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
@@ -32,7 +39,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         : "r"(addr), "r"(parity)
         : "memory");
     if (done) break;
-    if (clock64() - t0 > (1LL << 31)) __trap();
+    if (spins > (1u << 26)) __trap();
   }
 }
 
@@ -71,6 +78,19 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
   d |= (uint64_t)1 << 46;                             // descriptor version 1 (Blackwell)
   return d;                                           // base_offset 0, layout_type 0 = SWIZZLE_NONE
 }
+// K-major SWIZZLE_128B operand whose K extent is one 128-byte swizzle atom (32 tf32): row r occupies 128 contiguous
+// bytes at r*128 and its 16-byte unit u is stored at unit u ^ (r & 7) (what TMA writes with CU_TENSOR_MAP_SWIZZLE_128B);
+// groups of 8 rows are 1024 B apart (SBO), the tile base is 1024-byte aligned, a K-step of 8 advances the start
+// address by 32 bytes inside the atom.
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;                  // LBO: unused for a single swizzle atom along K
+  d |= (uint64_t)(1024 >> 4) << 32;        // SBO
+  d |= (uint64_t)1 << 46;                  // descriptor version 1 (Blackwell)
+  d |= (uint64_t)2 << 61;                  // layout type SWIZZLE_128B
+  return d;
+}
 // instruction descriptor: D fp32, A/B tf32, both K-major, shape M x N (cute::UMMA::InstrDescriptor bit layout)
 __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -104,6 +124,35 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
       : "memory");
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// whole warp: 16 consecutive fp32 columns of this warp's 32 TMEM lanes -> v[16]
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// one thread: plain arrive (release) on a CTA-local mbarrier
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// whole warp: writes of all lanes are ordered before one arrival of the warp (barrier count = number of warps)
+__device__ __forceinline__ void warp_arrive(uint64_t* bar) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0) mbar_arrive(bar);
+}
+// named barrier among `nthreads` threads of the CTA (id 1..15; id 0 is __syncthreads)
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // x ~= hi + lo with both parts representable in tf32 (round-to-nearest): |x - hi - lo| <= 2^-22 |x|
