@@ -77,6 +77,11 @@ int b200_conv_bwd_edge(int m0, int m1, int m2, int lout, int n_dst, int64_t n_ed
                        const int32_t* src, const float* x, const float* edge_attr, const float* weight,
                        const float* d_out, float denominator, float* d_weight, float* d_edge_attr, int accumulate,
                        void* stream);
+/* the same pass with d x[n_src,x_dim] added (zeroed inside, accumulated with RED.ADD per edge: the sums are
+ * order-nondeterministic like the reference's index_add scatter); replaces b200_conv_bwd_edge + b200_conv_bwd_x */
+int b200_conv_bwd(int m0, int m1, int m2, int lout, int n_dst, int n_src, int64_t n_edges, const int32_t* rowptr,
+                  const int32_t* src, const float* x, const float* edge_attr, const float* weight, const float* d_out,
+                  float denominator, float* d_weight, float* d_edge_attr, int accumulate, float* d_x, void* stream);
 /* d x[n_src,x_dim]; rrowptr[n_src+1] / eid_by_src[E]: CSR of the same edges sorted by source, dst[E] = edge_index[0] */
 int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* rrowptr, const int32_t* eid_by_src,
                     const int32_t* dst, const float* d_out, const float* edge_attr, const float* weight,

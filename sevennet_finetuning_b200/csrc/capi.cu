@@ -84,6 +84,15 @@ int b200_conv_bwd_edge(int m0, int m1, int m2, int lout, int n_dst, int64_t E, c
   fill_conv_desc(m0, m1, m2, lout, d);
   return conv_bwd_edge(d, n_dst, (int)E, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, ST(stream));
 }
+int b200_conv_bwd(int m0, int m1, int m2, int lout, int n_dst, int n_src, int64_t E, const int32_t* rowptr, const int32_t* src,
+                  const float* x, const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY,
+                  int accumulate, float* dx, void* stream) {
+  B200_REQUIRE(lout == 0 || lout == 2, "conv_bwd: lout must be 0 or 2");
+  B200_REQUIRE(dx != nullptr, "conv_bwd: d_x is NULL (use b200_conv_bwd_edge)");
+  ConvDesc d;
+  fill_conv_desc(m0, m1, m2, lout, d);
+  return conv_bwd_edge_x(d, n_dst, n_src, (int)E, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, dx, ST(stream));
+}
 int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* rrowptr, const int32_t* eid,
                     const int32_t* dst, const float* gout, const float* Y, const float* w, float denom, float* dx,
                     void* stream) {

@@ -149,11 +149,15 @@ template <int PID> __device__ __forceinline__ void p_bwdx(const float* rec, cons
 
 // backward wrt the per-edge weight and the spherical harmonics:
 //   dw = sum_{a,c} M[a][c] x[a] g[c];   dY[b] += w * sum_{a,c} C[a,b,c] x[a] g[c]
-template <int PID>
-__device__ __forceinline__ void p_bwde(const float* rec, const float* x, const float* g, float w, float& dw, float* dY) {
+// and, with DX, the gradient wrt the gathered source row from the same intermediates:
+//   dx[a] += w * sum_c M[a][c] g[c]
+template <int PID, bool DX>
+__device__ __forceinline__ void p_bwde(const float* rec, const float* x, const float* g, float w, float& dw, float* dY,
+                                       float* dx) {
   using P = PathT<PID>;
   if constexpr (PID == P000) {
     dw = x[0] * g[0];
+    if constexpr (DX) dx[0] = fmaf(w, g[0], dx[0]);
   } else if constexpr (PID == P011 || PID == P022) {
     constexpr int yo = (PID == P011) ? 1 : 4;
     float s = 0.f;
@@ -164,10 +168,14 @@ __device__ __forceinline__ void p_bwde(const float* rec, const float* x, const f
       dY[yo + c] = fmaf(t, g[c], dY[yo + c]);
     }
     dw = x[0] * s;
+    if constexpr (DX) dx[0] = fmaf(w, s, dx[0]);
   } else if constexpr (PID == P101 || PID == P202) {
     float s = 0.f;
 #pragma unroll
-    for (int c = 0; c < P::D3; ++c) s = fmaf(x[c], g[c], s);
+    for (int c = 0; c < P::D3; ++c) {
+      s = fmaf(x[c], g[c], s);
+      if constexpr (DX) dx[c] = fmaf(w, g[c], dx[c]);
+    }
     dw = s;
   } else if constexpr (PID == P110 || PID == P220) {
     constexpr int yo = (PID == P110) ? 1 : 4;
@@ -178,6 +186,7 @@ __device__ __forceinline__ void p_bwde(const float* rec, const float* x, const f
     for (int a = 0; a < P::D1; ++a) {
       s = fmaf(x[a], rec[yo + a], s);
       dY[yo + a] = fmaf(t, x[a], dY[yo + a]);
+      if constexpr (DX) dx[a] = fmaf(t, rec[yo + a], dx[a]);
     }
     dw = g[0] * k * s;
   } else {
@@ -186,12 +195,16 @@ __device__ __forceinline__ void p_bwde(const float* rec, const float* x, const f
     float G[P::D1 * P::D3];
     float s = 0.f;
 #pragma unroll
-    for (int a = 0; a < P::D1; ++a)
+    for (int a = 0; a < P::D1; ++a) {
+      float ta = 0.f;   // sum_c M[a][c] g[c]: shared by dw and dx
 #pragma unroll
       for (int c = 0; c < P::D3; ++c) {
         G[a * P::D3 + c] = x[a] * g[c];
-        s = fmaf(M[a * P::D3 + c], G[a * P::D3 + c], s);
+        ta = fmaf(M[a * P::D3 + c], g[c], ta);
       }
+      s = fmaf(x[a], ta, s);
+      if constexpr (DX) dx[a] = fmaf(w, ta, dx[a]);
+    }
     dw = s;
     float t[9];
 #pragma unroll
@@ -211,7 +224,8 @@ template <> struct PL<> {
   __device__ __forceinline__ static void load_w(const ConvDesc&, const float*, int, float*) {}
   __device__ __forceinline__ static void fwd(const float*, const float*, const float*, float*) {}
   __device__ __forceinline__ static void bwdx(const float*, const float*, const float*, float*) {}
-  __device__ __forceinline__ static void bwde(const float*, const float*, const float*, const float*, float*, float*) {}
+  template <bool DX>
+  __device__ __forceinline__ static void bwde(const float*, const float*, const float*, const float*, float*, float*, float*) {}
   __device__ __forceinline__ static void load_o(const ConvDesc&, const float*, int, float, float*) {}
   __device__ __forceinline__ static void store_o(const ConvDesc&, float*, int, float, const float*) {}
   __device__ __forceinline__ static void store_w(const ConvDesc&, float*, int, const float*) {}
@@ -238,10 +252,11 @@ template <int PID, int... REST> struct PL<PID, REST...> {
     p_bwdx<PID>(rec, g, wv[0], dx);
     R::bwdx(rec, g + P::D3, wv + 1, dx);
   }
+  template <bool DX>
   __device__ __forceinline__ static void bwde(const float* rec, const float* x, const float* g, const float* wv, float* dwv,
-                                              float* dY) {
-    p_bwde<PID>(rec, x, g, wv[0], dwv[0], dY);
-    R::bwde(rec, x, g + P::D3, wv + 1, dwv + 1, dY);
+                                              float* dY, float* dx) {
+    p_bwde<PID, DX>(rec, x, g, wv[0], dwv[0], dY, dx);
+    R::template bwde<DX>(rec, x, g + P::D3, wv + 1, dwv + 1, dY, dx);
   }
   // o[0..NACC) <- scale * row[slot of channel u]
   __device__ __forceinline__ static void load_o(const ConvDesc& d, const float* __restrict__ row, int u, float scale, float* o) {
@@ -259,17 +274,16 @@ template <int PID, int... REST> struct PL<PID, REST...> {
 // group -> path list, per (ROLE, LOUT)
 template <int ROLE, int LOUT, int G> struct GroupT { using L = PL<>; };
 template <> struct GroupT<0, 2, 0> { using L = PL<P000, P011, P022>; };
-template <> struct GroupT<1, 2, 0> { using L = PL<P101, P110, P111, P121>; };
-template <> struct GroupT<1, 2, 1> { using L = PL<P112, P122>; };
-template <> struct GroupT<2, 2, 0> { using L = PL<P212>; };
-template <> struct GroupT<2, 2, 1> { using L = PL<P222>; };
-template <> struct GroupT<2, 2, 2> { using L = PL<P211, P202>; };
-template <> struct GroupT<2, 2, 3> { using L = PL<P221, P220>; };
+// One group per role: a thread owns ALL paths of its channel, so x[src], the dY warp reduction and the RED.ADD of
+// d x[src] happen once per (edge, channel).  (Splitting a role's paths over 2-4 thread groups was measured slower:
+// 2.4x more RED traffic and one shuffle reduction per group.)  The group index is kept for other splits.
+template <> struct GroupT<1, 2, 0> { using L = PL<P101, P110, P111, P121, P112, P122>; };
+template <> struct GroupT<2, 2, 0> { using L = PL<P212, P222, P211, P202, P221, P220>; };
 template <> struct GroupT<0, 0, 0> { using L = PL<P000>; };
 template <> struct GroupT<1, 0, 0> { using L = PL<P110>; };
 template <> struct GroupT<2, 0, 0> { using L = PL<P220>; };
-template <int ROLE, int LOUT> __host__ __device__ constexpr int num_groups() { return LOUT == 0 ? 1 : (ROLE == 0 ? 1 : (ROLE == 1 ? 2 : 4)); }
-constexpr int kMaxAcc = 10;
+template <int ROLE, int LOUT> __host__ __device__ constexpr int num_groups() { return 1; }
+constexpr int kMaxAcc = 22;   // output components a thread accumulates: 3+1+3+3+5+5 (role 1), 5+5+3+5+3+1 (role 2)
 
 // ---- staging of one chunk of edges ----------------------------------------------------------------
 // eid: optional indirection (edge ids sorted by source, for the backward-x pass); gidx: row to gather per edge
@@ -455,10 +469,11 @@ __device__ __forceinline__ float warp_reduce8(float* v, int lane) {
   return v[0];
 }
 
-template <int ROLE, int LOUT, int G>
+template <int ROLE, int LOUT, int G, bool DX>
 __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
                                            const float* __restrict__ x, const float* __restrict__ w,
-                                           float* __restrict__ dw, const float* gv, int u, bool active, float* s_dY) {
+                                           float* __restrict__ dw, const float* gv, int u, bool active, float* s_dY,
+                                           float* __restrict__ dxo) {
   using L = typename GroupT<ROLE, LOUT, G>::L;
   constexpr int D1 = RoleT<ROLE, LOUT>::D1;
   const int xo = role_xoff<ROLE>(d) + u * D1;
@@ -473,8 +488,16 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
 #pragma unroll
       for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
       L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
-      L::bwde(rec + k * RoleT<ROLE, LOUT>::REC, xv, gv, wv, dwv, dY);
+      float dxv[D1];
+#pragma unroll
+      for (int a = 0; a < D1; ++a) dxv[a] = 0.f;
+      L::template bwde<DX>(rec + k * RoleT<ROLE, LOUT>::REC, xv, gv, wv, dwv, dY, dxv);
       L::store_w(d, dw + (size_t)s_e[k] * d.wn, u, dwv);
+      if constexpr (DX) {   // scatter to the source atom's row (RED.ADD; the row was zeroed by the launcher)
+        float* xr = dxo + (size_t)s_g[k] * d.xdim + xo;
+#pragma unroll
+        for (int a = 0; a < D1; ++a) atomicAdd(xr + a, dxv[a]);
+      }
     }
     if constexpr (LOUT == 0 && ROLE == 0) {
       // only path 000: no dependence on Y
@@ -485,12 +508,12 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
   }
 }
 
-template <int ROLE, int LOUT>
+template <int ROLE, int LOUT, bool DX>
 __global__ void __launch_bounds__(256)
 conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
                  const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w,
                  const float* __restrict__ gout, float inv_denom, float* __restrict__ dw, float* __restrict__ dYo,
-                 int accumulate) {
+                 int accumulate, float* __restrict__ dxo) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int NG = num_groups<ROLE, LOUT>();
   __shared__ __align__(16) float rec[TE * RT::REC];
@@ -516,10 +539,10 @@ conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const i
     __syncthreads();
     stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne);
     __syncthreads();
-    if (grp == 0) bwde_group<ROLE, LOUT, 0>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
-    else if (grp == 1) bwde_group<ROLE, LOUT, 1>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
-    else if (grp == 2) bwde_group<ROLE, LOUT, 2>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
-    else bwde_group<ROLE, LOUT, 3>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY);
+    if (grp == 0) bwde_group<ROLE, LOUT, 0, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
+    else if (grp == 1) bwde_group<ROLE, LOUT, 1, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
+    else if (grp == 2) bwde_group<ROLE, LOUT, 2, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
+    else bwde_group<ROLE, LOUT, 3, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
     if constexpr (!(LOUT == 0 && ROLE == 0)) {
       __syncthreads();
       for (int it = threadIdx.x; it < ne * 8; it += blockDim.x) {
@@ -557,14 +580,18 @@ static void launch_bwdx(const ConvDesc& d, int n_src, const int* rrowptr, const 
 template <int ROLE, int LOUT>
 static void launch_bwde(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
                         const float* w, const float* gout, float inv_denom, float* dw, float* dY, int accumulate,
-                        cudaStream_t st) {
+                        float* dx, cudaStream_t st) {
   const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
   if (mul == 0 || n_dst == 0) return;
   const int mulpad = round_up(mul, 32);
   const int threads = mulpad * num_groups<ROLE, LOUT>();
   const size_t sm = (size_t)(threads / 32) * TE * 8 * sizeof(float);
-  conv_bwde_kernel<ROLE, LOUT><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
-                                                            accumulate);
+  if (dx)
+    conv_bwde_kernel<ROLE, LOUT, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
+                                                                    accumulate, dx);
+  else
+    conv_bwde_kernel<ROLE, LOUT, false><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
+                                                                     accumulate, nullptr);
 }
 
 static bool desc_ok(const ConvDesc& d) {
@@ -603,25 +630,34 @@ int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid,
   return check_launch("conv_bwd_x", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
 }
 
-int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x, const float* Y,
-                  const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
-                  cudaStream_t st) {
+// d weight, d edge_attr and (dx != nullptr) d x[src] in one pass over the destination-sorted edges: the gradient
+// rows of the source atoms are accumulated with RED.ADD, so the per-edge weights are read once for all three.
+int conv_bwd_edge_x(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                    const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                    float* dx, cudaStream_t st) {
   B200_REQUIRE(desc_ok(d), "conv_bwd_edge: unsupported irreps");
   const float inv = 1.0f / denom;
+  if (dx) cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)n_src * d.xdim, st);
   // the three role kernels run back to back on one stream: the first may overwrite dY, the rest add
   int acc = accumulate;
   if (d.lout == 2) {
-    if (d.m0) { launch_bwde<0, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
-    if (d.m1) { launch_bwde<1, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
-    if (d.m2) { launch_bwde<2, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+    if (d.m0) { launch_bwde<0, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
+    if (d.m1) { launch_bwde<1, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
+    if (d.m2) { launch_bwde<2, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
   } else {
     // role 0 (path 000) does not touch dY
     if (!acc && !d.m1 && !d.m2) cudaMemsetAsync(dY, 0, sizeof(float) * 9 * (size_t)n_edges, st);
-    launch_bwde<0, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st);
-    if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
-    if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, st); acc = 1; }
+    launch_bwde<0, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st);
+    if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
+    if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
   }
   return check_launch("conv_bwd_edge", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
+}
+
+int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x, const float* Y,
+                  const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                  cudaStream_t st) {
+  return conv_bwd_edge_x(d, n_dst, 0, n_edges, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, nullptr, st);
 }
 
 }  // namespace b200

@@ -100,6 +100,7 @@ struct B200Model {
   std::vector<float> denom;  // host copies of {t}_convolution.denominator
   // optional per-category device timing (CUDA events on the compute stream)
   bool timing = false;
+  bool split_bwd_x = false;   // B200_SPLIT_BWD_X=1: d x[src] by the separate source-sorted kernel (deterministic sums)
   std::vector<cudaEvent_t> ev;
   std::vector<int> ev_cat;
   size_t ev_used = 0;
@@ -178,6 +179,7 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.si2 = make_linear(L.msg, L.gin);
     L.fused = fused_supported(L.conv, L.mlp) && getenv("B200_FUSED") && atoi(getenv("B200_FUSED")) != 0;   // opt-in
     m->layers.push_back(L);
+    m->split_bwd_x = getenv("B200_SPLIT_BWD_X") && atoi(getenv("B200_SPLIT_BWD_X")) != 0;
     const std::string s = std::to_string(t);
     m->expected[s + "_self_connection_intro.linear.weight"] = lin_numel(L.sc);
     m->expected[s + "_self_interaction_1.linear.weight"] = lin_numel(L.si1);
@@ -408,15 +410,16 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
                                            b.ddr, any_fused ? 1 : 0, st));
       any_fused = true;
     } else {
-      OP(CAT_CONV_BWD_EDGE, conv_bwd_edge(L.conv, N, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw, b.dY,
-                                          (any_fused || any_plain) ? 1 : 0, st));
+      // d weight, d Y and (t > 0) d x[src] in one pass: the source rows are accumulated with RED.ADD
+      OP(CAT_CONV_BWD_EDGE, conv_bwd_edge_x(L.conv, N, NA, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw,
+                                            b.dY, (any_fused || any_plain) ? 1 : 0, m->split_bwd_x ? nullptr : dxs, st));
       OP(CAT_MLP_BWD, radial_mlp_bwd(L.mlp, E, b.emb, W0, W1, W2, b.dw, b.demb, any_plain ? 1 : 0, st));
       any_plain = true;
     }
     if (t > 0) {
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
       OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
-      if (!L.fused)
+      if (!L.fused && m->split_bwd_x)
         OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
       OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));

@@ -26,6 +26,9 @@ int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, co
              const float* w, float denom, float* out, cudaStream_t st);
 int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst, const float* gout,
                const float* Y, const float* w, float denom, float* dx, cudaStream_t st);
+int conv_bwd_edge_x(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                    const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                    float* dx, cudaStream_t st);
 int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x,
                   const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
                   cudaStream_t st);

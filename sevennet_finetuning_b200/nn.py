@@ -161,10 +161,11 @@ class _ConvFn(torch.autograd.Function):
         gout = ops._f32(gout)
         rowptr = g['rowptr'][:g['n_dst'] + 1].contiguous()
         w = ops.radial_mlp_fwd(emb, W0, W1, W2)                       # recomputed, never saved
-        dw, dY = ops.conv_bwd_edge(muls, lout, rowptr, g['src'], x, Y, w, gout, d)
+        if ctx.needs_input_grad[0]:
+            dw, dY, dx = ops.conv_bwd(muls, lout, x.shape[0], rowptr, g['src'], x, Y, w, gout, d)
+        else:
+            (dw, dY), dx = ops.conv_bwd_edge(muls, lout, rowptr, g['src'], x, Y, w, gout, d), None
         dY[:, 0] = 0.0
-        dx = ops.conv_bwd_x(muls, lout, x.shape[0], g['rrowptr'], g['eid'], g['dst'], gout, Y, w, d) \
-            if ctx.needs_input_grad[0] else None
         demb = ops.radial_mlp_bwd(emb, W0, W1, W2, dw) if ctx.needs_input_grad[2] else None
         dW0 = dW1 = dW2 = None
         if any(ctx.needs_input_grad[3:6]):

@@ -186,6 +186,21 @@ def conv_bwd_edge(muls, lout, rowptr, src, x, Y, w, gout, denom, dY=None):
     return dw, dY
 
 
+def conv_bwd(muls, lout, n_src, rowptr, src, x, Y, w, gout, denom, dY=None):
+    """d weight, d edge_attr and d x[n_src] in one pass (b200_conv_bwd)."""
+    n = rowptr.shape[0] - 1
+    E = src.shape[0]
+    dw = torch.empty_like(w)
+    acc = dY is not None
+    if dY is None:
+        dY = torch.zeros(E, 9, dtype=torch.float32, device=x.device)
+    xdim = muls[0] + 3 * muls[1] + 5 * muls[2]
+    dx = torch.empty(n_src, xdim, dtype=torch.float32, device=x.device)
+    check(lib().b200_conv_bwd(*muls, lout, n, n_src, E, _p(rowptr), _p(src), _p(x), _p(Y), _p(w), _p(gout), float(denom),
+                              _p(dw), _p(dY), int(acc), _p(dx), _stream()), 'conv_bwd')
+    return dw, dY, dx
+
+
 def conv_bwd_x(muls, lout, n_src, rrowptr, eid, dst, gout, Y, w, denom):
     xdim = muls[0] + 3 * muls[1] + 5 * muls[2]
     dx = torch.empty(n_src, xdim, dtype=torch.float32, device=gout.device)

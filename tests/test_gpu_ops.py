@@ -184,6 +184,9 @@ def test_convolution_fwd_bwd(dev, muls, lout, name):
     rr, eid = ops.csr_transpose(n, s32)
     dx = ops.conv_bwd_x(muls, lout, n, rr, eid, d32, g32, Y32, w32, denom)
     assert _rel(dx, x.grad) < 2e-5, name
+    # one pass for all three gradients (d x accumulated with RED.ADD)
+    dw3, dY3, dx3 = ops.conv_bwd(muls, lout, n, rp, s32, x32, Y32, w32, g32, denom)
+    assert _rel(dw3, w.grad) < 2e-5 and _rel(dY3[:, 1:], Yr.grad[:, 1:]) < 2e-5 and _rel(dx3, x.grad) < 2e-5, name
 
 
 def test_convolution_empty_rows_and_long_rows(dev):
