@@ -265,18 +265,35 @@ def main():
     # dominant kernel category -> roofline (algorithmic bytes/flops per step: SURVEY 8d)
     # per-kernel figures are rank 0's (its own edges / atoms); the step figure is the whole job over N x peak
     Ek, Nk = (E, N) if par is None else (int(out['n_edges']), int(out['n_local']))
+    # SURVEY 8(d) byte model per category and step (fused model: per-edge weights never counted); the edge-gradient
+    # pass now also accumulates d x[src] (b200_conv_bwd), so it carries the whole backward figure
+    split = os.environ.get('B200_SPLIT_BWD_X', '0') not in ('', '0')
     conv_bytes = {'conv_fwd': 8292.0 * Ek + 43136.0 * Nk,
-                  'conv_bwd_edge': (16092.0 - 4 * 1920.0) * Ek + 43136.0 * Nk,  # x[src] read + weights; dOut read once per node
+                  'conv_bwd_edge': (16092.0 - (4 * 1920.0 if split else 0.0)) * Ek + 43136.0 * Nk,
                   'conv_bwd_x': 4 * 1920.0 * Ek}
     mlp_flops = {'radial_mlp_fwd': 2.0 * (29184 + 3 * 66048 + 18944) * Ek, 'radial_mlp_bwd': 2.0 * (29184 + 3 * 66048 + 18944) * Ek}
+    # HBM bytes the radial kernels must move in the un-fused layout: the per-edge weights [E, wn] written (fwd) / their
+    # gradient read (bwd) once, wn summed over the five layers = 3488
+    mlp_bytes = {'radial_mlp_fwd': 4.0 * 3488 * Ek, 'radial_mlp_bwd': 4.0 * 3488 * Ek}
     dom = max((k for k in cat_ms if k != 'halo_exchange'), key=cat_ms.get)
     if dom in mlp_flops:
         ach = mlp_flops[dom] / (cat_ms[dom] * 1e-3) / 1e12
-        roof = dict(kernel=dom, bound='tensor', achieved=ach, peak=pk['tf'], unit='TFLOP/s', frac=ach / pk['tf'], traffic=None)
+        roof = dict(kernel=dom, bound='tensor', achieved=ach, peak=pk['tf'], unit='TFLOP/s', frac=ach / pk['tf'], traffic=None,
+                    note='algorithmic fp32 flops (3xTF32 executes 2-3x as many tf32 flops; tf32 peak is half the bf16 figure)',
+                    hbm_side=dict(achieved=mlp_bytes[dom] / (cat_ms[dom] * 1e-3) / 1e9, peak=pk['hbm'], unit='GB/s',
+                                  frac=mlp_bytes[dom] / (cat_ms[dom] * 1e-3) / 1e9 / pk['hbm']))
     else:
         byt = conv_bytes.get(dom, 24384.0 * Ek + 86272.0 * Nk)
         ach = byt / (cat_ms[dom] * 1e-3) / 1e9
         roof = dict(kernel=dom, bound='hbm', achieved=ach, peak=pk['hbm'], unit='GB/s', frac=ach / pk['hbm'], traffic=None)
+    # measured DRAM traffic of the dominant category (sum over its launches of one step) from the committed ncu capture
+    try:
+        tr = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))
+        if world == 1 and tr.get('n_edges') == E and dom in tr.get('dram_bytes_per_step', {}):
+            roof['traffic'] = tr['dram_bytes_per_step'][dom]
+            roof['traffic_source'] = tr.get('source')
+    except Exception:
+        pass
     roof['peak_source'] = pk['src']
     roof['ms_per_step'] = cat_ms[dom]
     step_bytes = 24384.0 * E + 86272.0 * N

@@ -15,7 +15,9 @@
 
 namespace b200 {
 
-constexpr int TE = 32;  // edges staged per chunk
+// edges staged per chunk: the widest records (role 2, 400 B per edge, one warp per CTA) are staged 16 at a time so
+// that shared memory does not cap the resident CTAs below the 32-per-SM limit
+template <int ROLE> __host__ __device__ constexpr int te_of() { return ROLE == 2 ? 16 : 32; }
 constexpr float kInvSqrt3 = 0.5773502691896258f;
 constexpr float kInvSqrt5 = 0.4472135954999579f;
 
@@ -350,6 +352,7 @@ conv_fwd_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const in
                 const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w, float denom,
                 float* __restrict__ out) {
   using RT = RoleT<ROLE, LOUT>;
+  constexpr int TE = te_of<ROLE>();
   __shared__ __align__(16) float rec[TE * RT::REC];
   __shared__ int s_e[TE], s_g[TE];
   const int i = blockIdx.x;
@@ -405,6 +408,7 @@ conv_bwdx_kernel(ConvDesc d, int mulpad, const int* __restrict__ rrowptr, const 
   using RT = RoleT<ROLE, LOUT>;
   constexpr int D1 = RT::D1;
   constexpr int NG = num_groups<ROLE, LOUT>();
+  constexpr int TE = te_of<ROLE>();
   __shared__ __align__(16) float rec[TE * RT::REC];
   __shared__ int s_e[TE], s_g[TE];
   extern __shared__ float s_part[];  // [(NG-1)][mulpad][D1] partial sums of groups 1..NG-1
@@ -503,7 +507,7 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
       // only path 000: no dependence on Y
     } else {
       const float r = warp_reduce8(dY + 1, lane);
-      if ((lane & 3) == 0) s_dY[(warp * TE + k) * 8 + (lane >> 2)] = r;  // slot lane>>2 == component m
+      if ((lane & 3) == 0) s_dY[(warp * te_of<ROLE>() + k) * 8 + (lane >> 2)] = r;  // slot lane>>2 == component m
     }
   }
 }
@@ -516,6 +520,7 @@ conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const i
                  int accumulate, float* __restrict__ dxo) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int NG = num_groups<ROLE, LOUT>();
+  constexpr int TE = te_of<ROLE>();
   __shared__ __align__(16) float rec[TE * RT::REC];
   __shared__ int s_e[TE], s_g[TE];
   extern __shared__ float s_dY[];  // [nwarps][TE][8]
@@ -585,7 +590,7 @@ static void launch_bwde(const ConvDesc& d, int n_dst, const int* rowptr, const i
   if (mul == 0 || n_dst == 0) return;
   const int mulpad = round_up(mul, 32);
   const int threads = mulpad * num_groups<ROLE, LOUT>();
-  const size_t sm = (size_t)(threads / 32) * TE * 8 * sizeof(float);
+  const size_t sm = (size_t)(threads / 32) * te_of<ROLE>() * 8 * sizeof(float);
   if (dx)
     conv_bwde_kernel<ROLE, LOUT, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
                                                                     accumulate, dx);
