@@ -221,12 +221,17 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record()
+        evs = []
         for _ in range(steps):
             out = fn()
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            evs.append(ev)
         e1.record()
         barrier()
         wall = time.perf_counter() - t0
         ms = e0.elapsed_time(e1)
+        timed.per_step = [round((e0 if k == 0 else evs[k - 1]).elapsed_time(evs[k]), 3) for k in range(steps)]
         # host-synchronous pieces (edge count readback, D2H) sit between the events as well; use the larger
         t = torch.tensor([max(ms * 1e-3, wall if fn is step_e2e else ms * 1e-3)], device=dev, dtype=torch.float64)
         if world > 1:
@@ -248,6 +253,7 @@ def main():
     with ClockSampler(local) as cs:
         L.b200_model_set_timing(model._h, 1)
         t_res, out = timed(step_resident, a.steps)
+        per_step_res = list(timed.per_step)
         cat = (C.c_float * 9)()
         L.b200_model_get_timing(model._h, cat, 9)
         L.b200_model_set_timing(model._h, 0)
@@ -306,7 +312,7 @@ def main():
                 step_roofline=dict(bound='hbm', algorithmic_bytes=step_bytes, achieved=step_bytes / (step_ms * 1e-3) / 1e9,
                                    peak=pk['hbm'] * world, unit='GB/s',
                                    frac=step_bytes / (step_ms * 1e-3) / 1e9 / (pk['hbm'] * world)),
-                kernel_ms_per_step=cat_ms, clocks=clocks)
+                kernel_ms_per_step=cat_ms, ms_each_step=per_step_res, clocks=clocks)
     if rank == 0:
         if not a.no_cpu_baseline and world == 1:
             line['cpu_baseline'], _ = reference_cpu_time(a.cpu_atoms, 2, 1)

@@ -44,4 +44,19 @@ struct ConvDesc {
 
 inline int round_up(int a, int b) { return (a + b - 1) / b * b; }
 
+// The stream-ordered allocator returns freed memory to the driver at the next synchronisation unless the pool's
+// release threshold is raised; the operand packs (a few hundred KB, allocated and freed around every tensor-core
+// launch) would otherwise cost a driver allocation per call.  Once per device.
+inline void keep_async_pool() {
+  static bool done[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+    unsigned long long thr = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  }
+  done[dev] = true;
+}
+
 }  // namespace b200

@@ -778,6 +778,7 @@ int fused_radial(const EdgeParams& ep, const MlpDesc& m, long long E, const floa
 }
 
 static int make_pack(const FusedPlan& pl, const ConvDesc& d, const float* W2, cudaStream_t st, float** pack) {
+  keep_async_pool();
   if (cudaMallocAsync((void**)pack, (size_t)pl.nslab * 2 * F_APART, st) != cudaSuccess) {
     set_error("fused_conv: cudaMallocAsync of the operand pack failed");
     return B200_ERR_CUDA;

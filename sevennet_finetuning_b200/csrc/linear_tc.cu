@@ -268,6 +268,7 @@ int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float*
   B200_REQUIRE(build_lin_plan(d, transpose, pl, &pack_floats), "irreps_linear_tc: unsupported shape");
   if (n_nodes == 0) return B200_OK;
   float* pack;
+  keep_async_pool();
   if (cudaMallocAsync((void**)&pack, pack_floats * sizeof(float), st) != cudaSuccess) {
     set_error("irreps_linear_tc: cudaMallocAsync of the operand pack failed");
     return B200_ERR_CUDA;

@@ -612,6 +612,7 @@ struct Pack {
 static int with_pack(const MlpDesc& d, const float* W1, const float* W2, cudaStream_t st, Pack& p) {
   const int NT = (d.wn + TCN - 1) / TCN, NK = (d.wn + BK - 1) / BK;
   const size_t nf = (size_t)NT * 2 * OPB, nbk = (size_t)NK * 2 * BOPB, nw = (size_t)4 * W1B;
+  keep_async_pool();
   if (cudaMallocAsync((void**)&p.base, nf + nbk + nw, st) != cudaSuccess) {
     set_error("radial_mlp: cudaMallocAsync of the operand pack failed");
     return B200_ERR_CUDA;

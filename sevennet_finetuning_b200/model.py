@@ -118,12 +118,41 @@ class B200SevenNet:
         check(rc, 'model_compute')
         return energy, ae, force, virial
 
-    def calculate(self, pos, cell, pbc, types):
+    SORT_MIN_ATOMS = 4096
+
+    @staticmethod
+    def cell_order(pos, cell, cutoff):
+        """Permutation that puts the atoms in cell-list order (bins of about one cutoff in fractional coordinates):
+        neighbours of consecutive atoms overlap, so the x[src] gathers and the d x[src] RED.ADD scatter of the
+        convolution kernels stay in L2.  What LAMMPS' `atom_modify sort` does for the reference's pair styles."""
+        h = torch.as_tensor(np.asarray(cell, np.float64).reshape(3, 3), device=pos.device)
+        frac = torch.linalg.solve(h.T, pos.T).T
+        frac = frac - torch.floor(frac)
+        vol = abs(float(torch.linalg.det(h)))
+        nb = []
+        for k in range(3):
+            area = float(torch.linalg.norm(torch.linalg.cross(h[(k + 1) % 3], h[(k + 2) % 3])))
+            nb.append(max(1, int(vol / area / cutoff)))
+        c = [torch.clamp((frac[:, k] * nb[k]).long(), 0, nb[k] - 1) for k in range(3)]
+        return torch.argsort((c[0] * nb[1] + c[1]) * nb[2] + c[2], stable=True)
+
+    def calculate(self, pos, cell, pbc, types, sort_atoms=True):
         """One MD force call: radius graph + E/F/S.  pos float64 [N,3] (device), cell 3x3 (host),
         types int32 [N] (device).  stress = -virial/volume in the model's order [xx,yy,zz,xy,yz,zx]
-        (sevenn/nn/force_output.py:186-213)."""
+        (sevenn/nn/force_output.py:186-213).  Large systems are evaluated in cell-list atom order (`cell_order`);
+        per-atom results come back in the caller's order, `graph` is in the internal order and carries `perm`
+        (internal index -> caller's index)."""
+        perm = None
+        if sort_atoms and pos.shape[0] >= self.SORT_MIN_ATOMS:
+            perm = self.cell_order(pos, cell, self.config['cutoff'])
+            pos, types = pos[perm].contiguous(), types[perm].contiguous()
         g = ops.radius_graph(pos, cell, pbc, self.config['cutoff'])
         e, ae, f, vir = self.compute(types, g['rowptr'], g['src'], g['dst'], g['edge_vec'])
+        if perm is not None:
+            inv = torch.empty_like(perm)
+            inv[perm] = torch.arange(perm.shape[0], device=perm.device)
+            ae, f = ae[inv], f[inv]
+            g = dict(g, perm=perm)
         vol = abs(float(np.linalg.det(np.asarray(cell, np.float64).reshape(3, 3))))
         stress = -vir / vol if vol > 0 else None
         return dict(energy=e, atomic_energy=ae, forces=f, virial=vir, stress=stress, graph=g)

@@ -78,3 +78,29 @@ def test_full_size_properties(model):
     assert abs(e1 - e2) / len(pos) < 1e-6
     assert np.abs(o2['forces'].double().cpu().numpy() - f[perm]).max() < 2e-4
     assert o1['graph']['src'].shape[0] == o2['graph']['src'].shape[0]
+
+
+def test_cell_order_evaluation_matches_caller_order(model):
+    """large systems are evaluated in cell-list atom order; per-atom results come back in the caller's order"""
+    from sevennet_finetuning_b200.synthetic import SPECIES_INDEX, amorphous_cell
+    pos, cell, pbc, sym = amorphous_cell(6000, seed=5)
+    types = np.array([SPECIES_INDEX[s] for s in sym], np.int32)
+    dev = model.device
+    assert len(pos) >= model.SORT_MIN_ATOMS
+    args = (torch.tensor(pos, device=dev), cell, pbc, torch.tensor(types, device=dev))
+    a = model.calculate(*args, sort_atoms=True)
+    b = model.calculate(*args, sort_atoms=False)
+    assert 'perm' in a['graph'] and 'perm' not in b['graph']
+    perm = a['graph']['perm']
+    assert sorted(perm.tolist()) == list(range(len(pos)))
+    # same edge set: map the internal numbering back
+    ea = torch.stack([perm[a['graph']['dst'].long()], perm[a['graph']['src'].long()]]).cpu().numpy()
+    eb = torch.stack([b['graph']['dst'].long(), b['graph']['src'].long()]).cpu().numpy()
+    assert ea.shape == eb.shape
+    ka = np.sort(ea[0].astype(np.int64) * len(pos) + ea[1])
+    kb = np.sort(eb[0].astype(np.int64) * len(pos) + eb[1])
+    assert (ka == kb).all()
+    assert abs(float(a['energy']) - float(b['energy'])) / len(pos) <= 1e-6
+    assert float((a['atomic_energy'] - b['atomic_energy']).abs().max()) <= 1e-5
+    assert float((a['forces'] - b['forces']).abs().max()) <= 6e-5   # two fp32 summation orders, forces up to 10 eV/A
+    assert float((a['stress'] - b['stress']).abs().max()) <= 1e-4 * float(b['stress'].abs().max())
