@@ -122,16 +122,42 @@ __device__ __forceinline__ void hidden_mm(const float (*A)[TCN], const float* __
 
 // workers: emb tile -> embT, z1 = emb . W0 (K = nb, CUDA cores), h1 = c silu(z1 / sqrt(nb)) written as the
 // hi/lo operand [128 edges x 64] at h1 (hi) and h1 + OPB (lo).  emb / W0 in the reference layouts.
+// The emb values and this thread's W0 columns are requested first thing, so both round trips overlap.
 __device__ __forceinline__ void hidden1_operand(float (*embT)[TCN], uint8_t* h1, int nb, long long e0, int ne,
                                                 const float* __restrict__ emb, const float* __restrict__ W0) {
   const int ty = threadIdx.x & 31, tx = threadIdx.x >> 5;
-  for (int it = threadIdx.x; it < TCN * nb; it += TCW) {
-    const int m = it / nb, k = it % nb;
-    embT[k][m] = (m < ne) ? __ldg(emb + (e0 + m) * nb + k) : 0.f;
+  // element it = tid + 512 j of the [128 x nb] tile (nb <= 16: at most 4 per thread), coalesced
+  float ev[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int it = threadIdx.x + TCW * j;
+    ev[j] = (it < TCN * nb && it / nb < ne) ? __ldg(emb + e0 * nb + it) : 0.f;
+  }
+  constexpr int WPRE = 8;   // basis functions whose W0 rows are preloaded (SevenNet-0: all eight)
+  float4 wv[WPRE];
+#pragma unroll
+  for (int k = 0; k < WPRE; ++k)
+    wv[k] = k < nb ? __ldg(reinterpret_cast<const float4*>(W0 + k * TCH + 4 * tx)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int it = threadIdx.x + TCW * j;
+    if (it < TCN * nb) embT[it % nb][it / nb] = ev[j];
   }
   bar_sync(1, TCW);
   float acc[HR][4] = {};
-  hidden_mm(embT, W0, TCH, nb, ty, tx, acc);
+#pragma unroll
+  for (int k = 0; k < WPRE; ++k) {
+    if (k < nb) {
+      const float bv[4] = {wv[k].x, wv[k].y, wv[k].z, wv[k].w};
+#pragma unroll
+      for (int i = 0; i < HR; ++i) {
+        const float a = embT[k][ty + 32 * i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a, bv[j], acc[i][j]);
+      }
+    }
+  }
+  if (nb > WPRE) hidden_mm(embT + WPRE, W0 + WPRE * TCH, TCH, nb - WPRE, ty, tx, acc);
   const float s0 = 1.0f / sqrtf((float)nb);
 #pragma unroll
   for (int i = 0; i < HR; ++i) {
@@ -461,11 +487,12 @@ radial_mlp_bwd_tc_kernel(int nb, int wn, long long E, const float* __restrict__ 
       }
     };
     TCDBG(0, 0);
-    float4 pf0[2], pf1[2], pf2[2], pf3[2], pf4[2], pf5[2];
-    gload(0, pf0); gload(1, pf1); gload(2, pf2); gload(3, pf3); gload(4, pf4); gload(5, pf5);
     hidden1_operand(s.embT, opA, nb, e0, ne, emb, W0);
     fence_proxy_async();
     warp_arrive(&s.h1_ready);
+    // the first chunks of dw travel while the issuer runs the z2 product (about 4 k clocks until they are needed)
+    float4 pf0[2], pf1[2], pf2[2], pf3[2], pf4[2], pf5[2];
+    gload(0, pf0); gload(1, pf1); gload(2, pf2); gload(3, pf3); gload(4, pf4); gload(5, pf5);
     TCDBG(1, 0);
     mbar_wait(&s.z2_done, 0);
     TCDBG(2, 0);
