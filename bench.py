@@ -44,6 +44,9 @@ def peaks():
         return dict(hbm=6650.0, tf=1400.0, src='fallback')
 
 
+_JSON_OUT = None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -207,7 +210,13 @@ def main():
     dev = torch.device('cuda', local)
     if world > 1:
         if os.environ.get('NCCL_DEBUG', 'VERSION').upper() == 'VERSION':
-            os.environ['NCCL_DEBUG'] = 'WARN'   # keep stdout to the one JSON line (NCCL prints its version banner there)
+            os.environ['NCCL_DEBUG'] = 'WARN'
+        # NCCL writes its version banner straight to file descriptor 1: keep stdout to the one JSON line by pointing
+        # fd 1 at stderr for the rest of the run and printing the line through a duplicate of the original stdout
+        global _JSON_OUT
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), 'w')
+        os.dup2(2, 1)
         dist.init_process_group('nccl', device_id=dev)
     L = _lib.lib()
     model = B200SevenNet(state_dict=load_weights(), device=dev)
@@ -337,7 +346,7 @@ def main():
     if rank == 0:
         if not a.no_cpu_baseline and world == 1:
             line['cpu_baseline'], _ = reference_cpu_time(a.cpu_atoms, 2, 1)
-        print(json.dumps(line))
+        print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

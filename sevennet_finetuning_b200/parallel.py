@@ -203,6 +203,12 @@ class ParallelSevenNet:
         (``local_ids`` = their global indices)."""
         from . import ops
         cutoff = self.model.config['cutoff']
+        # cell-list atom order (as in B200SevenNet.calculate): local and ghost rows of a brick follow it, so the
+        # gathers and the RED scatter of the convolution kernels stay L2-local; local_ids are mapped back below
+        perm = None
+        if pos.shape[0] >= self.model.SORT_MIN_ATOMS:
+            perm = self.model.cell_order(pos, cell, cutoff)
+            pos, types = pos[perm].contiguous(), types[perm].contiguous()
         plan = HaloPlan(pos, cell, pbc, cutoff, self.grid, self.rank, self.comm).connect()
         self.last_plan = plan
         nl, ng = plan.n_local, plan.n_ghost
@@ -215,5 +221,6 @@ class ParallelSevenNet:
         tot = torch.cat([e, vir])
         self.comm.all_reduce_sum(tot)
         vol = abs(float(np.linalg.det(np.asarray(cell, np.float64).reshape(3, 3))))
+        local_ids = plan.local_ids if perm is None else perm[plan.local_ids.long()].to(plan.local_ids.dtype)
         return dict(energy=tot[:1], virial=tot[1:], stress=-tot[1:] / vol if vol > 0 else None,
-                    atomic_energy=ae, forces=f[:nl], local_ids=plan.local_ids, n_local=nl, n_ghost=ng, n_edges=e_loc)
+                    atomic_energy=ae, forces=f[:nl], local_ids=local_ids, n_local=nl, n_ghost=ng, n_edges=e_loc)
