@@ -104,3 +104,70 @@ def test_cell_order_evaluation_matches_caller_order(model):
     assert float((a['atomic_energy'] - b['atomic_energy']).abs().max()) <= 1e-5
     assert float((a['forces'] - b['forces']).abs().max()) <= 6e-5   # two fp32 summation orders, forces up to 10 eV/A
     assert float((a['stress'] - b['stress']).abs().max()) <= 1e-4 * float(b['stress'].abs().max())
+
+
+def _oracle_efs(weights, pos, cell, pbc, types):
+    """float64 oracle (test infrastructure): graph by the numpy restatement, model by oracle/refmodel.py"""
+    from oracle.graph import radius_graph
+    from oracle.refmodel import build_model
+    ei, S, D = radius_graph(pos, cell, pbc, 5.0)
+    torch.set_default_dtype(torch.float64)
+    try:
+        m = build_model(dict(shift=weights['rescale_atomic_energy.shift'].tolist(),
+                             scale=weights['rescale_atomic_energy.scale'].tolist(),
+                             conv_denominator=float(weights['0_convolution.denominator'][0])))
+        m.load_state_dict({k: torch.tensor(v) for k, v in weights.items()})
+        m = m.double().eval()
+        m.set_is_batch_data(False)
+        vol = abs(np.linalg.det(cell))
+        o = m({'x': torch.tensor(types, dtype=torch.long), 'edge_index': torch.tensor(ei),
+               'edge_vec': torch.tensor(D, dtype=torch.float64).requires_grad_(True), 'num_atoms': torch.tensor(len(pos)),
+               'cell_volume': torch.tensor(vol if vol > 0 else 1.0), 'batch': torch.zeros(0, dtype=torch.long)})
+        return ei, float(o['inferred_total_energy'].detach()), o['inferred_force'].detach().numpy(), o['atomic_energy'].detach().numpy().ravel()
+    finally:
+        torch.set_default_dtype(torch.float32)
+
+
+def test_cell_smaller_than_cutoff_self_images(model, weights):
+    """edge cases the reference's graph definition allows (dataload.py:36-47): a triclinic 2-atom cell shorter than
+    the cutoff, so atoms are neighbours of their own periodic images and of several images of each other"""
+    rng = np.random.default_rng(7)
+    cell = np.array([[3.3, 0.0, 0.0], [0.4, 3.1, 0.0], [-0.3, 0.5, 3.6]])
+    pos = np.array([[0.1, 0.2, 0.0], [1.7, 1.5, 1.9]]) + rng.normal(scale=0.05, size=(2, 3))
+    types = np.array([13, 7], np.int64)
+    ei, e64, f64, ae64 = _oracle_efs(weights, pos, cell, [True] * 3, types)
+    assert (ei[0] == ei[1]).any()                       # self-image edges are present
+    dev = model.device
+    out = model.calculate(torch.tensor(pos, device=dev), cell, [True] * 3, torch.tensor(types, dtype=torch.int32, device=dev))
+    assert (out['graph']['dst'].cpu().numpy() == ei[0]).all() and (out['graph']['src'].cpu().numpy() == ei[1]).all()
+    assert abs(float(out['energy']) - e64) / 2 <= 1e-6
+    assert np.abs(out['forces'].cpu().numpy() - f64).max() <= 1e-5
+    assert np.abs(out['atomic_energy'].cpu().numpy().ravel() - ae64).max() <= 1e-5
+
+
+def test_open_cluster_with_isolated_atom(model, weights):
+    """no periodicity, one atom without any neighbour: its row is empty in every CSR, its force is exactly zero and its
+    energy is the species shift plus the network's value for a bare atom"""
+    rng = np.random.default_rng(8)
+    pos = np.concatenate([rng.uniform(0, 6.0, size=(14, 3)), [[40.0, 40.0, 40.0]]])
+    # keep a physical minimum distance
+    for _ in range(50):
+        d = np.linalg.norm(pos[:, None] - pos[None], axis=-1) + np.eye(len(pos)) * 9
+        i, j = np.unravel_index(d.argmin(), d.shape)
+        if d[i, j] > 1.6:
+            break
+        pos[j] += (pos[j] - pos[i]) / d[i, j] * 0.8
+    cell = np.eye(3) * 100.0
+    from sevennet_finetuning_b200.synthetic import SPECIES_INDEX
+    types = np.array([SPECIES_INDEX['Si'], SPECIES_INDEX['O']])[rng.integers(0, 2, size=len(pos))]
+    ei, e64, f64, ae64 = _oracle_efs(weights, pos, cell, [False] * 3, types)
+    assert not (ei == len(pos) - 1).any()
+    dev = model.device
+    out = model.calculate(torch.tensor(pos, device=dev), cell, [False] * 3, torch.tensor(types, dtype=torch.int32, device=dev))
+    assert out['graph']['src'].shape[0] == ei.shape[1]
+    # fp32 round-off scales with the size of the per-atom terms (a compressed random cluster has some of tens of eV)
+    assert abs(float(out['energy']) - e64) / len(pos) <= 1e-6 * max(1.0, float(np.abs(ae64).max()) / 5.0)
+    f = out['forces'].cpu().numpy()
+    assert np.abs(f - f64).max() <= 1e-5 * max(1.0, float(np.abs(f64).max()) / 5.0)
+    assert (f[-1] == 0).all()
+    assert np.abs(out['atomic_energy'].cpu().numpy().ravel() - ae64).max() <= 1e-5
