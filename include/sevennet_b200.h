@@ -132,6 +132,10 @@ int b200_irreps_linear_wgrad(const LinDesc* d, int n_nodes, const float* x, cons
 /* in [n, ns+ng+3*m1+5*m2] = [scalars | gates | 1e | 2e], ng = m1+m2; out [n, ns+3*m1+5*m2] */
 int b200_gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, void* stream);
 int b200_gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* d_out, float* d_in, void* stream);
+/* second-order pass (the reverse of b200_gate_bwd; sevenn/nn/force_output.py:165-170 create_graph=self.training makes
+ * the fine-tuning loss differentiate the forces): a = dL/d(d_in) [n, in_dim] -> dL/d in (dx) and dL/d(d_out) (dg) */
+int b200_gate_bwd2(int ns, int m1, int m2, int n_nodes, const float* in, const float* d_out, const float* a, float* dx,
+                   float* dg, void* stream);
 
 /* ---- node embedding: sevenn/nn/node_embedding.py:39-48 + nn/linear.py:37-44 (one-hot . W / sqrt(n_species)) */
 int b200_embed_fwd(int n_nodes, int n_species, int dim, const int32_t* types, const float* W, float* x, void* stream);

@@ -66,6 +66,7 @@ SIGNATURES = {
     'b200_irreps_linear_wgrad': (_i, [_P(LinDesc), _i, _vp, _vp, _vp, _i, _vp]),
     'b200_gate_fwd': (_i, [_i, _i, _i, _i, _vp, _vp, _vp]),
     'b200_gate_bwd': (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    'b200_gate_bwd2': (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_embed_fwd': (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     'b200_rescale_fwd': (_i, [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     'b200_colsum': (_i, [_i, _i, _vp, _vp, _vp]),

@@ -117,6 +117,11 @@ int b200_gate_fwd(int ns, int m1, int m2, int n, const float* in, float* out, vo
 int b200_gate_bwd(int ns, int m1, int m2, int n, const float* in, const float* dout, float* din, void* stream) {
   return gate_bwd(ns, m1, m2, n, in, dout, din, ST(stream));
 }
+int b200_gate_bwd2(int ns, int m1, int m2, int n, const float* in, const float* dout, const float* a, float* dx, float* dg,
+                   void* stream) {
+  B200_REQUIRE(n == 0 || (in && dout && a && dx && dg), "gate_bwd2: null argument");
+  return gate_bwd2(ns, m1, m2, n, in, dout, a, dx, dg, ST(stream));
+}
 int b200_embed_fwd(int n, int nsp, int dim, const int32_t* types, const float* W, float* x, void* stream) {
   return embed_fwd(n, nsp, dim, types, W, x, ST(stream));
 }

@@ -56,6 +56,71 @@ __global__ void gate_bwd_kernel(int ns, int m1, int m2, long long n_nodes, const
   }
 }
 
+// Second-order pass of the gate (reverse of gate_bwd; force-matching fine-tuning differentiates the forces, which are
+// themselves a reverse pass: sevenn/nn/force_output.py:165-170 create_graph=self.training).  With phi = c*silu:
+//   gate_bwd:  din_s = phi'(s) g_s,  din_t[u] = phi'(t_u) sum_m v[u,m] g_v[u,m],  din_v[u,m] = phi(t_u) g_v[u,m]
+// and a = d L / d din, this kernel returns d L / d in (dx) and d L / d g (dg).
+__device__ __forceinline__ void silu_vdd(float z, float& v, float& d, float& dd) {
+  const float s = 1.0f / (1.0f + expf(-z));
+  v = kSilu2Mom * z * s;
+  d = kSilu2Mom * s * (1.0f + z * (1.0f - s));
+  dd = kSilu2Mom * s * (1.0f - s) * (2.0f + z * (1.0f - 2.0f * s));
+}
+
+__global__ void gate_bwd2_dx_kernel(int ns, int m1, int m2, long long n_nodes, const float* __restrict__ in,
+                                    const float* __restrict__ g_, const float* __restrict__ a_, float* __restrict__ dx) {
+  const int ng = m1 + m2, din = ns + ng + 3 * m1 + 5 * m2, dout = ns + 3 * m1 + 5 * m2;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= n_nodes * din) return;
+  const long long n = idx / din;
+  const int c = (int)(idx % din);
+  const float* r = in + n * din;
+  const float* a = a_ + n * din;
+  const float* g = g_ + n * dout;
+  float v, d, dd;
+  if (c < ns) {
+    silu_vdd(r[c], v, d, dd);
+    dx[idx] = a[c] * dd * g[c];
+  } else if (c < ns + ng) {
+    const int u = c - ns;
+    const int D = u < m1 ? 3 : 5;
+    const int off = u < m1 ? u * 3 : 3 * m1 + (u - m1) * 5;
+    float svg = 0.f, sag = 0.f;
+    for (int m = 0; m < D; ++m) {
+      svg = fmaf(g[ns + off + m], r[ns + ng + off + m], svg);
+      sag = fmaf(g[ns + off + m], a[ns + ng + off + m], sag);
+    }
+    silu_vdd(r[c], v, d, dd);
+    dx[idx] = a[c] * dd * svg + d * sag;
+  } else {
+    const int off = c - ns - ng;
+    const int u = off < 3 * m1 ? off / 3 : m1 + (off - 3 * m1) / 5;
+    silu_vdd(r[ns + u], v, d, dd);
+    dx[idx] = a[ns + u] * d * g[ns + off];
+  }
+}
+
+__global__ void gate_bwd2_dg_kernel(int ns, int m1, int m2, long long n_nodes, const float* __restrict__ in,
+                                    const float* __restrict__ a_, float* __restrict__ dg) {
+  const int ng = m1 + m2, din = ns + ng + 3 * m1 + 5 * m2, dout = ns + 3 * m1 + 5 * m2;
+  const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (idx >= n_nodes * dout) return;
+  const long long n = idx / dout;
+  const int c = (int)(idx % dout);
+  const float* r = in + n * din;
+  const float* a = a_ + n * din;
+  float v, d, dd;
+  if (c < ns) {
+    silu_vdd(r[c], v, d, dd);
+    dg[idx] = a[c] * d;
+  } else {
+    const int off = c - ns;
+    const int u = off < 3 * m1 ? off / 3 : m1 + (off - 3 * m1) / 5;
+    silu_vdd(r[ns + u], v, d, dd);
+    dg[idx] = a[ns + u] * d * r[ns + ng + off] + a[ns + ng + off] * v;
+  }
+}
+
 __global__ void embed_fwd_kernel(long long n_nodes, int n_species, int dim, const int* __restrict__ types,
                                  const float* __restrict__ W, float* __restrict__ x) {
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -102,6 +167,15 @@ int gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* 
   const long long tot = (long long)n_nodes * (ns + m1 + m2 + 3 * m1 + 5 * m2);
   gate_bwd_kernel<<<blocks_for(tot, 256), 256, 0, st>>>(ns, m1, m2, n_nodes, in, dout, din);
   return check_launch("gate_bwd");
+}
+int gate_bwd2(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, const float* a, float* dx,
+              float* dg, cudaStream_t st) {
+  if (n_nodes == 0) return B200_OK;
+  const long long tin = (long long)n_nodes * (ns + m1 + m2 + 3 * m1 + 5 * m2);
+  const long long tout = (long long)n_nodes * (ns + 3 * m1 + 5 * m2);
+  gate_bwd2_dx_kernel<<<blocks_for(tin, 256), 256, 0, st>>>(ns, m1, m2, n_nodes, in, dout, a, dx);
+  gate_bwd2_dg_kernel<<<blocks_for(tout, 256), 256, 0, st>>>(ns, m1, m2, n_nodes, in, a, dg);
+  return check_launch("gate_bwd2");
 }
 int embed_fwd(int n_nodes, int n_species, int dim, const int* types, const float* W, float* x, cudaStream_t st) {
   if (n_nodes == 0) return B200_OK;

@@ -54,6 +54,8 @@ int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const flo
 
 int gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, cudaStream_t st);
 int gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, float* din, cudaStream_t st);
+int gate_bwd2(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, const float* a, float* dx,
+              float* dg, cudaStream_t st);
 int embed_fwd(int n_nodes, int n_species, int dim, const int* types, const float* W, float* x, cudaStream_t st);
 int rescale_fwd(int n_nodes, const int* types, const float* scaled, const float* scale, const float* shift,
                 int species_wise, float* out, cudaStream_t st);

@@ -8,10 +8,12 @@ unchanged.  Every forward and every first-order backward is a kernel of libseven
 ``torch.autograd.Function``; per-edge intermediates (weights, messages) are recomputed in backward instead of
 saved.  There is no CPU path: a CPU tensor raises.
 
-Scope of autograd: first order, including parameter gradients (energy-type losses train exactly).  Second order
-(``create_graph=True`` through the force output, ``sevenn/nn/force_output.py:168``, needed by force-matching
-losses) is not implemented in the kernels yet: ``ForceStressOutputFromEdge`` raises in training mode instead of
-silently returning non-differentiable forces.
+Scope of autograd.  In ``eval()`` mode: first order, per-edge intermediates recomputed (the MD / calculator flavour).
+In ``train()`` mode the modules switch to the Functions of ``higher_order.py``, which stay differentiable through their
+own backward pass: ``ForceStressOutputFromEdge`` then calls ``autograd.grad(..., create_graph=True)`` exactly like the
+reference (``sevenn/nn/force_output.py:165-170``) and a loss on forces / stress can be back-propagated to the parameters
+(``sevenn/train/trainer.py:173-186``).  The only non-kernel arithmetic on that path is the 17-values-per-edge spherical
+harmonics / Bessel / cutoff evaluation, whose second derivatives are taken by autograd over elementwise tensor ops.
 """
 import math
 from collections import OrderedDict
@@ -19,6 +21,7 @@ from collections import OrderedDict
 import torch
 import torch.nn as nn
 
+from . import higher_order as ho
 from . import ops
 from ._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, EdgeParams
 
@@ -48,7 +51,7 @@ def _graph_of(data):
         rowptr[1:] = torch.cumsum(torch.bincount(dst64, minlength=n_src), 0).to(torch.int32)
     rrowptr, eid = ops.csr_transpose(n_src, src)
     g = dict(key=(ei.data_ptr(), ei.shape[1]), perm=perm, dst=dst, src=src, rowptr=rowptr, rrowptr=rrowptr, eid=eid,
-             n_dst=n, n_src=n_src)
+             n_dst=n, n_src=n_src, rowptr_dst=rowptr[:n + 1].contiguous())
     data['_b200_graph'] = g
     return g
 
@@ -89,6 +92,26 @@ def _cutoff_torch(p, r):
         return torch.where(r < p.r_on, torch.ones_like(r), f)
     x, pp = r / p.r_cut, p.poly_p
     return 1 - (pp + 1) * (pp + 2) / 2 * x ** pp + pp * (pp + 2) * x ** (pp + 1) - pp * (pp + 1) / 2 * x ** (pp + 2)
+
+
+def _second_order(module):
+    """train() mode with grad enabled: the forces must stay differentiable (force_output.py:168 create_graph=self.training)."""
+    return module.training and torch.is_grad_enabled()
+
+
+def _edge_embed_tensor_ops(vec, coeffs, p):
+    """EdgeEmbedding.forward (edge_embedding.py:220-230) with elementwise tensor ops, same formulas and component order
+    as ``csrc/edge.cu``; used in train() mode only, where autograd must differentiate it twice."""
+    r = torch.sqrt((vec * vec).sum(-1))
+    u = vec / r.clamp_min(1e-12).unsqueeze(-1) if p.normalize_sph else vec
+    ux, uy, uz = u.unbind(-1)
+    s3, s5 = math.sqrt(3.0), math.sqrt(5.0)
+    Y = torch.stack([torch.ones_like(ux), s3 * ux, s3 * uy, s3 * uz, s5 * s3 * ux * uz, s5 * s3 * ux * uy,
+                     s5 * (uy * uy - 0.5 * (ux * ux + uz * uz)), s5 * s3 * uy * uz,
+                     s5 * 0.5 * s3 * (uz * uz - ux * ux)], dim=-1)
+    rr = r.unsqueeze(-1)
+    emb = (2.0 / p.r_cut) * torch.sin(coeffs * rr) / rr * _cutoff_torch(p, rr)
+    return r, Y, emb
 
 
 class _LinearFn(torch.autograd.Function):
@@ -242,7 +265,13 @@ class EdgeEmbedding(nn.Module):
         return EdgeParams(b.num_basis, B200_CUTOFF_POLY, int(self.spherical.normalize), float(c.cutoff_length), 0.0, float(c.p))
 
     def forward(self, data):
-        ln, Y, emb = _EdgeEmbedFn.apply(data['edge_vec'], self.basis_function.coeffs, self._params())
+        if _second_order(self):
+            vec = data['edge_vec']
+            if not vec.is_cuda:
+                raise RuntimeError('sevennet_b200: CPU tensor passed to a CUDA-only module')
+            ln, Y, emb = _edge_embed_tensor_ops(vec.to(torch.float32), self.basis_function.coeffs, self._params())
+        else:
+            ln, Y, emb = _EdgeEmbedFn.apply(data['edge_vec'], self.basis_function.coeffs, self._params())
         data['edge_length'], data['edge_attr'], data['edge_embedding'] = ln, Y, emb
         return data
 
@@ -291,9 +320,11 @@ class IrrepsLinear(nn.Module):
         if self.is_embed and 'atom_type' in data:
             # one-hot input: a row gather of W / sqrt(n_species) instead of a dense product with 89x wasted work
             nsp, dim = ops.muls_of(self.irreps_in)[0], ops.muls_of(self.irreps_out)[0]
-            data[self.key_output] = _EmbedFn.apply(data['atom_type'], self.linear.weight, nsp, dim)
+            fn = ho.EmbedF if _second_order(self) else _EmbedFn
+            data[self.key_output] = fn.apply(data['atom_type'], self.linear.weight, nsp, dim)
         else:
-            data[self.key_output] = _LinearFn.apply(x, self.linear.weight, self.desc, self.numel)
+            fn = ho.LinF if _second_order(self) else _LinearFn
+            data[self.key_output] = fn.apply(x, self.linear.weight, self.desc, self.numel)
         return data
 
 
@@ -307,7 +338,8 @@ class SelfConnectionLinearIntro(nn.Module):
         self.linear = IrrepsLinear._Holder(self.numel)
 
     def forward(self, data):
-        data['self_cont_tmp'] = _LinearFn.apply(data[self.key_x], self.linear.weight, self.desc, self.numel)
+        fn = ho.LinF if _second_order(self) else _LinearFn
+        data['self_cont_tmp'] = fn.apply(data[self.key_x], self.linear.weight, self.desc, self.numel)
         return data
 
 
@@ -360,6 +392,7 @@ class IrrepsConvolution(nn.Module):
             data_key_x, data_key_filter, data_key_weight_input, data_key_edge_idx)
         self.is_parallel = is_parallel
         self._comm_size = self.muls[0] + 3 * self.muls[1] + 5 * self.muls[2]   # convolution.py:102
+        self._mlp_descs = None
 
     def forward(self, data):
         g = _graph_of(data)
@@ -370,6 +403,17 @@ class IrrepsConvolution(nn.Module):
         if g['perm'] is not None:
             Y, emb = Y.index_select(0, g['perm']), emb.index_select(0, g['perm'])
         nn_ = self.weight_nn
+        if _second_order(self):
+            hs = [nn_.layer0.weight.shape[0], nn_.layer0.weight.shape[1], nn_.layer1.weight.shape[1], self.weight_numel]
+            if self._mlp_descs is None:
+                self._mlp_descs = [ops.make_lin_desc(f'{a}x0e', f'{b}x0e') for a, b in zip(hs[:-1], hs[1:])]
+            w = ho.radial_mlp(emb, nn_.layer0.weight, nn_.layer1.weight, nn_.layer2.weight, self._mlp_descs)
+            if self.denominator.requires_grad:   # train_denominator: keep 1/denominator in the graph
+                out = ho.ConvF.apply(x, Y, w, g, self.muls, self.lout, 1.0) / self.denominator
+            else:
+                out = ho.ConvF.apply(x, Y, w, g, self.muls, self.lout, float(self.denominator))
+            data[self.key_x] = out
+            return data
         out = _ConvFn.apply(x, Y, emb, nn_.layer0.weight, nn_.layer1.weight, nn_.layer2.weight, self.denominator, g,
                             self.muls, self.lout)
         data[self.key_x] = out   # rows of the local atoms only (convolution.py:119-121)
@@ -391,7 +435,8 @@ class EquivariantGate(nn.Module):
         return '+'.join(parts)
 
     def forward(self, data):
-        data[self.key_x] = _GateFn.apply(data[self.key_x], *self.muls)
+        fn = ho.GateF if _second_order(self) else _GateFn
+        data[self.key_x] = fn.apply(data[self.key_x], *self.muls)
         return data
 
 
@@ -457,13 +502,9 @@ class ForceStressOutputFromEdge(nn.Module):
         self._is_batch_data = True
 
     def forward(self, data):
-        if self.training and torch.is_grad_enabled():
-            raise NotImplementedError(
-                'sevennet_b200: force output with create_graph=True (force/stress-matching loss) needs the second-order '
-                'kernels, which are not built yet; train on the energy or call .eval() for inference')
         energy = data[self.key_energy]
         rij = data[self.key_edge]
-        (fij,) = torch.autograd.grad([energy.sum()], [rij], create_graph=False, allow_unused=True)
+        (fij,) = torch.autograd.grad([energy.sum()], [rij], create_graph=_second_order(self), allow_unused=True)
         g = _graph_of(data)
         n = g['n_src']
         if fij is None:

@@ -303,3 +303,11 @@ def edge_embed_bwd_r(params, vec, dY, dr):
     dvec = torch.empty(E, 3, dtype=torch.float32, device=vec.device)
     check(lib().b200_edge_embed_bwd_r(C.byref(params), E, _p(vec), _p(dY), _p(dr), _p(dvec), _stream()), 'edge_embed_bwd_r')
     return dvec
+
+
+def gate_bwd2(ns, m1, m2, x, gout, a):
+    """Second-order pass of the gate: a = dL/d(gate_bwd output) -> (dL/dx, dL/d gout)."""
+    dx = torch.empty_like(x)
+    dg = torch.empty_like(gout)
+    check(lib().b200_gate_bwd2(ns, m1, m2, x.shape[0], _p(x), _p(gout), _p(a), _p(dx), _p(dg), _stream()), 'gate_bwd2')
+    return dx, dg

@@ -109,11 +109,216 @@ def test_parameter_gradients_of_energy(twin, gold, weights):
     twin.eval()
 
 
-def test_force_output_refuses_second_order(twin, gold):
-    g = gold('si216.npz')
+def _finetune_loss(out, lab, n):
+    """Huber(delta=0.01) on E/atom, forces, stress [kbar] with the shipped fine-tuning weights
+    (example_inputs/fine_tuning/FT_w_reEWC/input_full.yaml:41-56; sevenn/train/loss.py:96-214,268-292)."""
+    hub = torch.nn.HuberLoss(delta=0.01)
+    le = hub(out['inferred_total_energy'].reshape(-1) / n, lab['e'].reshape(-1) / n)
+    lf = hub(out['inferred_force'].reshape(-1), lab['f'].reshape(-1))
+    ls = hub(out['inferred_stress'].reshape(-1) * 1602.1766208, lab['s'].reshape(-1) * 1602.1766208)
+    return le + 1.0 * lf + 0.01 * ls
+
+
+def test_parameter_gradients_of_force_stress_loss(twin, gold, weights):
+    """The fine-tuning gradient: d L(E, F, S) / d theta with F = -dE/dr taken with create_graph=True
+    (sevenn/nn/force_output.py:165-170, sevenn/train/trainer.py:173-186) - a reverse pass through the reverse pass of
+    every kernel - against double-precision autograd through the oracle model."""
+    g = gold('hfo2_96.npz')
+    dev = torch.device('cuda:0')
+    n = len(g['pos'])
+    rng = np.random.default_rng(5)
+    lab64 = {'e': torch.tensor(float(g['o64_energy']) + 0.3, dtype=torch.float64), 'f': torch.tensor(g['o64_force'] + rng.normal(0, 0.05, (n, 3))),
+             's': torch.tensor(g['o64_stress'].reshape(-1) + rng.normal(0, 1e-3, 6))}
     twin.train()
     twin.set_is_batch_data(False)
-    data, _, _ = _data(g, torch.device('cuda:0'))
-    with pytest.raises(NotImplementedError):
-        twin(data)
+    for p in twin.parameters():   # every parameter, including shift / scale / conv denominators
+        p.requires_grad_(True)
+        p.grad = None
+    data, ei, D = _data(g, dev)
+    out = twin(data)
+    assert out['inferred_force'].requires_grad          # the forces stay in the graph in train() mode
+    lab32 = {k: v.to(dev, torch.float32) for k, v in lab64.items()}
+    loss = _finetune_loss(out, lab32, n)
+    loss.backward()
+    torch.set_default_dtype(torch.float64)
+    try:
+        ref = _oracle(weights)
+        ref.train()
+        ref.set_is_batch_data(False)
+        for p in ref.parameters():
+            p.requires_grad_(True)
+        d = {'x': torch.tensor(g['types']), 'edge_index': torch.tensor(ei),
+             'edge_vec': torch.tensor(D, dtype=torch.float64).requires_grad_(True), 'num_atoms': torch.tensor(n),
+             'cell_volume': torch.tensor(abs(np.linalg.det(g['cell']))), 'batch': torch.zeros(0, dtype=torch.long)}
+        o = ref(d)
+        lref = _finetune_loss(o, lab64, n)
+        lref.backward()
+    finally:
+        torch.set_default_dtype(torch.float32)
+    assert abs(float(loss) - float(lref)) <= 1e-5 * abs(float(lref))
+    refg = dict(ref.named_parameters())
+    worst = 0.0
+    for k, p in twin.named_parameters():
+        if not p.requires_grad:
+            continue
+        assert p.grad is not None, k
+        a, b = p.grad.double().cpu().reshape(-1), refg[k].grad.reshape(-1)
+        rel = float((a - b).abs().max() / max(float(b.abs().max()), 1e-12))
+        worst = max(worst, rel)
+        assert rel < 1e-3, (k, rel)
+    print('worst relative fine-tuning-gradient error', worst)
     twin.eval()
+
+
+@pytest.mark.parametrize('muls,lout', [((8, 0, 0), 2), ((8, 4, 4), 2), ((8, 4, 4), 0)])
+def test_convolution_family_second_order(muls, lout):
+    """ConvF / ConvB (higher_order.py): gradient of a functional of the first-order gradients, against the oracle's
+    tensor product + scatter in float64."""
+    from oracle.refnn import TensorProductUVU, message_gather
+    from sevennet_finetuning_b200 import higher_order as ho, ops
+    dev = torch.device('cuda:0')
+    rng = np.random.default_rng(3)
+    n, E = 13, 90
+    dst = np.sort(rng.integers(0, n, E))
+    src = rng.integers(0, n, E)
+    rowptr = np.concatenate([[0], np.cumsum(np.bincount(dst, minlength=n))])
+    xdim = muls[0] + 3 * muls[1] + 5 * muls[2]
+    wn, od = ops.conv_dims(*muls, lout)
+    ir_x = '+'.join(f'{m}x{l}e' for l, m in enumerate(muls) if m)
+    ir_o = '+'.join(f'1x{l}e' for l in range(lout + 1))
+    x64 = torch.tensor(rng.normal(size=(n, xdim)), requires_grad=True)
+    Yv64 = torch.tensor(rng.normal(size=(E, 8)), requires_grad=True)
+    w64 = torch.tensor(rng.normal(size=(E, wn)), requires_grad=True)
+    g64 = torch.tensor(rng.normal(size=(n, od)), requires_grad=True)
+    cs = [torch.tensor(rng.normal(size=s)) for s in [(n, xdim), (E, 8), (E, wn)]]
+    denom = 3.5
+
+    def functional(conv, x, Yv, w, g, cs):
+        Y = torch.cat([torch.ones_like(Yv[:, :1]), Yv], 1)
+        out = conv(x, Y, w)
+        dx, dYv, dw = torch.autograd.grad((out * g).sum(), [x, Yv, w], create_graph=True)
+        S = (dx * cs[0]).sum() + (dYv * cs[1]).sum() + (dw * cs[2]).sum()
+        return out, torch.autograd.grad(S, [x, Yv, w, g], allow_unused=True)
+
+    torch.set_default_dtype(torch.float64)
+    try:
+        tp = TensorProductUVU(ir_x, '1x0e+1x1e+1x2e', ir_o).double()
+        sd, dd = torch.tensor(src), torch.tensor(dst)
+        o_ref, g_ref = functional(lambda x, Y, w: message_gather(x, dd, tp(x[sd], Y, w)) / denom, x64, Yv64, w64, g64, cs)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    graph = dict(rowptr_dst=torch.tensor(rowptr, dtype=torch.int32, device=dev), src=torch.tensor(src, dtype=torch.int32, device=dev))
+    f32 = [t.detach().to(dev, torch.float32).requires_grad_(True) for t in (x64, Yv64, w64, g64)]
+    o, gg = functional(lambda x, Y, w: ho.ConvF.apply(x, Y, w, graph, muls, lout, denom), *f32,
+                       [c.to(dev, torch.float32) for c in cs])
+    assert (o.double().cpu() - o_ref).abs().max() <= 2e-5 * o_ref.abs().max()
+    for a, b, name in zip(gg, g_ref, 'x Y w g'.split()):
+        if b is None or float(b.abs().max()) == 0.0:
+            assert a is None or float(a.abs().max()) < 1e-6, name
+            continue
+        assert (a.double().cpu() - b).abs().max() <= 5e-5 * b.abs().max(), name
+
+
+def test_linear_and_gate_families_second_order():
+    """LinF / LinT / LinWG and GateF / GateB against float64 tensor-op restatements (e3nn Linear: x W / sqrt(fan_in) per
+    l block; Gate: c*silu on scalars and gates, gates multiply the l > 0 channels)."""
+    from sevennet_finetuning_b200 import higher_order as ho, ops
+    dev = torch.device('cuda:0')
+    rng = np.random.default_rng(4)
+    n = 37
+    mi, mo = (24, 16, 8), (24, 8, 8)
+    desc, numel = ops.make_lin_desc('24x0e+16x1e+8x2e', '24x0e+8x1e+8x2e')
+    din = sum(m * (2 * l + 1) for l, m in enumerate(mi))
+    x64 = torch.tensor(rng.normal(size=(n, din)), requires_grad=True)
+    W64 = torch.tensor(rng.normal(size=(numel,)), requires_grad=True)
+    C = 1.6791767923989418
+
+    def lin64(x, W):
+        outs, io, wo = [], 0, 0
+        for l in range(3):
+            D = 2 * l + 1
+            xb = x[:, io:io + mi[l] * D].reshape(-1, mi[l], D)
+            Wb = W[wo:wo + mi[l] * mo[l]].reshape(mi[l], mo[l])
+            outs.append(torch.einsum('nud,uv->nvd', xb, Wb).reshape(x.shape[0], -1) / mi[l] ** 0.5)
+            io += mi[l] * D
+            wo += mi[l] * mo[l]
+        return torch.cat(outs, 1)
+
+    def gate64(y):
+        ns, m1, m2 = mo[0] - mo[1] - mo[2], mo[1], mo[2]
+        s, t, v1, v2 = y[:, :ns], y[:, ns:ns + m1 + m2], y[:, mo[0]:mo[0] + 3 * m1], y[:, mo[0] + 3 * m1:]
+        act = lambda z: C * z * torch.sigmoid(z)
+        gt = act(t)
+        return torch.cat([act(s), (v1.reshape(-1, m1, 3) * gt[:, :m1, None]).reshape(y.shape[0], -1),
+                          (v2.reshape(-1, m2, 5) * gt[:, m1:, None]).reshape(y.shape[0], -1)], 1)
+
+    ns, m1, m2 = mo[0] - mo[1] - mo[2], mo[1], mo[2]
+    dout = ns + 3 * m1 + 5 * m2
+    c1 = torch.tensor(rng.normal(size=(n, dout)))
+    c2 = torch.tensor(rng.normal(size=(n, din)))
+
+    def functional(f, x, W, c1, c2):
+        out = f(x, W)
+        (dx,) = torch.autograd.grad((out * c1).sum() + (out ** 2).sum(), [x], create_graph=True)
+        S = (dx * c2).sum() + (dx ** 2).sum()
+        return out, torch.autograd.grad(S, [x, W])
+
+    o_ref, g_ref = functional(lambda x, W: gate64(lin64(x, W)), x64, W64, c1, c2)
+    x32 = x64.detach().to(dev, torch.float32).requires_grad_(True)
+    W32 = W64.detach().to(dev, torch.float32).requires_grad_(True)
+    o, gg = functional(lambda x, W: ho.GateF.apply(ho.LinF.apply(x, W, desc, numel), ns, m1, m2), x32, W32,
+                       c1.to(dev, torch.float32), c2.to(dev, torch.float32))
+    assert (o.double().cpu() - o_ref).abs().max() <= 1e-5 * o_ref.abs().max()
+    for a, b, name in zip(gg, g_ref, 'x W'.split()):
+        assert (a.double().cpu() - b).abs().max() <= 1e-4 * b.abs().max(), name
+
+
+def test_rehearsal_ewc_step(weights):
+    """One iteration of the rehearsal loop (sevenn/train/trainer.py:173-210) on a batch of small synthetic crystals:
+    batched forward, E/F/S + EWC loss, two optimizer steps; the loss of the same batch goes down."""
+    from sevennet_finetuning_b200 import finetune as ft, nn as b200nn
+    from sevennet_finetuning_b200.model import B200SevenNet
+    from sevennet_finetuning_b200.synthetic import bulk_batch
+    dev = torch.device('cuda:0')
+    cfg = dict(shift=weights['rescale_atomic_energy.shift'].tolist(), scale=weights['rescale_atomic_energy.scale'].tolist(),
+               conv_denominator=float(weights['0_convolution.denominator'][0]))
+    model = b200nn.build_E3_equivariant_model(cfg)
+    sd = {k: torch.tensor(v) for k, v in weights.items()}
+    model.load_state_dict(sd)
+    engine = B200SevenNet(state_dict=weights, device=dev)
+    graphs = ft.synthetic_graphs(bulk_batch(4, seed=1, target_atoms=32), 5.0, dev, label_model=engine, noise=0.002, seed=1)
+    mem = ft.synthetic_graphs(bulk_batch(4, seed=2, target_atoms=32), 5.0, dev, label_model=engine, noise=0.002, seed=2)
+    fisher = {k: torch.ones_like(v) * 1e-3 for k, v in sd.items()}
+    lf = ft.get_loss_functions('huber', {'delta': 0.01}, 1.0, True, 0.01, fisher, {k: v.clone() for k, v in sd.items()},
+                               ewc_lambda=1e5, device=dev)
+    tr = ft.RehearsalTrainer(model, lf, 'adam', {'lr': 1e-4}, device=dev)
+    b, bm = ft.collate(graphs, dev), ft.collate(mem, dev)
+    out = tr.model(ft.to_device(ft.collate(graphs), dev))
+    assert out['inferred_total_energy'].shape == (4,) and out['inferred_stress'].shape == (4, 6)
+    # batched train-mode forward agrees with the engine labels up to the label noise
+    assert (out['inferred_total_energy'].detach().cpu() - b['total_energy'].cpu()).abs().max() < 0.5
+    # directional check of the batched gradient (E/F/S terms; the EWC term is a plain quadratic, checked below):
+    # L(theta - eps g) - L(theta) = -eps |g|^2 + O(eps^2), with eps sized for a 1 % drop
+    lf_data = lf[:3]
+    tr.model.train()
+    tr.optimizer.zero_grad()
+    l0 = ft.total_loss(lf_data, tr.model(b), tr.model, dev)
+    l0.backward()
+    params = [p for p in tr.model.parameters() if p.grad is not None]
+    g2 = sum(float((p.grad ** 2).sum()) for p in params)
+    eps = 0.01 * float(l0) / g2
+    with torch.no_grad():
+        for p in params:
+            p -= eps * p.grad
+    l1 = ft.total_loss(lf_data, tr.model(ft.collate(graphs, dev)), tr.model, dev)
+    ratio = (float(l0) - float(l1)) / (eps * g2)
+    assert 0.7 < ratio < 1.1, (float(l0), float(l1), ratio)
+    # EWC known answer: theta moved by -eps g from theta*, Fisher = 1e-3 everywhere
+    ewc = float(lf[3][0].get_loss(None, tr.model))
+    assert abs(ewc - 1e-3 * eps * eps * g2) <= 2e-2 * ewc   # fp32 rounding of the tiny update theta - eps g
+    # the full rehearsal iteration: train batch step + replay batch step (gradients accumulate, trainer.py:185-210)
+    l2, m2 = tr.run_one_step(ft.collate(graphs, dev), ft.collate(mem, dev))
+    assert torch.isfinite(l2).all() and torch.isfinite(m2).all()
+    fish, opt, cnt = tr.compute_fisher_matrix([ft.collate(graphs[:1], dev), ft.collate(graphs[1:2], dev)])
+    assert cnt == 2 and set(fish) == set(dict(tr.model.named_parameters()))
+    assert all(torch.isfinite(v).all() and float(v.min()) >= 0 for v in fish.values())
