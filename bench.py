@@ -8,7 +8,11 @@ into N bricks (2x1x1 / 2x2x1 / 2x2x2), one rank per brick, ghost features exchan
 over NCCL (sevennet_finetuning_b200/parallel.py); weak scaling (fixed atoms per GPU), value = atoms of the
 whole cell x steps / max-over-ranks time.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--atoms A] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--atoms A] [--impl reference] [--workload md|finetune]
+
+`--workload finetune` measures the other half of the metric: config 2 (N = 1) / config 5 (N > 1, DDP over NCCL),
+structures/s of the reference's rehearsal + EWC iteration (sevenn/train/trainer.py:173-210) over the B200 module twins.
+The default MD line at N = 1 also carries that measurement under the key `finetune`.
 
 One JSON line on stdout (rank 0).  `value` = device-resident inputs; `e2e` = host buffers in, host
 results out, through the public API (B200SevenNet.calculate).  `--impl reference` times the
@@ -164,6 +168,187 @@ def reference_cpu_time(n_atoms, steps, warmup, seed=1):
                        f'({dt:.2f} s/call), graph via the numpy restatement'), dt
 
 
+FT_METRIC = 'SevenNet-0 fine-tune structures/s'
+FT_UNIT = 'structures/s'
+# byte model of one structure-step: the second-order pass runs, per interaction layer, 1 + 3
+# forward-type and 1 + 3 backward-type tensor-product kernels (higher_order.ConvB.backward), each moving the fused-model
+# bytes of SURVEY 8(d): 4 x (8,292 E + 43,136 N) + 4 x (16,092 E + 43,136 N)
+FT_BYTES_E, FT_BYTES_N = 4 * 8292.0 + 4 * 16092.0, 8 * 43136.0
+
+
+def finetune_cfg(world, batch):
+    if world == 1:
+        return {'workload': f'config 2: SevenNet-0 fine-tuning step (Huber E/F/S loss + rehearsal replay batch + EWC Fisher penalty, '
+                            f'Adam), batches of {batch} synthetic ~100-atom bulk crystals + {batch} replay structures',
+                'parallelism': 'single', 'l2': 'inputs larger than L2'}
+    return {'workload': f'config 5: data-parallel SevenNet-0 fine-tuning with rehearsal + EWC, {batch} + {batch} synthetic '
+                        f'~100-atom bulk crystals per GPU and step, gradient all-reduce over NCCL (DDP)',
+            'parallelism': f'dp{world}', 'l2': 'inputs larger than L2'}
+
+
+def finetune_reference_cpu(n_struct, steps, warmup):
+    """The reference's fine-tuning iteration (sevenn/train/trainer.py:173-210) on the host cores through the oracle
+    restatement of its modules (the reference package itself needs e3nn and cannot be imported; its frozen TorchScript
+    graphs have no parameters to train) on a bounded sample: n_struct + n_struct structures per step."""
+    from oracle.graph import radius_graph
+    from oracle.refmodel import build_model
+    from sevennet_finetuning_b200 import finetune as ft
+    from sevennet_finetuning_b200.synthetic import SPECIES_INDEX, bulk_batch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    w = load_weights()
+    m = build_model(dict(shift=w['rescale_atomic_energy.shift'].tolist(), scale=w['rescale_atomic_energy.scale'].tolist(),
+                         conv_denominator=float(w['0_convolution.denominator'][0])))
+    sd = {k: torch.tensor(v) for k, v in w.items()}
+    m.load_state_dict(sd)
+    m.train()
+    m.set_is_batch_data(True)
+
+    def graphs(seed):
+        out = []
+        for pos, cell, pbc, sym in bulk_batch(n_struct, seed=seed):
+            ei, S, D = radius_graph(pos, cell, pbc, 5.0)
+            n = len(pos)
+            out.append({'x': torch.tensor([SPECIES_INDEX[t] for t in sym]), 'edge_index': torch.tensor(ei),
+                        'edge_vec': torch.tensor(D, dtype=torch.float32), 'cell_volume': abs(float(np.linalg.det(cell))),
+                        'num_atoms': n, 'total_energy': -5.0 * n, 'force_of_atoms': torch.zeros(n, 3), 'stress': torch.zeros(6)})
+        return out
+    tb, mb = ft.collate(graphs(11)), ft.collate(graphs(12))
+    lf = ft.get_loss_functions('huber', {'delta': 0.01}, 1.0, True, 0.01, {k: torch.full_like(v, 1e-3) for k, v in sd.items()},
+                               {k: v.clone() for k, v in sd.items()}, ewc_lambda=1e5, device='cpu')
+    opt = torch.optim.Adam([p for p in m.parameters() if p.requires_grad], lr=1e-6)
+
+    def step():
+        opt.zero_grad()
+        for k, b in enumerate((tb, mb)):
+            d = {kk: v.clone() for kk, v in b.items()}
+            d['edge_vec'].requires_grad_(True)
+            loss = ft.total_loss(lf, m(d), m, 'cpu')
+            loss.backward()
+            opt.step()
+        return float(loss.detach())
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    ne = int(tb['edge_index'].shape[1] + mb['edge_index'].shape[1])
+    return dict(value=2 * n_struct / dt, unit=FT_UNIT, cores=cores, kind='port',
+                sample=f'{n_struct} + {n_struct} structures per step of the same generator ({int(tb["x"].shape[0] + mb["x"].shape[0])} '
+                       f'atoms, {ne} edges), {steps} timed steps ({dt:.2f} s/step), oracle restatement of the reference modules'), dt
+
+
+def finetune_bench(a, rank, world, local, warmup, cpu_baseline=True, clocks=True):
+    """Config 2 (N = 1) / config 5 (N > 1): structures/s of the rehearsal + EWC iteration over the B200 module twins."""
+    import torch.distributed as dist
+    from sevennet_finetuning_b200 import _lib, finetune as ft, nn as b200nn, ops
+    from sevennet_finetuning_b200.model import B200SevenNet
+    from sevennet_finetuning_b200.synthetic import bulk_batch
+    dev = torch.device('cuda', local)
+    L = _lib.lib()
+    w = load_weights()
+    sd = {k: torch.tensor(v) for k, v in w.items()}
+    cfg = dict(shift=w['rescale_atomic_energy.shift'].tolist(), scale=w['rescale_atomic_energy.scale'].tolist(),
+               conv_denominator=float(w['0_convolution.denominator'][0]))
+    model = b200nn.build_E3_equivariant_model(cfg)
+    model.load_state_dict(sd)
+    engine = B200SevenNet(state_dict=w, device=dev)
+    B = a.batch
+    # two different (train, replay) batch pairs per rank, alternated, so no step re-reads the previous step's inputs
+    pairs = []
+    for k in range(2):
+        tg = ft.synthetic_graphs(bulk_batch(B, seed=100 + 10 * rank + k), 5.0, dev, label_model=engine, noise=0.002, seed=k)
+        mg = ft.synthetic_graphs(bulk_batch(B, seed=500 + 10 * rank + k), 5.0, dev, label_model=engine, noise=0.002, seed=k)
+        pairs.append((ft.collate(tg, pin=True), ft.collate(mg, pin=True)))
+    del engine
+    torch.cuda.empty_cache()
+    # EWC: Fisher / theta* of the shape the reference ships (fisher_sevenn.pt / opt_params_sevenn.pt); synthetic Fisher
+    g = torch.Generator().manual_seed(7)
+    fisher = {k: torch.rand(v.shape, generator=g) * 1e-3 for k, v in sd.items()}
+    lf = ft.get_loss_functions('huber', {'delta': 0.01}, 1.0, True, 0.01, fisher, {k: v.clone() for k, v in sd.items()},
+                               ewc_lambda=1e5, device=dev)
+    tr = ft.RehearsalTrainer(model, lf, 'adam', {'lr': 1e-6}, device=dev, distributed=world > 1, local_rank=local)
+    dev_pairs = [(ft.to_device(t, dev), ft.to_device(m, dev)) for t, m in pairs]
+    it = {'k': 0}
+
+    def step_resident():
+        t, m = dev_pairs[it['k'] % 2]
+        it['k'] += 1
+        t['edge_vec'].grad = m['edge_vec'].grad = None
+        return tr.run_one_step(dict(t), dict(m))   # the modules rewrite keys of the dict they are given (x -> features)
+
+    def step_e2e():
+        t, m = pairs[it['k'] % 2]
+        it['k'] += 1
+        l, lm = tr.run_one_step(ft.to_device(t, dev), ft.to_device(m, dev))
+        return float(l), float(lm)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        t = torch.tensor([max(e0.elapsed_time(e1) * 1e-3, wall if fn is step_e2e else 0.0)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), out
+
+    for _ in range(warmup):
+        step_resident()
+    launches0 = L.b200_launch_count()
+    cs = ClockSampler(local)
+    if clocks:
+        cs.__enter__()
+    t_res, _ = timed(step_resident, a.steps)
+    launches = L.b200_launch_count() - launches0
+    for _ in range(2):
+        step_e2e()
+    t_e2e, losses = timed(step_e2e, a.steps)
+    if clocks:
+        cs.__exit__()
+    # which kernel family dominates: per-op CUDA events over two extra (untimed) steps
+    ops.enable_timing(True)
+    step_resident()
+    step_resident()
+    per_op = {k: v[0] / 2 for k, v in ops.timing_summary().items()}
+    ops.enable_timing(False)
+    n_struct = 2 * B * world
+    E = sum(int(t['edge_index'].shape[1] + m['edge_index'].shape[1]) for t, m in pairs) / 2
+    N = sum(int(t['x'].shape[0] + m['x'].shape[0]) for t, m in pairs) / 2
+    pk = peaks()
+    step_ms = t_res / a.steps * 1e3
+    byt = FT_BYTES_E * E + FT_BYTES_N * N
+    dom = max(per_op, key=per_op.get)
+    conv_ms = per_op.get('conv_fwd', 0.0) + per_op.get('conv_bwd', 0.0)
+    roof = dict(kernel='conv_fwd+conv_bwd (uvu tensor product + scatter and their reverse / second-order passes)', bound='hbm',
+                achieved=byt / (conv_ms * 1e-3) / 1e9, peak=pk['hbm'], unit='GB/s', frac=byt / (conv_ms * 1e-3) / 1e9 / pk['hbm'],
+                traffic=None, peak_source=pk['src'], ms_per_step=conv_ms, slowest_op=dom)
+    line = dict(metric=FT_METRIC, value=n_struct * a.steps / t_res, unit=FT_UNIT, n_gpus=world, steps=a.steps, warmup=warmup,
+                ms_per_step=step_ms, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32', data='synthetic',
+                config=finetune_cfg(world, B), n_atoms_per_step=N, n_edges_per_step=E,
+                e2e=dict(value=n_struct * a.steps / t_e2e, unit=FT_UNIT,
+                         h2d_bytes_per_step=int(sum(ft.batch_bytes(t) + ft.batch_bytes(m) for t, m in pairs) / 2),
+                         d2h_bytes_per_step=8, ms_per_step=t_e2e / a.steps * 1e3),
+                gpu_launches=int(launches), roofline=roof,
+                step_roofline=dict(bound='hbm', algorithmic_bytes=byt, achieved=byt / (step_ms * 1e-3) / 1e9, peak=pk['hbm'],
+                                   unit='GB/s', frac=byt / (step_ms * 1e-3) / 1e9 / pk['hbm']),
+                op_ms_per_step=per_op, last_losses=list(losses), clocks=cs.summary() if clocks else None)
+    if rank == 0 and cpu_baseline and world == 1:
+        line['cpu_baseline'], _ = finetune_reference_cpu(2, 1, 1)
+    return line
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -174,6 +359,10 @@ def main():
     ap.add_argument('--impl', default='b200')
     ap.add_argument('--cpu-atoms', type=int, default=600)
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--workload', default='md', choices=['md', 'finetune'],
+                    help="md: configs 3/4 (atom-steps/s, the default line); finetune: configs 2/5 (structures/s)")
+    ap.add_argument('--batch', type=int, default=32, help='finetune: structures per train batch (and per replay batch)')
+    ap.add_argument('--no-finetune', action='store_true', help='md line without the appended fine-tune measurement')
     a = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
@@ -193,6 +382,15 @@ def main():
 
     if a.impl == 'reference':
         if rank != 0:
+            return
+        if a.workload == 'finetune':
+            steps = max(1, min(a.steps, 2))
+            cb, dt = finetune_reference_cpu(2, steps, min(a.warmup, 1))
+            print(json.dumps(dict(metric=FT_METRIC, value=cb['value'], unit=FT_UNIT, n_gpus=a.gpus, steps=steps, warmup=min(a.warmup, 1),
+                                  ms_per_step=dt * 1e3, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32',
+                                  data='synthetic', config=finetune_cfg(world, a.batch), impl='reference', cpu_baseline=cb,
+                                  e2e=dict(value=cb['value'], unit=FT_UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                                  gpu_launches=0)))
             return
         steps = max(1, min(a.steps, 3))
         cb, dt = reference_cpu_time(a.cpu_atoms, steps, min(a.warmup, 1))
@@ -218,6 +416,13 @@ def main():
         _JSON_OUT = os.fdopen(os.dup(1), 'w')
         os.dup2(2, 1)
         dist.init_process_group('nccl', device_id=dev)
+    if a.workload == 'finetune':
+        line = finetune_bench(a, rank, world, local, warmup, cpu_baseline=not a.no_cpu_baseline)
+        if rank == 0:
+            print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     L = _lib.lib()
     model = B200SevenNet(state_dict=load_weights(), device=dev)
     pos, cell, pbc, types = make_cell(n_total, seed=0)
@@ -343,6 +548,20 @@ def main():
                                    peak=pk['hbm'] * world, unit='GB/s',
                                    frac=step_bytes / (step_ms * 1e-3) / 1e9 / (pk['hbm'] * world)),
                 kernel_ms_per_step=cat_ms, ms_each_step=per_step_res, clocks=clocks)
+    if world == 1 and not a.no_finetune:
+        # second half of BASELINE.json's metric ("...; fine-tune structures/s"): config 2 in the same run, after the MD
+        # workspace is released (full line: python bench.py --workload finetune)
+        model._ws = None
+        del out, pos_d, types_d
+        torch.cuda.empty_cache()
+        try:
+            fa = argparse.Namespace(**vars(a))
+            fa.steps = min(a.steps, 5)
+            fl = finetune_bench(fa, rank, world, local, 3, cpu_baseline=not a.no_cpu_baseline, clocks=False)
+            line['finetune'] = {k: fl[k] for k in ('metric', 'value', 'unit', 'ms_per_step', 'steps', 'config', 'e2e', 'gpu_launches',
+                                                   'roofline', 'step_roofline', 'op_ms_per_step', 'cpu_baseline') if k in fl}
+        except Exception as ex:   # the MD line stands on its own
+            line['finetune'] = {'error': repr(ex)}
     if rank == 0:
         if not a.no_cpu_baseline and world == 1:
             line['cpu_baseline'], _ = reference_cpu_time(a.cpu_atoms, 2, 1)

@@ -146,6 +146,62 @@ irreps_linear_wgrad_kernel(LinDesc d, int n_nodes, const float* __restrict__ x, 
     }
 }
 
+// Split-K weight gradient for many rows (the radial MLP's weight gradient runs over every EDGE of a training batch,
+// sevenn/nn/convolution.py:97-106 under loss.backward(), trainer.py:185): 64x64 tile of W per CTA, 4x4 register
+// micro-tiles, the row range cut into `splits` slices (grid.z) whose partial tiles are reduced in fp64 in a fixed order.
+template <int D>
+__global__ void __launch_bounds__(256)
+wgrad_splitk_kernel(LinBlock b, int in_dim, int out_dim, int n_nodes, int nodes_per_split, const float* __restrict__ x,
+                    const float* __restrict__ dy, float* __restrict__ part) {
+  constexpr int NCH = 32 / D;   // nodes per staged chunk (<= 32 GEMM rows)
+  const int k0 = blockIdx.x * 64, o0 = blockIdx.y * 64;
+  const int nb = blockIdx.z * nodes_per_split, ne = min(n_nodes, nb + nodes_per_split);
+  __shared__ __align__(16) float xs[32][68], ys[32][68];
+  const int tk = threadIdx.x / 16, to = threadIdx.x % 16;
+  float acc[4][4] = {};
+  const int wk = min(64, b.mul_in - k0) * D, wo = min(64, b.mul_out - o0) * D;   // valid contiguous floats per node
+  for (int n0 = nb; n0 < ne; n0 += NCH) {
+    const int nn = min(NCH, ne - n0);
+    for (int j = threadIdx.x; j < nn * 64 * D; j += 256) {
+      const int node = j / (64 * D), rem = j % (64 * D), c = rem / D, m = rem % D;
+      const size_t row = (size_t)(n0 + node);
+      xs[node * D + m][c] = rem < wk ? __ldg(x + row * in_dim + b.in_off + k0 * D + rem) : 0.f;
+      ys[node * D + m][c] = rem < wo ? __ldg(dy + row * out_dim + b.out_off + o0 * D + rem) : 0.f;
+    }
+    __syncthreads();
+    const int rows = nn * D;
+#pragma unroll 4
+    for (int r = 0; r < rows; ++r) {
+      const float4 a = *reinterpret_cast<const float4*>(&xs[r][tk * 4]);
+      const float4 g = *reinterpret_cast<const float4*>(&ys[r][to * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w}, gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) acc[i][jj] = fmaf(av[i], gv[jj], acc[i][jj]);
+    }
+    __syncthreads();
+  }
+  float* pt = part + (size_t)blockIdx.z * b.mul_in * b.mul_out;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const int k = k0 + tk * 4 + i, o = o0 + to * 4 + jj;
+      if (k < b.mul_in && o < b.mul_out) pt[(size_t)k * b.mul_out + o] = acc[i][jj];
+    }
+}
+
+__global__ void wgrad_reduce_kernel(int numel, int splits, float scale, const float* __restrict__ part, float* __restrict__ dW,
+                                    int accumulate) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= numel) return;
+  double s = 0.0;
+  for (int k = 0; k < splits; ++k) s += (double)part[(size_t)k * numel + i];
+  const float v = (float)(s * (double)scale);
+  dW[i] = accumulate ? dW[i] + v : v;
+}
+
 static bool lin_ok(const LinDesc& d) {
   if (d.nblk < 1 || d.nblk > 4) return false;
   for (int i = 0; i < d.nblk; ++i)
@@ -171,6 +227,29 @@ int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W,
 int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const float* dy, float* dW, int accumulate,
                         cudaStream_t st) {
   B200_REQUIRE(lin_ok(d), "irreps_linear_wgrad: 1..4 blocks with 2l+1 in {1,3,5}");
+  if (n_nodes >= 2048) {   // many rows: split the reduction over the rows across CTAs
+    keep_async_pool();
+    for (int i = 0; i < d.nblk; ++i) {
+      const LinBlock& b = d.blk[i];
+      const int tiles = ((b.mul_in + 63) / 64) * ((b.mul_out + 63) / 64);
+      int splits = max(1, min((4 * 148 + tiles - 1) / tiles, n_nodes / 256));
+      const int per = (n_nodes + splits - 1) / splits;
+      splits = (n_nodes + per - 1) / per;
+      const int numel = b.mul_in * b.mul_out;
+      float* part = nullptr;
+      if (cudaMallocAsync((void**)&part, sizeof(float) * (size_t)splits * numel, st) != cudaSuccess) {
+        set_error("irreps_linear_wgrad: cudaMallocAsync of the split-K partials failed");
+        return B200_ERR_CUDA;
+      }
+      dim3 grid((b.mul_in + 63) / 64, (b.mul_out + 63) / 64, splits);
+      if (b.d == 1) wgrad_splitk_kernel<1><<<grid, 256, 0, st>>>(b, d.in_dim, d.out_dim, n_nodes, per, x, dy, part);
+      else if (b.d == 3) wgrad_splitk_kernel<3><<<grid, 256, 0, st>>>(b, d.in_dim, d.out_dim, n_nodes, per, x, dy, part);
+      else wgrad_splitk_kernel<5><<<grid, 256, 0, st>>>(b, d.in_dim, d.out_dim, n_nodes, per, x, dy, part);
+      wgrad_reduce_kernel<<<(numel + 255) / 256, 256, 0, st>>>(numel, splits, b.scale, part, dW + b.w_off, accumulate);
+      cudaFreeAsync(part, st);
+    }
+    return check_launch("irreps_linear_wgrad", 2 * d.nblk);
+  }
   int mk = 0, mo = 0;
   for (int i = 0; i < d.nblk; ++i) { mk = max(mk, d.blk[i].mul_in); mo = max(mo, d.blk[i].mul_out); }
   dim3 grid((mk + 31) / 32, (mo + 31) / 32, d.nblk);

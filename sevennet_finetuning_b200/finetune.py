@@ -188,6 +188,7 @@ class RehearsalTrainer:
         opt = {'adam': torch.optim.Adam, 'adamw': torch.optim.AdamW, 'sgd': torch.optim.SGD}[optimizer.lower()]
         self.optimizer = opt(params, **(optim_param or {'lr': 1e-4}))
         self.loss_functions = loss_functions
+        self._params = params
         for ld, _ in loss_functions:
             if isinstance(ld, EWCLoss):
                 ld.to(self.device)
@@ -196,18 +197,27 @@ class RehearsalTrainer:
         output = self.model(batch)
         return output, total_loss(self.loss_functions, output, self.model, self.device)
 
+    def _backward(self, loss):
+        # the reference calls loss.backward() (trainer.py:185,209), which also fills edge_vec.grad (a leaf that requires
+        # grad) and never reads it; restricting the reverse pass to the parameters gives identical parameter gradients
+        # without that branch.  Under DDP the plain call is kept (its reducer hooks expect it).
+        if self.distributed:
+            loss.backward()
+        else:
+            loss.backward(inputs=self._params)
+
     def run_one_step(self, batch, batch_mem=None):
         """One iteration of the rehearsal loop (trainer.py:173-210).  ``batch`` / ``batch_mem`` are device dicts
         (``to_device``).  Returns (train loss, replay loss) as device tensors."""
         self.model.train()
         self.optimizer.zero_grad()
         _, loss = self._fwd_loss(batch)
-        loss.backward()
+        self._backward(loss)
         self.optimizer.step()
         mem_loss = None
         if batch_mem is not None:
             _, mem_loss = self._fwd_loss(batch_mem)
-            mem_loss.backward()
+            self._backward(mem_loss)
             self.optimizer.step()
         return loss.detach(), (None if mem_loss is None else mem_loss.detach())
 

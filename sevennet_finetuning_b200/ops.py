@@ -14,6 +14,37 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+# ---- optional per-op CUDA-event timing (bench.py: which kernel family dominates a fine-tuning step) ----------------------
+_TIMING = None
+
+
+def enable_timing(flag=True):
+    global _TIMING
+    _TIMING = {} if flag else None
+
+
+def timing_summary():
+    """{op name: (total ms, calls)} since enable_timing(); synchronises."""
+    torch.cuda.synchronize()
+    return {k: (sum(a.elapsed_time(b) for a, b in v), len(v)) for k, v in (_TIMING or {}).items()}
+
+
+def _timed(fn):
+    import functools
+
+    @functools.wraps(fn)
+    def wrap(*a, **k):
+        if _TIMING is None:
+            return fn(*a, **k)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn(*a, **k)
+        e1.record()
+        _TIMING.setdefault(fn.__name__, []).append((e0, e1))
+        return out
+    return wrap
+
+
 def _p(t):
     if t is None:
         return None
@@ -127,6 +158,7 @@ def csr_transpose(n_nodes, src):
 
 
 # ---- edge / radial ------------------------------------------------------------------------------------
+@_timed
 def edge_embed_fwd(params, vec, coeffs):
     E = vec.shape[0]
     ln = torch.empty(E, dtype=torch.float32, device=vec.device)
@@ -137,6 +169,7 @@ def edge_embed_fwd(params, vec, coeffs):
     return ln, Y, emb
 
 
+@_timed
 def edge_embed_bwd(params, vec, coeffs, dY, demb):
     E = vec.shape[0]
     dvec = torch.empty(E, 3, dtype=torch.float32, device=vec.device)
@@ -145,6 +178,7 @@ def edge_embed_bwd(params, vec, coeffs, dY, demb):
     return dvec
 
 
+@_timed
 def radial_mlp_fwd(emb, W0, W1, W2):
     E = emb.shape[0]
     d = MlpDesc(W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1])
@@ -153,6 +187,7 @@ def radial_mlp_fwd(emb, W0, W1, W2):
     return w
 
 
+@_timed
 def radial_mlp_bwd(emb, W0, W1, W2, dw, demb=None):
     E = emb.shape[0]
     d = MlpDesc(W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1])
@@ -165,6 +200,7 @@ def radial_mlp_bwd(emb, W0, W1, W2, dw, demb=None):
 
 
 # ---- convolution ----------------------------------------------------------------------------------------
+@_timed
 def conv_fwd(muls, lout, rowptr, src, x, Y, w, denom):
     n = rowptr.shape[0] - 1
     _, od = conv_dims(*muls, lout)
@@ -174,6 +210,7 @@ def conv_fwd(muls, lout, rowptr, src, x, Y, w, denom):
     return out
 
 
+@_timed
 def conv_bwd_edge(muls, lout, rowptr, src, x, Y, w, gout, denom, dY=None):
     n = rowptr.shape[0] - 1
     E = src.shape[0]
@@ -186,6 +223,7 @@ def conv_bwd_edge(muls, lout, rowptr, src, x, Y, w, gout, denom, dY=None):
     return dw, dY
 
 
+@_timed
 def conv_bwd(muls, lout, n_src, rowptr, src, x, Y, w, gout, denom, dY=None):
     """d weight, d edge_attr and d x[n_src] in one pass (b200_conv_bwd)."""
     n = rowptr.shape[0] - 1
@@ -201,6 +239,7 @@ def conv_bwd(muls, lout, n_src, rowptr, src, x, Y, w, gout, denom, dY=None):
     return dw, dY, dx
 
 
+@_timed
 def conv_bwd_x(muls, lout, n_src, rrowptr, eid, dst, gout, Y, w, denom):
     xdim = muls[0] + 3 * muls[1] + 5 * muls[2]
     dx = torch.empty(n_src, xdim, dtype=torch.float32, device=gout.device)
@@ -210,6 +249,7 @@ def conv_bwd_x(muls, lout, n_src, rrowptr, eid, dst, gout, Y, w, denom):
 
 
 # ---- node side --------------------------------------------------------------------------------------------
+@_timed
 def irreps_linear(desc, x, W, transpose=False, out=None):
     n = x.shape[0]
     width = desc.in_dim if transpose else desc.out_dim
@@ -222,6 +262,7 @@ def irreps_linear(desc, x, W, transpose=False, out=None):
     return out
 
 
+@_timed
 def irreps_linear_wgrad(desc, x, dy, numel):
     dW = torch.zeros(numel, dtype=torch.float32, device=x.device)
     check(lib().b200_irreps_linear_wgrad(C.byref(desc), x.shape[0], _p(x), _p(dy), _p(dW), 0, _stream()),
@@ -229,12 +270,14 @@ def irreps_linear_wgrad(desc, x, dy, numel):
     return dW
 
 
+@_timed
 def gate_fwd(ns, m1, m2, x):
     out = torch.empty(x.shape[0], ns + 3 * m1 + 5 * m2, dtype=torch.float32, device=x.device)
     check(lib().b200_gate_fwd(ns, m1, m2, x.shape[0], _p(x), _p(out), _stream()), 'gate_fwd')
     return out
 
 
+@_timed
 def gate_bwd(ns, m1, m2, x, gout):
     gin = torch.empty_like(x)
     check(lib().b200_gate_bwd(ns, m1, m2, x.shape[0], _p(x), _p(gout), _p(gin), _stream()), 'gate_bwd')
@@ -305,6 +348,7 @@ def edge_embed_bwd_r(params, vec, dY, dr):
     return dvec
 
 
+@_timed
 def gate_bwd2(ns, m1, m2, x, gout, a):
     """Second-order pass of the gate: a = dL/d(gate_bwd output) -> (dL/dx, dL/d gout)."""
     dx = torch.empty_like(x)

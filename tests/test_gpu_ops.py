@@ -238,6 +238,25 @@ def test_irreps_linear(dev, irin, irout):
     assert _rel(y2, 2 * y) < 2e-5
 
 
+@pytest.mark.parametrize('irin,irout,n', [('64x0e', '960x0e', 30011), ('8x0e', '64x0e', 5000),
+                                          ('20x0e+7x1e+5x2e', '33x0e+70x1e+3x2e', 4099), ('128x0e+64x1e+32x2e', '224x0e+64x1e+32x2e', 2048)])
+def test_irreps_linear_wgrad_many_rows(dev, irin, irout, n):
+    """split-K weight gradient (rows = edges of a training batch for the radial MLP layers) against float64"""
+    from oracle import refnn
+    from sevennet_finetuning_b200 import ops
+    torch.manual_seed(2)
+    lin = refnn.O3Linear(irin, irout).double()
+    x = torch.randn(n, refnn.irreps_dim(lin.irreps_in), dtype=torch.float64)
+    y = lin(x)
+    g = torch.randn_like(y)
+    (y * g).sum().backward()
+    desc, numel = ops.make_lin_desc(irin, irout)
+    x32, g32 = x.float().to(dev), g.float().to(dev)
+    dW = ops.irreps_linear_wgrad(desc, x32, g32, numel)
+    assert _rel(dW, lin.weight.grad) < 2e-5
+    assert torch.equal(dW, ops.irreps_linear_wgrad(desc, x32, g32, numel))   # fixed reduction order
+
+
 @pytest.mark.parametrize('irx', ['128x0e+64x1e+32x2e', '128x0e', '16x0e+3x1e', '16x0e+5x2e'])
 def test_gate(dev, irx):
     from oracle import refnn
