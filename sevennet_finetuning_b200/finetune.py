@@ -176,13 +176,16 @@ class RehearsalTrainer:
         self.distributed = distributed
         if distributed:
             from torch.nn.parallel import DistributedDataParallel as DDP
-            device = torch.device('cuda', local_rank)
+            cuda = torch.device(device).type == 'cuda'
+            device = torch.device('cuda', local_rank) if cuda else torch.device('cpu')   # cpu: gloo tests of the host logic
             torch.distributed.barrier()
-            self.model = DDP(model.to(device), device_ids=[device])
-            self.model.module.set_is_batch_data(True)
+            self.model = DDP(model.to(device), device_ids=[device] if cuda else None)
+            if hasattr(self.model.module, 'set_is_batch_data'):
+                self.model.module.set_is_batch_data(True)
         else:
             self.model = model.to(device)
-            self.model.set_is_batch_data(True)
+            if hasattr(self.model, 'set_is_batch_data'):
+                self.model.set_is_batch_data(True)
         self.device = torch.device(device)
         params = [p for p in self.model.parameters() if p.requires_grad]
         opt = {'adam': torch.optim.Adam, 'adamw': torch.optim.AdamW, 'sgd': torch.optim.SGD}[optimizer.lower()]
