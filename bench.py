@@ -330,7 +330,7 @@ def finetune_bench(a, rank, world, local, warmup, cpu_baseline=True, clocks=True
     step_ms = t_res / a.steps * 1e3
     byt = FT_BYTES_E * E + FT_BYTES_N * N
     dom = max(per_op, key=per_op.get)
-    conv_ms = per_op.get('conv_fwd', 0.0) + per_op.get('conv_bwd', 0.0)
+    conv_ms = sum(v for k, v in per_op.items() if k.split()[0] in ('conv_fwd', 'conv_bwd')) or 1e-9
     roof = dict(kernel='conv_fwd+conv_bwd (uvu tensor product + scatter and their reverse / second-order passes)', bound='hbm',
                 achieved=byt / (conv_ms * 1e-3) / 1e9, peak=pk['hbm'], unit='GB/s', frac=byt / (conv_ms * 1e-3) / 1e9 / pk['hbm'],
                 traffic=None, peak_source=pk['src'], ms_per_step=conv_ms, slowest_op=dom)

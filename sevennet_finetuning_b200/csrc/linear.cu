@@ -5,6 +5,7 @@
 // W_l[mul_in, mul_out] / sqrt(fan_in); flat weight = concatenation of W_l in instruction order.
 //
 // CUDA-core SGEMM (fp32): rows of the GEMM are (node, m) pairs; 64x64 tiles, 4x4 register micro-tiles.
+#include <stdint.h>
 #include <stdlib.h>
 
 #include "ops.h"
@@ -147,48 +148,77 @@ irreps_linear_wgrad_kernel(LinDesc d, int n_nodes, const float* __restrict__ x, 
 }
 
 // Split-K weight gradient for many rows (the radial MLP's weight gradient runs over every EDGE of a training batch,
-// sevenn/nn/convolution.py:97-106 under loss.backward(), trainer.py:185): 64x64 tile of W per CTA, 4x4 register
-// micro-tiles, the row range cut into `splits` slices (grid.z) whose partial tiles are reduced in fp64 in a fixed order.
+// sevenn/nn/convolution.py:97-106 under loss.backward(), trainer.py:185): dW = X^T G with the reduction over rows.
+// 64x64 tile of W per CTA on the tensor cores: warp-level m16n8k8 tf32 MMAs with every operand split hi + lo
+// (3xTF32: hi*hi + hi*lo + lo*hi, fp32-grade products), 8 warps x (16 x 32) outputs; the row range is cut into
+// `splits` slices (grid.z) whose partial tiles are reduced in fp64 in a fixed order (wgrad_reduce_kernel).
+__device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+  const float r = v - __uint_as_float(hi);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+}
+__device__ __forceinline__ void mma_tf32_16x8x8(float* c, const uint32_t* a, const uint32_t* b) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
 template <int D>
 __global__ void __launch_bounds__(256)
 wgrad_splitk_kernel(LinBlock b, int in_dim, int out_dim, int n_nodes, int nodes_per_split, const float* __restrict__ x,
                     const float* __restrict__ dy, float* __restrict__ part) {
-  constexpr int NCH = 32 / D;   // nodes per staged chunk (<= 32 GEMM rows)
+  constexpr int KR = 64;        // GEMM rows (node, m) staged per chunk
+  constexpr int NCH = KR / D;   // nodes per chunk
+  constexpr int LD = 72;        // row stride == 8 (mod 32): the fragment loads below hit 32 distinct banks
   const int k0 = blockIdx.x * 64, o0 = blockIdx.y * 64;
   const int nb = blockIdx.z * nodes_per_split, ne = min(n_nodes, nb + nodes_per_split);
-  __shared__ __align__(16) float xs[32][68], ys[32][68];
-  const int tk = threadIdx.x / 16, to = threadIdx.x % 16;
+  __shared__ __align__(16) float xs[KR * LD], ys[KR * LD];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int m0 = (warp & 3) * 16, n0 = (warp >> 2) * 32;
   float acc[4][4] = {};
   const int wk = min(64, b.mul_in - k0) * D, wo = min(64, b.mul_out - o0) * D;   // valid contiguous floats per node
-  for (int n0 = nb; n0 < ne; n0 += NCH) {
-    const int nn = min(NCH, ne - n0);
-    for (int j = threadIdx.x; j < nn * 64 * D; j += 256) {
+  for (int n0n = nb; n0n < ne; n0n += NCH) {
+    const int nn = min(NCH, ne - n0n);
+    for (int j = threadIdx.x; j < NCH * 64 * D; j += 256) {
       const int node = j / (64 * D), rem = j % (64 * D), c = rem / D, m = rem % D;
-      const size_t row = (size_t)(n0 + node);
-      xs[node * D + m][c] = rem < wk ? __ldg(x + row * in_dim + b.in_off + k0 * D + rem) : 0.f;
-      ys[node * D + m][c] = rem < wo ? __ldg(dy + row * out_dim + b.out_off + o0 * D + rem) : 0.f;
+      const size_t row = (size_t)(n0n + node);
+      const bool in = node < nn;
+      xs[(node * D + m) * LD + c] = (in && rem < wk) ? __ldg(x + row * in_dim + b.in_off + k0 * D + rem) : 0.f;
+      ys[(node * D + m) * LD + c] = (in && rem < wo) ? __ldg(dy + row * out_dim + b.out_off + o0 * D + rem) : 0.f;
     }
+    if constexpr (NCH * D < KR)   // rows the node loop does not cover (D = 3: 63, D = 5: 60 of 64)
+      for (int j = threadIdx.x; j < (KR - NCH * D) * 64; j += 256) {
+        xs[(NCH * D + j / 64) * LD + j % 64] = 0.f;
+        ys[(NCH * D + j / 64) * LD + j % 64] = 0.f;
+      }
     __syncthreads();
-    const int rows = nn * D;
-#pragma unroll 4
-    for (int r = 0; r < rows; ++r) {
-      const float4 a = *reinterpret_cast<const float4*>(&xs[r][tk * 4]);
-      const float4 g = *reinterpret_cast<const float4*>(&ys[r][to * 4]);
-      const float av[4] = {a.x, a.y, a.z, a.w}, gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll 2
+    for (int k8 = 0; k8 < KR; k8 += 8) {
+      uint32_t ah[4], al[4];
+      split_tf32(xs[(k8 + t) * LD + m0 + g], ah[0], al[0]);
+      split_tf32(xs[(k8 + t) * LD + m0 + g + 8], ah[1], al[1]);
+      split_tf32(xs[(k8 + t + 4) * LD + m0 + g], ah[2], al[2]);
+      split_tf32(xs[(k8 + t + 4) * LD + m0 + g + 8], ah[3], al[3]);
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj) acc[i][jj] = fmaf(av[i], gv[jj], acc[i][jj]);
+      for (int j = 0; j < 4; ++j) {
+        uint32_t bh[2], bl[2];
+        split_tf32(ys[(k8 + t) * LD + n0 + j * 8 + g], bh[0], bl[0]);
+        split_tf32(ys[(k8 + t + 4) * LD + n0 + j * 8 + g], bh[1], bl[1]);
+        mma_tf32_16x8x8(acc[j], al, bh);
+        mma_tf32_16x8x8(acc[j], ah, bl);
+        mma_tf32_16x8x8(acc[j], ah, bh);
+      }
     }
     __syncthreads();
   }
   float* pt = part + (size_t)blockIdx.z * b.mul_in * b.mul_out;
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int jj = 0; jj < 4; ++jj) {
-      const int k = k0 + tk * 4 + i, o = o0 + to * 4 + jj;
-      if (k < b.mul_in && o < b.mul_out) pt[(size_t)k * b.mul_out + o] = acc[i][jj];
+    for (int q = 0; q < 4; ++q) {
+      const int k = k0 + m0 + g + (q >> 1) * 8, o = o0 + n0 + j * 8 + 2 * t + (q & 1);
+      if (k < b.mul_in && o < b.mul_out) pt[(size_t)k * b.mul_out + o] = acc[j][q];
     }
 }
 
@@ -232,7 +262,7 @@ int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const flo
     for (int i = 0; i < d.nblk; ++i) {
       const LinBlock& b = d.blk[i];
       const int tiles = ((b.mul_in + 63) / 64) * ((b.mul_out + 63) / 64);
-      int splits = max(1, min((4 * 148 + tiles - 1) / tiles, n_nodes / 256));
+      int splits = max(1, min((4 * 148 + tiles - 1) / tiles, n_nodes / 32));   // >= 32 nodes per slice
       const int per = (n_nodes + splits - 1) / splits;
       splits = (n_nodes + per - 1) / per;
       const int numel = b.mul_in * b.mul_out;

@@ -21,6 +21,19 @@ from torch.autograd.function import once_differentiable
 from . import ops
 
 
+class force_pass:
+    """Context of the first reverse pass (d E / d edge_vec, force_output.py:165-170): autograd asks every Function for
+    all of its input gradients, but only the edge-vector branch is consumed there, so the weight-gradient kernels are
+    skipped while it is active (they run in the loss's own reverse pass)."""
+    active = False
+
+    def __enter__(self):
+        force_pass.active = True
+
+    def __exit__(self, *a):
+        force_pass.active = False
+
+
 def _c(t):
     return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.to(torch.float32).contiguous()
 
@@ -39,7 +52,8 @@ class LinF(Function):
     def backward(ctx, g):
         x, W = ctx.saved_tensors
         dx = LinT.apply(g, W, ctx.desc, ctx.numel) if ctx.needs_input_grad[0] else None
-        dW = LinWG.apply(x, g, ctx.desc, ctx.numel).view_as(W) if ctx.needs_input_grad[1] else None
+        dW = (LinWG.apply(x, g, ctx.desc, ctx.numel).view_as(W)
+              if ctx.needs_input_grad[1] and not force_pass.active else None)
         return dx, dW, None, None
 
 

@@ -504,7 +504,11 @@ class ForceStressOutputFromEdge(nn.Module):
     def forward(self, data):
         energy = data[self.key_energy]
         rij = data[self.key_edge]
-        (fij,) = torch.autograd.grad([energy.sum()], [rij], create_graph=_second_order(self), allow_unused=True)
+        if _second_order(self):
+            with ho.force_pass():
+                (fij,) = torch.autograd.grad([energy.sum()], [rij], create_graph=True, allow_unused=True)
+        else:
+            (fij,) = torch.autograd.grad([energy.sum()], [rij], create_graph=False, allow_unused=True)
         g = _graph_of(data)
         n = g['n_src']
         if fij is None:

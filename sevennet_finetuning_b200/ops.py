@@ -16,6 +16,7 @@ def _stream():
 
 # ---- optional per-op CUDA-event timing (bench.py: which kernel family dominates a fine-tuning step) ----------------------
 _TIMING = None
+_TIMING_SHAPES = False
 
 
 def enable_timing(flag=True):
@@ -40,7 +41,10 @@ def _timed(fn):
         e0.record()
         out = fn(*a, **k)
         e1.record()
-        _TIMING.setdefault(fn.__name__, []).append((e0, e1))
+        key = fn.__name__
+        if _TIMING_SHAPES:
+            key += ' ' + ' '.join('x'.join(map(str, t.shape)) for t in a if torch.is_tensor(t) and t.dim() == 2)[:60]
+        _TIMING.setdefault(key, []).append((e0, e1))
         return out
     return wrap
 
