@@ -50,6 +50,16 @@ int b200_edge_embed_fwd(const EdgeParams* p, int64_t n_edges, const float* edge_
 /* d edge_vec[E,3] = J^T (d edge_attr[E,9] (NULL ok), d edge_embedding[E,nb] (NULL ok)) */
 int b200_edge_embed_bwd(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* bessel_coeffs,
                         const float* d_edge_attr, const float* d_edge_embedding, float* d_edge_vec, void* stream);
+/* d bessel_coeffs[nb] = sum_e d_edge_embedding[e, n] * d emb_n / d k_n (trainable frequencies, edge_embedding.py:95-101) */
+int b200_edge_embed_dk(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* bessel_coeffs,
+                       const float* d_edge_embedding, float* d_coeffs, void* stream);
+/* second-order pass: the reverse of b200_edge_embed_bwd (force_output.py:165-170 create_graph=self.training).
+ * a[E,3] = dL/d(d_edge_vec).  Outputs: dL/d edge_vec (Hessian-vector product) [E,3]; dL/d(d_edge_attr) [E,9] and
+ * dL/d(d_edge_embedding) [E,nb] (NULL ok); dL/d bessel_coeffs [nb] (NULL ok).  d_edge_attr / d_edge_embedding are the
+ * inputs the first reverse pass was called with (NULL ok = zero). */
+int b200_edge_embed_bwd2(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* bessel_coeffs,
+                         const float* d_edge_attr, const float* d_edge_embedding, const float* a, float* d_edge_vec,
+                         float* d_d_edge_attr, float* d_d_edge_embedding, float* d_coeffs, void* stream);
 /* same with dE/d|edge_vec| given directly (d_r[E], from b200_fused_conv_bwd) instead of d edge_embedding */
 int b200_edge_embed_bwd_r(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* d_edge_attr,
                           const float* d_r, float* d_edge_vec, void* stream);

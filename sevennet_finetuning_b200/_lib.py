@@ -49,6 +49,8 @@ SIGNATURES = {
     'b200_launch_count': (C.c_longlong, []),
     'b200_edge_embed_fwd': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_edge_embed_bwd': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_edge_embed_bwd2': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_edge_embed_dk': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp]),
     'b200_radial_mlp_fwd': (_i, [_P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_radial_mlp_bwd': (_i, [_P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     'b200_edge_embed_bwd_r': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp]),

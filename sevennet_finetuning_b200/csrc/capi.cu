@@ -45,6 +45,16 @@ int b200_edge_embed_bwd(const EdgeParams* p, int64_t E, const float* vec, const 
   B200_REQUIRE(p && (E == 0 || (vec && coeffs && dvec)), "edge_embed_bwd: null argument");
   return edge_embed_bwd(*p, E, vec, coeffs, dY, demb, dvec, ST(stream));
 }
+int b200_edge_embed_bwd2(const EdgeParams* p, int64_t E, const float* vec, const float* coeffs, const float* gY,
+                         const float* gemb, const float* a, float* dvec2, float* dgY, float* dgemb, float* dk, void* stream) {
+  B200_REQUIRE(p && (E == 0 || (vec && coeffs && a && dvec2)), "edge_embed_bwd2: null argument");
+  return edge_embed_bwd2(*p, E, vec, coeffs, gY, gemb, a, dvec2, dgY, dgemb, dk, ST(stream));
+}
+int b200_edge_embed_dk(const EdgeParams* p, int64_t E, const float* vec, const float* coeffs, const float* gemb, float* dk,
+                       void* stream) {
+  B200_REQUIRE(p && dk && (E == 0 || (vec && coeffs && gemb)), "edge_embed_dk: null argument");
+  return edge_embed_dk(*p, E, vec, coeffs, gemb, dk, ST(stream));
+}
 int b200_edge_embed_bwd_r(const EdgeParams* p, int64_t E, const float* vec, const float* dY, const float* dr, float* dvec,
                           void* stream) {
   B200_REQUIRE(p && (E == 0 || (vec && dvec)), "edge_embed_bwd_r: null argument");

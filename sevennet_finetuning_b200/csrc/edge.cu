@@ -147,6 +147,239 @@ __global__ void force_virial_kernel(int n_atoms, const int* __restrict__ rowptr,
   }
 }
 
+// ---- second-order pass (fine-tuning: the loss differentiates the forces, sevenn/nn/force_output.py:165-170 with
+// create_graph=self.training, sevenn/train/trainer.py:173-186) ------------------------------------------------------------
+// The first reverse pass is dvec = B(vec, k; gY, gemb) = sum_c gY_c grad Y_c + sum_n gemb_n grad emb_n.  With
+// a = dL/d(dvec), S = <a, dvec>:
+//   dS/d gY_c   = D_a Y_c,  dS/d gemb_n = D_a emb_n          (directional derivative of the forward map along a)
+//   dS/d vec    = D_a B(vec)                                  (Hessian-vector product)
+//   dS/d k_n    = sum_e gemb_n D_a (d emb_n / d k_n)          (Bessel frequencies are trainable, edge_embedding.py:95-101)
+// All four are the tangent parts of the same forward / reverse formulas evaluated on dual numbers (value, derivative
+// along a): the arithmetic below is the float code of the kernels above, templated on the scalar type.
+struct Dual {
+  float v, d;
+};
+__device__ __forceinline__ Dual mk(float v, float d = 0.f) { Dual r; r.v = v; r.d = d; return r; }
+__device__ __forceinline__ Dual operator+(Dual a, Dual b) { return mk(a.v + b.v, a.d + b.d); }
+__device__ __forceinline__ Dual operator-(Dual a, Dual b) { return mk(a.v - b.v, a.d - b.d); }
+__device__ __forceinline__ Dual operator*(Dual a, Dual b) { return mk(a.v * b.v, a.d * b.v + a.v * b.d); }
+__device__ __forceinline__ Dual operator/(Dual a, Dual b) {
+  const float q = a.v / b.v;
+  return mk(q, (a.d - q * b.d) / b.v);
+}
+__device__ __forceinline__ Dual operator*(float a, Dual b) { return mk(a * b.v, a * b.d); }
+__device__ __forceinline__ Dual operator*(Dual b, float a) { return mk(a * b.v, a * b.d); }
+__device__ __forceinline__ Dual operator+(float a, Dual b) { return mk(a + b.v, b.d); }
+__device__ __forceinline__ Dual operator-(float a, Dual b) { return mk(a - b.v, -b.d); }
+__device__ __forceinline__ Dual operator-(Dual b, float a) { return mk(b.v - a, b.d); }
+__device__ __forceinline__ Dual dsqrt(Dual a) {
+  const float s = sqrtf(a.v);
+  return mk(s, 0.5f * a.d / s);
+}
+__device__ __forceinline__ void dsincos(Dual a, Dual& s, Dual& c) {
+  float sv, cv;
+  sincosf(a.v, &sv, &cv);
+  s = mk(sv, cv * a.d);
+  c = mk(cv, -sv * a.d);
+}
+__device__ __forceinline__ Dual dpow(Dual a, float e) { return mk(powf(a.v, e), e * powf(a.v, e - 1.0f) * a.d); }
+
+// cutoff envelope f(r) and f'(r) on duals (same branches and formulas as cutoff_vd)
+__device__ __forceinline__ void cutoff_vd_dual(const EdgeParams& p, Dual r, Dual& f, Dual& df) {
+  if (p.cutoff_kind == B200_CUTOFF_XPLOR) {
+    const float ron2 = p.r_on * p.r_on, rc2 = p.r_cut * p.r_cut;
+    if (r.v < p.r_on) {
+      f = mk(1.0f);
+      df = mk(0.0f);
+    } else {
+      const float den = (rc2 - ron2) * (rc2 - ron2) * (rc2 - ron2);
+      const Dual r2 = r * r, a = rc2 - r2;
+      f = a * a * (rc2 + 2.0f * r2 - 3.0f * ron2) * (1.0f / den);
+      df = 12.0f * r * a * (ron2 - r2) * (1.0f / den);
+    }
+  } else {
+    const float pp = p.poly_p;
+    const Dual x = r * (1.0f / p.r_cut);
+    const float c0 = (pp + 1.0f) * (pp + 2.0f) * 0.5f, c1 = pp * (pp + 2.0f), c2 = pp * (pp + 1.0f) * 0.5f;
+    const Dual xp1 = dpow(x, pp - 1.0f), xp = xp1 * x, xq = xp * x, xr = xq * x;
+    f = 1.0f - c0 * xp + c1 * xq - c2 * xr;
+    df = (c1 * (pp + 1.0f) * xp - c0 * pp * xp1 - c2 * (pp + 2.0f) * xq) * (1.0f / p.r_cut);
+  }
+}
+
+constexpr int kEdge2Threads = 128;
+
+// one thread per edge; dk partial sums per block (fp64) -> partial[blockIdx][num_basis]
+__global__ void __launch_bounds__(kEdge2Threads)
+edge_embed_bwd2_kernel(EdgeParams p, long long E, const float* __restrict__ vec, const float* __restrict__ coeffs,
+                       const float* __restrict__ gY, const float* __restrict__ gemb, const float* __restrict__ a_,
+                       float* __restrict__ dvec2, float* __restrict__ dgY, float* __restrict__ dgemb,
+                       double* __restrict__ dk_partial) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  __shared__ double red[kEdge2Threads / 32][32];
+  float dk_local[32];
+#pragma unroll 1
+  for (int n = 0; n < p.num_basis; ++n) dk_local[n] = 0.f;
+  if (e < E) {
+    const Dual vx = mk(vec[e * 3], a_[e * 3]), vy = mk(vec[e * 3 + 1], a_[e * 3 + 1]), vz = mk(vec[e * 3 + 2], a_[e * 3 + 2]);
+    const Dual r = dsqrt(vx * vx + vy * vy + vz * vz);
+    const float s3 = 1.7320508075688772f, s5 = 2.23606797749979f, sa = 3.872983346207417f;
+    Dual n = mk(1.0f), ux = vx, uy = vy, uz = vz;
+    if (p.normalize_sph) {
+      n = r.v > 1e-12f ? r : mk(1e-12f);
+      ux = vx / n; uy = vy / n; uz = vz / n;
+    }
+    // ---- forward tangents: dS/d gY, dS/d gemb
+    if (dgY) {
+      float* o = dgY + e * 9;
+      const Dual x2z2 = ux * ux + uz * uz;
+      o[0] = 0.f;
+      o[1] = s3 * ux.d; o[2] = s3 * uy.d; o[3] = s3 * uz.d;
+      o[4] = (s5 * s3 * (ux * uz)).d;
+      o[5] = (s5 * s3 * (ux * uy)).d;
+      o[6] = (s5 * (uy * uy - 0.5f * x2z2)).d;
+      o[7] = (s5 * s3 * (uy * uz)).d;
+      o[8] = (s5 * 0.5f * s3 * (uz * uz - ux * ux)).d;
+    }
+    Dual f, df;
+    cutoff_vd_dual(p, r, f, df);
+    const float pre = 2.0f / p.r_cut;
+    Dual gx = mk(0.f), gy = mk(0.f), gz = mk(0.f);
+    // ---- radial part: reverse formulas of edge_embed_bwd_kernel on duals
+    Dual dr = mk(0.f);
+    for (int q = 0; q < p.num_basis; ++q) {
+      const float k = coeffs[q];
+      Dual s, c;
+      dsincos(k * r, s, c);
+      const Dual b = pre * s / r;
+      const Dual db = pre * (k * c * r - s) / (r * r);
+      if (dgemb) dgemb[e * p.num_basis + q] = (b * f).d;
+      if (gemb) {
+        const float ge = gemb[e * p.num_basis + q];
+        dr = dr + ge * (db * f + b * df);
+        dk_local[q] = ge * (pre * c * f).d;    // d emb_q / d k_q = pre cos(k r) f(r)
+      }
+    }
+    if (gemb) {
+      const Dual ir = mk(1.0f) / r;
+      gx = gx + dr * vx * ir; gy = gy + dr * vy * ir; gz = gz + dr * vz * ir;
+    }
+    if (gY) {
+      const float* g = gY + e * 9;
+      const float g1 = g[1], g2 = g[2], g3 = g[3], g4 = g[4], g5 = g[5], g6 = g[6], g7 = g[7], g8 = g[8];
+      Dual hx = s3 * g1 + (sa * g4) * uz + (sa * g5) * uy - (s5 * g6) * ux - (sa * g8) * ux;
+      Dual hy = s3 * g2 + (sa * g5) * ux + (2.0f * s5 * g6) * uy + (sa * g7) * uz;
+      Dual hz = s3 * g3 + (sa * g4) * ux - (s5 * g6) * uz + (sa * g7) * uy + (sa * g8) * uz;
+      if (p.normalize_sph) {
+        const Dual dot = ux * hx + uy * hy + uz * hz;
+        hx = (hx - ux * dot) / n; hy = (hy - uy * dot) / n; hz = (hz - uz * dot) / n;
+      }
+      gx = gx + hx; gy = gy + hy; gz = gz + hz;
+    }
+    dvec2[e * 3] = gx.d; dvec2[e * 3 + 1] = gy.d; dvec2[e * 3 + 2] = gz.d;
+  }
+  if (dk_partial) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int q = 0; q < p.num_basis; ++q) {
+      double v = (double)dk_local[q];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) red[warp][q] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < p.num_basis) {
+      double t = 0.0;
+      for (int w = 0; w < kEdge2Threads / 32; ++w) t += red[w][threadIdx.x];
+      dk_partial[(size_t)blockIdx.x * p.num_basis + threadIdx.x] = t;
+    }
+  }
+}
+
+// first-order coefficient gradient d k_n = sum_e gemb[e, n] (2 / r_c) cos(k_n r) f(r), same two-stage reduction
+__global__ void __launch_bounds__(kEdge2Threads)
+edge_embed_dk_kernel(EdgeParams p, long long E, const float* __restrict__ vec, const float* __restrict__ coeffs,
+                     const float* __restrict__ gemb, double* __restrict__ dk_partial) {
+  const long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  __shared__ double red[kEdge2Threads / 32][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float r = 1.f, f = 0.f, df;
+  if (e < E) {
+    const float vx = vec[e * 3], vy = vec[e * 3 + 1], vz = vec[e * 3 + 2];
+    r = sqrtf(vx * vx + vy * vy + vz * vz);
+    cutoff_vd(p, r, f, df);
+  }
+  for (int q = 0; q < p.num_basis; ++q) {
+    double v = e < E ? (double)(gemb[e * p.num_basis + q] * (2.0f / p.r_cut) * cosf(coeffs[q] * r) * f) : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][q] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < p.num_basis) {
+    double t = 0.0;
+    for (int w = 0; w < kEdge2Threads / 32; ++w) t += red[w][threadIdx.x];
+    dk_partial[(size_t)blockIdx.x * p.num_basis + threadIdx.x] = t;
+  }
+}
+
+__global__ void edge_dk_reduce_kernel(int nblocks, int nb, const double* __restrict__ partial, float* __restrict__ dk) {
+  __shared__ double sh[256];
+  const int q = blockIdx.x;
+  double s = 0.0;
+  for (int b = threadIdx.x; b < nblocks; b += blockDim.x) s += partial[(size_t)b * nb + q];
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) dk[q] = (float)sh[0];
+}
+
+int edge_embed_bwd2(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* gY,
+                    const float* gemb, const float* a, float* dvec2, float* dgY, float* dgemb, float* dk, cudaStream_t st) {
+  B200_REQUIRE(p.num_basis >= 1 && p.num_basis <= 32, "edge_embed_bwd2: num_basis out of range");
+  if (E == 0) {
+    if (dk) cudaMemsetAsync(dk, 0, sizeof(float) * p.num_basis, st);
+    return B200_OK;
+  }
+  const unsigned nblocks = (unsigned)((E + kEdge2Threads - 1) / kEdge2Threads);
+  double* partial = nullptr;
+  if (dk) {
+    keep_async_pool();
+    if (cudaMallocAsync((void**)&partial, sizeof(double) * (size_t)nblocks * p.num_basis, st) != cudaSuccess) {
+      set_error("edge_embed_bwd2: cudaMallocAsync failed");
+      return B200_ERR_CUDA;
+    }
+  }
+  edge_embed_bwd2_kernel<<<nblocks, kEdge2Threads, 0, st>>>(p, E, vec, coeffs, gY, gemb, a, dvec2, dgY, dgemb, partial);
+  if (dk) {
+    edge_dk_reduce_kernel<<<p.num_basis, 256, 0, st>>>((int)nblocks, p.num_basis, partial, dk);
+    cudaFreeAsync(partial, st);
+  }
+  return check_launch("edge_embed_bwd2", dk ? 2 : 1);
+}
+
+int edge_embed_dk(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* gemb, float* dk,
+                  cudaStream_t st) {
+  B200_REQUIRE(p.num_basis >= 1 && p.num_basis <= 32, "edge_embed_dk: num_basis out of range");
+  if (E == 0) {
+    cudaMemsetAsync(dk, 0, sizeof(float) * p.num_basis, st);
+    return B200_OK;
+  }
+  const unsigned nblocks = (unsigned)((E + kEdge2Threads - 1) / kEdge2Threads);
+  double* partial = nullptr;
+  keep_async_pool();
+  if (cudaMallocAsync((void**)&partial, sizeof(double) * (size_t)nblocks * p.num_basis, st) != cudaSuccess) {
+    set_error("edge_embed_dk: cudaMallocAsync failed");
+    return B200_ERR_CUDA;
+  }
+  edge_embed_dk_kernel<<<nblocks, kEdge2Threads, 0, st>>>(p, E, vec, coeffs, gemb, partial);
+  edge_dk_reduce_kernel<<<p.num_basis, 256, 0, st>>>((int)nblocks, p.num_basis, partial, dk);
+  cudaFreeAsync(partial, st);
+  return check_launch("edge_embed_dk", 2);
+}
+
 int edge_embed_fwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, float* len, float* Y,
                    float* emb, cudaStream_t st) {
   B200_REQUIRE(p.num_basis >= 1 && p.num_basis <= 32, "edge_embed_fwd: num_basis out of range");

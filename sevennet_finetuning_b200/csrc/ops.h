@@ -10,6 +10,10 @@ int edge_embed_fwd(const EdgeParams& p, long long E, const float* vec, const flo
                    float* emb, cudaStream_t st);
 int edge_embed_bwd(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
                    const float* demb, float* dvec, cudaStream_t st);
+int edge_embed_bwd2(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* gY,
+                    const float* gemb, const float* a, float* dvec2, float* dgY, float* dgemb, float* dk, cudaStream_t st);
+int edge_embed_dk(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* gemb, float* dk,
+                  cudaStream_t st);
 int edge_embed_bwd_full(const EdgeParams& p, long long E, const float* vec, const float* coeffs, const float* dY,
                         const float* demb, const float* dr, float* dvec, cudaStream_t st);
 int edge_embed_bwd_r(const EdgeParams& p, long long E, const float* vec, const float* dY, const float* dr, float* dvec,

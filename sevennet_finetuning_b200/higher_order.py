@@ -38,6 +38,57 @@ def _c(t):
     return t if (t.dtype == torch.float32 and t.is_contiguous()) else t.to(torch.float32).contiguous()
 
 
+# ---- edge embedding: spherical harmonics + Bessel x cutoff (sevenn/nn/edge_embedding.py:220-230) -------------------------
+class EdgeF(Function):
+    """(edge_vec, bessel coeffs) -> (edge_length, edge_attr Y[E,9], edge_embedding[E,nb])."""
+
+    @staticmethod
+    def forward(ctx, vec, coeffs, params):
+        ctx.save_for_backward(vec, coeffs)
+        ctx.params = params
+        ln, Y, emb = ops.edge_embed_fwd(params, _c(vec.detach()), _c(coeffs.detach()))
+        ctx.mark_non_differentiable(ln)     # edge_length is informational: no module of the path consumes it
+        return ln, Y, emb
+
+    @staticmethod
+    def backward(ctx, g_len, gY, gemb):
+        vec, coeffs = ctx.saved_tensors
+        dvec, dk = EdgeB.apply(vec, coeffs, gY, gemb, ctx.params)
+        return (dvec if ctx.needs_input_grad[0] else None), (dk if ctx.needs_input_grad[1] else None), None
+
+
+class EdgeB(Function):
+    """First reverse pass of EdgeF: (d edge_vec [E,3], d coeffs [nb]) from (d Y, d emb)."""
+
+    @staticmethod
+    def forward(ctx, vec, coeffs, gY, gemb, params):
+        ctx.save_for_backward(vec, coeffs, gY, gemb)
+        ctx.params = params
+        v, k = _c(vec.detach()), _c(coeffs.detach())
+        gY_ = None if gY is None else _c(gY.detach())
+        ge_ = None if gemb is None else _c(gemb.detach())
+        dvec = ops.edge_embed_bwd(params, v, k, gY_, ge_)
+        if ge_ is None or force_pass.active:   # the force pass consumes d edge_vec only
+            dk = torch.zeros_like(k)
+        else:
+            dk = ops.edge_embed_dk(params, v, k, ge_)
+        return dvec, dk
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, a_vec, a_k):
+        vec, coeffs, gY, gemb = ctx.saved_tensors
+        if a_k is not None and bool((a_k != 0).any()):
+            raise NotImplementedError('sevennet_b200: second derivative through the Bessel-coefficient gradient')
+        if a_vec is None:
+            return None, None, None, None, None
+        dvec2, dgY, dgemb, dk = ops.edge_embed_bwd2(ctx.params, _c(vec), _c(coeffs), None if gY is None else _c(gY),
+                                                    None if gemb is None else _c(gemb), _c(a_vec),
+                                                    want_dk=ctx.needs_input_grad[1] and gemb is not None)
+        return (dvec2 if ctx.needs_input_grad[0] else None), dk, (dgY if gY is not None else None), \
+               (dgemb if gemb is not None else None), None
+
+
 # ---- per-l block-diagonal linear (sevenn/nn/linear.py:46-49; e3nn o3.Linear / FullyConnectedNet layer) ------------------
 class LinF(Function):
     """y = L(x, W): rows x [n, in_dim], flat weight W."""

@@ -12,8 +12,10 @@ Scope of autograd.  In ``eval()`` mode: first order, per-edge intermediates reco
 In ``train()`` mode the modules switch to the Functions of ``higher_order.py``, which stay differentiable through their
 own backward pass: ``ForceStressOutputFromEdge`` then calls ``autograd.grad(..., create_graph=True)`` exactly like the
 reference (``sevenn/nn/force_output.py:165-170``) and a loss on forces / stress can be back-propagated to the parameters
-(``sevenn/train/trainer.py:173-186``).  The only non-kernel arithmetic on that path is the 17-values-per-edge spherical
-harmonics / Bessel / cutoff evaluation, whose second derivatives are taken by autograd over elementwise tensor ops.
+(``sevenn/train/trainer.py:173-186``).  Every forward, reverse and second-order evaluation on that path is a kernel of
+libsevennet_b200.so (the edge embedding's second derivatives are dual-number evaluations of its own formulas,
+``b200_edge_embed_bwd2``); tensor ops remain only for the loss, the rescale/reduce scalars and the force scatter, as in
+the reference.
 """
 import math
 from collections import OrderedDict
@@ -80,38 +82,13 @@ class _EdgeEmbedFn(torch.autograd.Function):
         dco = None
         if ctx.needs_input_grad[1] and gemb is not None:
             # d emb[e, n] / d k_n = (2 / r_c) cos(k_n r) f_cut(r)   (edge_embedding.py:114-116)
-            r = torch.linalg.norm(v, dim=-1, keepdim=True)
-            dco = (gemb * (2.0 / p.r_cut) * torch.cos(coeffs * r) * _cutoff_torch(p, r)).sum(0)
+            dco = ops.edge_embed_dk(p, v, ops._f32(coeffs), gemb)
         return dvec, dco, None
-
-
-def _cutoff_torch(p, r):
-    if p.cutoff_kind == B200_CUTOFF_XPLOR:
-        rc2, ron2, r2 = p.r_cut ** 2, p.r_on ** 2, r * r
-        f = (rc2 - r2) ** 2 * (rc2 + 2 * r2 - 3 * ron2) / (rc2 - ron2) ** 3
-        return torch.where(r < p.r_on, torch.ones_like(r), f)
-    x, pp = r / p.r_cut, p.poly_p
-    return 1 - (pp + 1) * (pp + 2) / 2 * x ** pp + pp * (pp + 2) * x ** (pp + 1) - pp * (pp + 1) / 2 * x ** (pp + 2)
 
 
 def _second_order(module):
     """train() mode with grad enabled: the forces must stay differentiable (force_output.py:168 create_graph=self.training)."""
     return module.training and torch.is_grad_enabled()
-
-
-def _edge_embed_tensor_ops(vec, coeffs, p):
-    """EdgeEmbedding.forward (edge_embedding.py:220-230) with elementwise tensor ops, same formulas and component order
-    as ``csrc/edge.cu``; used in train() mode only, where autograd must differentiate it twice."""
-    r = torch.sqrt((vec * vec).sum(-1))
-    u = vec / r.clamp_min(1e-12).unsqueeze(-1) if p.normalize_sph else vec
-    ux, uy, uz = u.unbind(-1)
-    s3, s5 = math.sqrt(3.0), math.sqrt(5.0)
-    Y = torch.stack([torch.ones_like(ux), s3 * ux, s3 * uy, s3 * uz, s5 * s3 * ux * uz, s5 * s3 * ux * uy,
-                     s5 * (uy * uy - 0.5 * (ux * ux + uz * uz)), s5 * s3 * uy * uz,
-                     s5 * 0.5 * s3 * (uz * uz - ux * ux)], dim=-1)
-    rr = r.unsqueeze(-1)
-    emb = (2.0 / p.r_cut) * torch.sin(coeffs * rr) / rr * _cutoff_torch(p, rr)
-    return r, Y, emb
 
 
 class _LinearFn(torch.autograd.Function):
@@ -269,7 +246,9 @@ class EdgeEmbedding(nn.Module):
             vec = data['edge_vec']
             if not vec.is_cuda:
                 raise RuntimeError('sevennet_b200: CPU tensor passed to a CUDA-only module')
-            ln, Y, emb = _edge_embed_tensor_ops(vec.to(torch.float32), self.basis_function.coeffs, self._params())
+            if vec.dtype != torch.float32:
+                vec = vec.to(torch.float32)
+            ln, Y, emb = ho.EdgeF.apply(vec, self.basis_function.coeffs, self._params())
         else:
             ln, Y, emb = _EdgeEmbedFn.apply(data['edge_vec'], self.basis_function.coeffs, self._params())
         data['edge_length'], data['edge_attr'], data['edge_embedding'] = ln, Y, emb

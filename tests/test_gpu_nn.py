@@ -219,6 +219,52 @@ def test_convolution_family_second_order(muls, lout):
         assert (a.double().cpu() - b).abs().max() <= 5e-5 * b.abs().max(), name
 
 
+@pytest.mark.parametrize('cutoff', ['xplor', 'poly'])
+def test_edge_embedding_second_order(cutoff):
+    """EdgeF / EdgeB (b200_edge_embed_bwd2: dual-number evaluation of the embedding's own formulas): gradient of a
+    functional of d/d edge_vec, with respect to edge_vec, the Bessel coefficients and the incoming gradients, against
+    float64 autograd through the oracle's EdgeEmbedding (sevenn/nn/edge_embedding.py:114-116,138-145,163-173,190-198)."""
+    from oracle import refnn
+    from sevennet_finetuning_b200 import higher_order as ho
+    from sevennet_finetuning_b200._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, EdgeParams
+    dev = torch.device('cuda:0')
+    rng = np.random.default_rng(8)
+    E = 257
+    d = rng.normal(size=(E, 3))
+    d = d / np.linalg.norm(d, axis=1, keepdims=True) * rng.uniform(0.8, 4.95, (E, 1))   # both branches of the envelope
+    torch.set_default_dtype(torch.float64)
+    try:
+        env = refnn.XPLORCutoff(5.0, 4.5) if cutoff == 'xplor' else refnn.PolynomialCutoff(5.0, 6)
+        ref = refnn.EdgeEmbedding(refnn.BesselBasis(5.0, 8), env, refnn.SphericalEncoding(2, 1, normalize=True)).double()
+        v64 = torch.tensor(d, requires_grad=True)
+        gY64 = torch.tensor(rng.normal(size=(E, 9)), requires_grad=True)
+        ge64 = torch.tensor(rng.normal(size=(E, 8)), requires_grad=True)
+        c64 = torch.tensor(rng.normal(size=(E, 3)))
+        o = ref({'edge_vec': v64})
+        k64 = ref.basis_function.coeffs
+        (dv,) = torch.autograd.grad((o['edge_attr'] * gY64).sum() + (o['edge_embedding'] * ge64).sum(), [v64], create_graph=True)
+        S = (dv * c64).sum() + (dv ** 2).sum()
+        want = torch.autograd.grad(S, [v64, k64, gY64, ge64])
+        dv_ref = dv.detach()
+    finally:
+        torch.set_default_dtype(torch.float32)
+    p = EdgeParams(8, B200_CUTOFF_XPLOR if cutoff == 'xplor' else B200_CUTOFF_POLY, 1, 5.0, 4.5, 6.0)
+    v = v64.detach().to(dev, torch.float32).requires_grad_(True)
+    k = k64.detach().to(dev, torch.float32).requires_grad_(True)
+    gY = gY64.detach().to(dev, torch.float32).requires_grad_(True)
+    ge = ge64.detach().to(dev, torch.float32).requires_grad_(True)
+    ln, Y, emb = ho.EdgeF.apply(v, k, p)
+    (dv32,) = torch.autograd.grad((Y * gY).sum() + (emb * ge).sum(), [v], create_graph=True)
+    S32 = (dv32 * c64.to(dev, torch.float32)).sum() + (dv32 ** 2).sum()
+    got = torch.autograd.grad(S32, [v, k, gY, ge])
+    assert (dv32.detach().double().cpu() - dv_ref).abs().max() <= 2e-5 * dv_ref.abs().max()
+    for a, b, name in zip(got, want, ['edge_vec', 'coeffs', 'gY', 'gemb']):
+        b = b.clone()
+        if name == 'gY':
+            b[:, 0] = 0     # Y[:, 0] is the constant 1: its incoming gradient is never read
+        assert (a.double().cpu() - b).abs().max() <= 1e-4 * b.abs().max(), name
+
+
 def test_linear_and_gate_families_second_order():
     """LinF / LinT / LinWG and GateF / GateB against float64 tensor-op restatements (e3nn Linear: x W / sqrt(fan_in) per
     l block; Gate: c*silu on scalars and gates, gates multiply the l > 0 channels)."""
