@@ -84,16 +84,28 @@ class EWCLoss(LossDefinition):
         self.fisher_dict = {k: v.to(device) for k, v in self.fisher_dict.items()}
         self.opt_params_dict = {k: v.to(device) for k, v in self.opt_params_dict.items()}
         self.device = device
+        self._flat_key = None
 
     def get_loss(self, batch_data, model=None):
         if model is None:
             raise ValueError('EWC requires model to compute loss')
-        loss = torch.zeros(1, device=self.device)
+        # same sum as the reference's per-parameter loop (loss.py:259-264), evaluated on one flattened vector: a few
+        # kernels per step instead of several per parameter tensor
+        names, params = [], []
         for name, p in model.named_parameters():
             name = name[7:] if name.startswith('module.') else name   # DDP prefix
             if name in self.fisher_dict and name in self.opt_params_dict:
-                loss = loss + torch.sum(self.fisher_dict[name] * (p - self.opt_params_dict[name]) ** 2)
-        return loss
+                names.append(name)
+                params.append(p)
+        if not params:
+            return torch.zeros(1, device=self.device)
+        key = tuple(names)
+        if getattr(self, '_flat_key', None) != key:
+            self._flat_key = key
+            self._flat_fisher = torch.cat([self.fisher_dict[n].reshape(-1) for n in names])
+            self._flat_opt = torch.cat([self.opt_params_dict[n].reshape(-1) for n in names])
+        d = torch.cat([p.reshape(-1) for p in params]) - self._flat_opt
+        return torch.sum(self._flat_fisher * d * d).reshape(1)
 
 
 def get_loss_functions(loss='huber', loss_param=None, force_loss_weight=1.0, is_train_stress=True, stress_loss_weight=0.01,
@@ -136,6 +148,10 @@ def collate(graphs, device=None, pin=False):
         out['stress'] = torch.stack([torch.as_tensor(g['stress'], dtype=torch.float32).reshape(6) for g in graphs])
     if pin:
         out = {k: v.pin_memory() for k, v in out.items()}
+    # edges of every structure sorted by their centre atom (what ase / the CUDA cell list emit) stay sorted under the
+    # node offsets: let the convolution skip its sortedness check (nn._graph_of)
+    if all(bool((torch.as_tensor(g['edge_index'])[0][1:] >= torch.as_tensor(g['edge_index'])[0][:-1]).all()) for g in graphs):
+        out['_b200_dst_sorted'] = True
     if device is not None:
         out = to_device(out, device)
     return out
@@ -144,13 +160,13 @@ def collate(graphs, device=None, pin=False):
 def to_device(batch, device):
     """``batch.to(device, non_blocking=True)`` (trainer.py:176) + the requires_grad the dataset sets on edge_vec
     (``sevenn/train/dataload.py`` via ``AtomGraphData``; ``util.py:243``)."""
-    out = {k: v.to(device, non_blocking=True) for k, v in batch.items()}
+    out = {k: (v.to(device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in batch.items()}
     out['edge_vec'].requires_grad_(True)
     return out
 
 
 def batch_bytes(batch):
-    return int(sum(v.numel() * v.element_size() for v in batch.values()))
+    return int(sum(v.numel() * v.element_size() for v in batch.values() if torch.is_tensor(v)))
 
 
 def shard_indices(n_items, rank, world_size, seed=0, epoch=0, shuffle=True):

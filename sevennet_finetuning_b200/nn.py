@@ -44,7 +44,9 @@ def _graph_of(data):
         n_src = n
     E = ei.shape[1]
     perm = None
-    if E > 1 and bool((dst64[1:] < dst64[:-1]).any()):
+    # a loader that built the edges itself can vouch for their order (finetune.collate) and spare the device->host
+    # round trip of the check, which would otherwise stall the launch queue once per forward
+    if E > 1 and data.get('_b200_dst_sorted') is not True and bool((dst64[1:] < dst64[:-1]).any()):
         perm = torch.argsort(dst64, stable=True)
         dst64, src64 = dst64[perm], src64[perm]
     dst, src = dst64.to(torch.int32).contiguous(), src64.to(torch.int32).contiguous()
@@ -84,6 +86,15 @@ class _EdgeEmbedFn(torch.autograd.Function):
             # d emb[e, n] / d k_n = (2 / r_c) cos(k_n r) f_cut(r)   (edge_embedding.py:114-116)
             dco = ops.edge_embed_dk(p, v, ops._f32(coeffs), gemb)
         return dvec, dco, None
+
+
+def _num_structures(data):
+    """Number of structures of a batch: the reference reads ``int(batch.max()) + 1`` (linear.py:79, force_output.py:204),
+    a device->host synchronisation; the per-structure ``num_atoms`` vector of a collated batch carries the same number."""
+    na = data.get('num_atoms')
+    if torch.is_tensor(na) and na.dim() == 1 and na.numel() >= 1:
+        return int(na.numel())
+    return int(data['batch'].max()) + 1
 
 
 def _second_order(module):
@@ -461,7 +472,7 @@ class AtomReduce(nn.Module):
     def forward(self, data):
         src = data[self.key_input].squeeze(1)
         if self._is_batch_data:
-            size = int(data['batch'].max()) + 1
+            size = _num_structures(data)
             out = torch.zeros(size, dtype=src.dtype, device=src.device)
             out.scatter_reduce_(0, data['batch'], src, reduce='sum')
             data[self.key_output] = out * self.constant
@@ -504,7 +515,7 @@ class ForceStressOutputFromEdge(nn.Module):
         vir = torch.cat([diag, s12.unsqueeze(-1), s23.unsqueeze(-1), s31.unsqueeze(-1)], dim=-1)
         if self._is_batch_data:
             batch = data['batch']
-            nb = int(batch.max()) + 1
+            nb = _num_structures(data)
             per = torch.zeros(nb, 6, dtype=vir.dtype, device=vir.device)
             per.index_add_(0, batch[ei[1]], vir)
             data[self.key_stress] = -per / data[self.key_cell_volume].view(-1, 1)

@@ -32,7 +32,8 @@ def test_collate_offsets_and_keys():
     hi = torch.tensor([5] * 12 + [12] * 20 + [15] * 4)
     assert bool(((b['edge_index'] >= lo) & (b['edge_index'] < hi)).all())
     assert torch.equal(b['edge_index'][:, 12:32] - 5, gs[1]['edge_index'])
-    assert ft.batch_bytes(b) == sum(v.numel() * v.element_size() for v in b.values())
+    assert ft.batch_bytes(b) == sum(v.numel() * v.element_size() for v in b.values() if torch.is_tensor(v))
+    assert '_b200_dst_sorted' not in b      # random edge order: no promise made
 
 
 def test_loss_definitions_match_reference_formulas():
@@ -111,7 +112,7 @@ def _worker(rank, world, port, q):
     b = ft.to_device(ft.collate([graphs[i] for i in mine]), 'cpu')
     m = ft.to_device(ft.collate([mem[i] for i in mine]), 'cpu')
     l, lm = tr.run_one_step(b, m)
-    q.put((rank, [p.detach().clone() for p in tr.model.module.parameters()], float(l), float(lm)))
+    q.put((rank, [p.detach().tolist() for p in tr.model.module.parameters()], float(l), float(lm)))   # plain lists: no fd passing
     dist.barrier()
     dist.destroy_process_group()
 
@@ -133,7 +134,7 @@ def test_rehearsal_step_under_ddp_gloo_world2():
         p.join(timeout=60)
         assert p.exitcode == 0
     for a, b in zip(res[0][1], res[1][1]):
-        assert torch.equal(a, b)
+        assert a == b
     # single-process restatement: average of per-rank gradients, accumulated across the two backward calls
     torch.manual_seed(0)
     model = _Toy()
@@ -153,4 +154,4 @@ def test_rehearsal_step_under_ddp_gloo_world2():
             p.grad = acc[k].clone()
         opt.step()
     for a, b in zip(res[0][1], model.parameters()):
-        assert torch.allclose(a, b.detach(), rtol=1e-5, atol=1e-7), (a, b)
+        assert torch.allclose(torch.tensor(a), b.detach(), rtol=1e-5, atol=1e-7), (a, b)
