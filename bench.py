@@ -221,7 +221,7 @@ def finetune_reference_cpu(n_struct, steps, warmup):
     def step():
         opt.zero_grad()
         for k, b in enumerate((tb, mb)):
-            d = {kk: v.clone() for kk, v in b.items()}
+            d = {kk: (v.clone() if torch.is_tensor(v) else v) for kk, v in b.items()}
             d['edge_vec'].requires_grad_(True)
             loss = ft.total_loss(lf, m(d), m, 'cpu')
             loss.backward()
