@@ -74,6 +74,24 @@ int b200_radial_mlp_fwd(const MlpDesc* d, int64_t n_edges, const float* emb, con
 int b200_radial_mlp_bwd(const MlpDesc* d, int64_t n_edges, const float* emb, const float* W0, const float* W1,
                         const float* W2, const float* d_weight, float* d_emb, int accumulate, void* stream);
 
+/* ---- tabulated radial weights (MD path; same reference lines as the radial MLP) ----------------------------------
+ * w_k(r) = weight_nn(BesselBasis(r) * cutoff(r))_k depends on the edge length only.  For fixed parameters it is evaluated
+ * once in float64 on a uniform grid (spacing ~ r_cut / 4000, the XPLOR switching radius on a node) together with its exact
+ * derivative and stored per interval as the coefficients of the cubic Hermite interpolant, table[n_intervals][4][wn]
+ * (the slope is then as accurate as the value: no fp32 differences of neighbouring nodes).  Every edge evaluates its cubic
+ * (b200_radial_table_fwd) and the reverse pass contracts d w with the derivative of the same spline
+ * (b200_radial_table_bwd: d_r[E] (+)= sum_k d_weight[e,k] * d w_k/d r).  b200_model_compute uses this unless
+ * B200_RADIAL_TABLE=0; training passes use the explicit MLP above. */
+size_t b200_radial_table_floats(const EdgeParams* p, const MlpDesc* d);
+int b200_radial_table_build(const EdgeParams* p, const MlpDesc* d, const float* bessel_coeffs, const float* W0,
+                            const float* W1, const float* W2, float* table, void* stream);
+/* order: edge ids sorted by grid interval (NULL = natural order); sorted visiting keeps the table rows in L1 */
+int b200_radial_table_fwd(const EdgeParams* p, const MlpDesc* d, int64_t n_edges, const float* edge_length,
+                          const int32_t* order, const float* table, float* weight, void* stream);
+int b200_radial_table_bwd(const EdgeParams* p, const MlpDesc* d, int64_t n_edges, const float* edge_length,
+                          const int32_t* order, const float* table, const float* d_weight, float* d_r, int accumulate,
+                          void* stream);
+
 /* ---- convolution: sevenn/nn/convolution.py:105-121 (TensorProduct 'uvu' + message_gather + /denominator) ----
  * x irreps m0x0e+m1x1e+m2x2e, filter 0e+1e+2e, output keeps l3 <= lout (0 or 2); instruction and slot
  * order as built by IrrepsConvolution.__init__ (:72-95).  Edges are given as a CSR sorted by

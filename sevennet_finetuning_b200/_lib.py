@@ -54,6 +54,10 @@ SIGNATURES = {
     'b200_radial_mlp_fwd': (_i, [_P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_radial_mlp_bwd': (_i, [_P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     'b200_edge_embed_bwd_r': (_i, [_P(EdgeParams), _i64, _vp, _vp, _vp, _vp, _vp]),
+    'b200_radial_table_floats': (_sz, [_P(EdgeParams), _P(MlpDesc)]),
+    'b200_radial_table_build': (_i, [_P(EdgeParams), _P(MlpDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_radial_table_fwd': (_i, [_P(EdgeParams), _P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp]),
+    'b200_radial_table_bwd': (_i, [_P(EdgeParams), _P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     'b200_fused_supported': (_i, [_i, _i, _i, _i, _P(MlpDesc)]),
     'b200_fused_radial_bytes': (_sz, [_i64]),
     'b200_fused_radial': (_i, [_P(EdgeParams), _P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libsevennet_b200.so')
-SOURCES = ['capi.cu', 'conv.cu', 'edge.cu', 'radial.cu', 'radial_tc.cu', 'fused.cu', 'linear.cu', 'linear_tc.cu', 'node.cu', 'graph.cu', 'engine.cu']
+SOURCES = ['capi.cu', 'conv.cu', 'edge.cu', 'radial.cu', 'radial_tc.cu', 'radial_table.cu', 'fused.cu', 'linear.cu', 'linear_tc.cu', 'node.cu', 'graph.cu', 'engine.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '--use_fast_math=false', '-Xcompiler', '-fPIC', '-Xcompiler', '-O2']
 

@@ -55,6 +55,22 @@ int b200_edge_embed_dk(const EdgeParams* p, int64_t E, const float* vec, const f
   B200_REQUIRE(p && dk && (E == 0 || (vec && coeffs && gemb)), "edge_embed_dk: null argument");
   return edge_embed_dk(*p, E, vec, coeffs, gemb, dk, ST(stream));
 }
+size_t b200_radial_table_floats(const EdgeParams* p, const MlpDesc* d) { return (p && d) ? radial_table_floats(*p, *d) : 0; }
+int b200_radial_table_build(const EdgeParams* p, const MlpDesc* d, const float* coeffs, const float* W0, const float* W1,
+                            const float* W2, float* table, void* stream) {
+  B200_REQUIRE(p && d && coeffs && W0 && W1 && W2 && table, "radial_table_build: null argument");
+  return radial_table_build(*p, *d, coeffs, W0, W1, W2, table, ST(stream));
+}
+int b200_radial_table_fwd(const EdgeParams* p, const MlpDesc* d, int64_t E, const float* len, const int32_t* order,
+                          const float* table, float* w, void* stream) {
+  B200_REQUIRE(p && d && (E == 0 || (len && table && w)), "radial_table_fwd: null argument");
+  return radial_table_fwd(*p, *d, E, len, order, table, w, ST(stream));
+}
+int b200_radial_table_bwd(const EdgeParams* p, const MlpDesc* d, int64_t E, const float* len, const int32_t* order,
+                          const float* table, const float* dw, float* dr, int accumulate, void* stream) {
+  B200_REQUIRE(p && d && (E == 0 || (len && table && dw && dr)), "radial_table_bwd: null argument");
+  return radial_table_bwd(*p, *d, E, len, order, table, dw, dr, accumulate, ST(stream));
+}
 int b200_edge_embed_bwd_r(const EdgeParams* p, int64_t E, const float* vec, const float* dY, const float* dr, float* dvec,
                           void* stream) {
   B200_REQUIRE(p && (E == 0 || (vec && dvec)), "edge_embed_bwd_r: null argument");

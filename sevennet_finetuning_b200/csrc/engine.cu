@@ -85,6 +85,7 @@ struct Layer {
   LinDesc sc, si1, si2;
   int lout;
   bool fused;   // radial layer + convolution run as the fused tcgen05 kernels (fused.cu)
+  bool table;   // per-edge weights interpolated from the tabulated radial function (radial_table.cu)
 };
 
 }  // namespace b200
@@ -101,6 +102,8 @@ struct B200Model {
   // optional per-category device timing (CUDA events on the compute stream)
   bool timing = false;
   bool split_bwd_x = false;   // B200_SPLIT_BWD_X=1: d x[src] by the separate source-sorted kernel (deterministic sums)
+  std::vector<float*> tables; // per layer: tabulated radial weights (device), rebuilt when a parameter changes
+  bool tables_dirty = true;
   std::vector<cudaEvent_t> ev;
   std::vector<int> ev_cat;
   size_t ev_used = 0;
@@ -177,7 +180,9 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.sc = make_linear(L.in, L.gin);
     L.si1 = make_linear(L.in, L.in);
     L.si2 = make_linear(L.msg, L.gin);
-    L.fused = fused_supported(L.conv, L.mlp) && getenv("B200_FUSED") && atoi(getenv("B200_FUSED")) != 0;   // opt-in
+    const bool fused_env = getenv("B200_FUSED") && atoi(getenv("B200_FUSED")) != 0;   // opt-in
+    L.fused = fused_env && fused_supported(L.conv, L.mlp);
+    L.table = !fused_env && radial_table_supported(L.mlp) && !(getenv("B200_RADIAL_TABLE") && atoi(getenv("B200_RADIAL_TABLE")) == 0);
     m->layers.push_back(L);
     m->split_bwd_x = getenv("B200_SPLIT_BWD_X") && atoi(getenv("B200_SPLIT_BWD_X")) != 0;
     const std::string s = std::to_string(t);
@@ -222,6 +227,7 @@ extern "C" int b200_model_set_param(B200Model* m, const char* name, const float*
     set_error("model_set_param: cudaMemcpy failed");
     return B200_ERR_CUDA;
   }
+  m->tables_dirty = true;
   const std::string nm(name);
   const std::string suffix = "_convolution.denominator";
   if (nm.size() > suffix.size() && nm.compare(nm.size() - suffix.size(), suffix.size(), suffix) == 0)
@@ -232,6 +238,7 @@ extern "C" int b200_model_set_param(B200Model* m, const char* name, const float*
 extern "C" void b200_model_destroy(B200Model* m) {
   if (!m) return;
   for (auto& kv : m->params) cudaFree(kv.second.first);
+  for (auto t : m->tables) cudaFree(t);
   for (auto e : m->ev) cudaEventDestroy(e);
   delete m;
 }
@@ -247,10 +254,10 @@ struct Plan {
   }
 };
 struct Buffers {
-  float *Y, *emb, *dY, *demb, *ddr, *dvec, *dw, *x[2], *conv_out, *g_x[2], *g_gin, *g_conv, *h, *s, *g_h, *g_s, *virial_atom;
+  float *Y, *emb, *len, *dY, *demb, *ddr, *dvec, *dw, *x[2], *conv_out, *g_x[2], *g_gin, *g_conv, *h, *s, *g_h, *g_s, *virial_atom;
   std::vector<float*> w, xs, gin, rad;
-  int *rrowptr, *eid;
-  void* tws;
+  int *rrowptr, *eid, *rorder;
+  void *tws, *tws2;
 };
 void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buffers& b) {
   const int N = NL;
@@ -265,6 +272,7 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
   const int nb = m->cfg.edge.num_basis;
   b.Y = p.take<float>((size_t)E * 9);
   b.emb = p.take<float>((size_t)E * nb);
+  b.len = p.take<float>((size_t)E);
   b.dY = p.take<float>((size_t)E * 9);
   b.demb = p.take<float>((size_t)E * nb);
   b.ddr = p.take<float>((size_t)E);
@@ -290,6 +298,9 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
   b.rrowptr = p.take<int>((size_t)NA + 1);
   b.eid = p.take<int>((size_t)E);
   b.tws = p.take<char>(transpose_workspace_bytes(NA, E));
+  // edges sorted by the interval of the tabulated radial functions (radial_table.cu)
+  b.rorder = p.take<int>((size_t)E);
+  b.tws2 = p.take<char>(radial_table_order_bytes(E));
 }
 
 __global__ void rescale_bwd_kernel(int n, const int* __restrict__ types, const float* __restrict__ scale, int species_wise,
@@ -350,9 +361,32 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   const float* coeffs = P(m, "edge_embedding.basis_function.coeffs");
   const int nl = c.n_layers;
 
+  // tabulated radial functions: rebuilt (float64, a few hundred microseconds per layer) after a parameter change
+  if (m->tables_dirty) {
+    if (m->tables.empty()) m->tables.assign(nl, nullptr);
+    for (int t = 0; t < nl; ++t) {
+      const Layer& L = m->layers[t];
+      if (!L.table) continue;
+      const std::string s = std::to_string(t);
+      if (!m->tables[t] && cudaMalloc(&m->tables[t], sizeof(float) * radial_table_floats(c.edge, L.mlp)) != cudaSuccess) {
+        set_error("model_compute: cudaMalloc of the radial table failed");
+        return B200_ERR_CUDA;
+      }
+      OP(CAT_MLP_FWD, radial_table_build(c.edge, L.mlp, coeffs, P(m, s + "_convolution.weight_nn.layer0.weight"),
+                                         P(m, s + "_convolution.weight_nn.layer1.weight"),
+                                         P(m, s + "_convolution.weight_nn.layer2.weight"), m->tables[t], st));
+    }
+    m->tables_dirty = false;
+  }
+
   // ---------------- forward ----------------
-  OP(CAT_EDGE, edge_embed_fwd(c.edge, E, edge_vec, coeffs, nullptr, b.Y, b.emb, st));
+  OP(CAT_EDGE, edge_embed_fwd(c.edge, E, edge_vec, coeffs, b.len, b.Y, b.emb, st));
   OP(CAT_EDGE, csr_transpose(NA, E, src, b.tws, b.rrowptr, b.eid, st));
+  bool any_table = false;
+  for (const Layer& L : m->layers) any_table = any_table || L.table;
+  if (any_table) {   // counting sort of the edges by table interval, once per call for all layers and both passes
+    OP(CAT_EDGE, radial_table_order(c.edge, E, b.len, b.tws2, b.rorder, st));
+  }
   float* x = b.x[0];
   float* xn = b.x[1];
   OP(CAT_NODE, embed_fwd(NA, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
@@ -373,7 +407,8 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       OP(CAT_MLP_FWD, fused_radial(c.edge, L.mlp, E, edge_vec, coeffs, W0, W1, b.rad[t], st));
       OP(CAT_CONV_FWD, fused_conv_fwd(L.conv, N, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, denom[t], b.conv_out, st));
     } else {
-      OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, W0, W1, W2, b.w[t], st));
+      if (L.table) OP(CAT_MLP_FWD, radial_table_fwd(c.edge, L.mlp, E, b.len, b.rorder, m->tables[t], b.w[t], st));
+      else OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, W0, W1, W2, b.w[t], st));
       OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
     }
     OP(CAT_NODE, irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
@@ -394,7 +429,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   float* g = b.g_x[0];
   float* gp = b.g_x[1];
   OP(CAT_NODE, irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
-  bool any_fused = false, any_plain = false;
+  bool dy_written = false, ddr_written = false, demb_written = false;   // which per-edge gradient buffers hold a sum already
   for (int t = nl - 1; t >= 0; --t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
@@ -407,14 +442,20 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     float* dxs = t > 0 ? b.conv_out : nullptr;
     if (L.fused) {
       OP(CAT_CONV_BWD_EDGE, fused_conv_bwd(L.conv, NA, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, b.g_conv, denom[t], dxs, b.dY,
-                                           b.ddr, any_fused ? 1 : 0, st));
-      any_fused = true;
+                                           b.ddr, ddr_written ? 1 : 0, st));
+      dy_written = ddr_written = true;
     } else {
       // d weight, d Y and (t > 0) d x[src] in one pass: the source rows are accumulated with RED.ADD
       OP(CAT_CONV_BWD_EDGE, conv_bwd_edge_x(L.conv, N, NA, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw,
-                                            b.dY, (any_fused || any_plain) ? 1 : 0, m->split_bwd_x ? nullptr : dxs, st));
-      OP(CAT_MLP_BWD, radial_mlp_bwd(L.mlp, E, b.emb, W0, W1, W2, b.dw, b.demb, any_plain ? 1 : 0, st));
-      any_plain = true;
+                                            b.dY, dy_written ? 1 : 0, m->split_bwd_x ? nullptr : dxs, st));
+      dy_written = true;
+      if (L.table) {   // d E / d r directly: joins the per-edge radial gradient of the fused layers (b.ddr)
+        OP(CAT_MLP_BWD, radial_table_bwd(c.edge, L.mlp, E, b.len, b.rorder, m->tables[t], b.dw, b.ddr, ddr_written ? 1 : 0, st));
+        ddr_written = true;
+      } else {
+        OP(CAT_MLP_BWD, radial_mlp_bwd(L.mlp, E, b.emb, W0, W1, W2, b.dw, b.demb, demb_written ? 1 : 0, st));
+        demb_written = true;
+      }
     }
     if (t > 0) {
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
@@ -426,8 +467,8 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       std::swap(g, gp);
     }
   }
-  OP(CAT_EDGE, edge_embed_bwd_full(c.edge, E, edge_vec, coeffs, b.dY, any_plain ? b.demb : nullptr,
-                                   any_fused ? b.ddr : nullptr, b.dvec, st));
+  OP(CAT_EDGE, edge_embed_bwd_full(c.edge, E, edge_vec, coeffs, b.dY, demb_written ? b.demb : nullptr,
+                                   ddr_written ? b.ddr : nullptr, b.dvec, st));
   OP(CAT_FORCE, force_virial(NA, rowptr, b.rrowptr, b.eid, edge_vec, b.dvec, force, b.virial_atom, st));
   HALO(B200_HALO_FORCE, -1, force, 3);
   OP(CAT_NODE, colsum(NA, 6, b.virial_atom, virial, st));   // per-source rows (force_output.py:186-213): ghosts included

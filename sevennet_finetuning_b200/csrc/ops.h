@@ -37,6 +37,24 @@ int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, 
                   const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
                   cudaStream_t st);
 
+// tabulated radial weights (radial_table.cu): the MD path's replacement of the per-edge MLP evaluation
+struct RadialTableGrid {
+  double h;   // grid spacing
+  int n;      // number of intervals; nodes 0..n
+};
+RadialTableGrid radial_table_grid(const EdgeParams& p);
+size_t radial_table_floats(const EdgeParams& p, const MlpDesc& d);
+bool radial_table_supported(const MlpDesc& d);
+int radial_table_build(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
+                       const float* W2, float* T, cudaStream_t st);
+size_t radial_table_order_bytes(long long E);
+int radial_table_order(const EdgeParams& p, long long E, const float* len, void* ws, int* order, cudaStream_t st);   // edge ids sorted by interval
+// order: edge ids sorted by interval (nullptr = natural order)
+int radial_table_fwd(const EdgeParams& p, const MlpDesc& d, long long E, const float* len, const int* order, const float* T,
+                     float* w, cudaStream_t st);
+int radial_table_bwd(const EdgeParams& p, const MlpDesc& d, long long E, const float* len, const int* order, const float* T,
+                     const float* dw, float* dr, int accumulate, cudaStream_t st);
+
 // fused path (fused.cu): radial operand tiles, then convolution forward / backward with the weights kept in TMEM
 bool fused_supported(const ConvDesc& d, const MlpDesc& m);
 size_t fused_radial_bytes(long long E);

@@ -382,3 +382,33 @@ def edge_embed_bwd2(params, vec, coeffs, gY, gemb, a, want_dk=True):
     check(lib().b200_edge_embed_bwd2(C.byref(params), E, _p(vec), _p(coeffs), _p(gY), _p(gemb), _p(a), _p(dvec2), _p(dgY),
                                      _p(dgemb), _p(dk), _stream()), 'edge_embed_bwd2')
     return dvec2, dgY, dgemb, dk
+
+
+# ---- tabulated radial weights (MD path) -----------------------------------------------------------------------------------
+def radial_table_build(params, coeffs, W0, W1, W2):
+    d = MlpDesc(W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1])
+    n = lib().b200_radial_table_floats(C.byref(params), C.byref(d))
+    T = torch.empty(n, dtype=torch.float32, device=W0.device)
+    check(lib().b200_radial_table_build(C.byref(params), C.byref(d), _p(coeffs), _p(W0), _p(W1), _p(W2), _p(T), _stream()),
+          'radial_table_build')
+    return T
+
+
+@_timed
+def radial_table_fwd(params, wn, nb, h1, h2, length, T, order=None):
+    d = MlpDesc(nb, h1, h2, wn)
+    w = torch.empty(length.shape[0], wn, dtype=torch.float32, device=length.device)
+    check(lib().b200_radial_table_fwd(C.byref(params), C.byref(d), length.shape[0], _p(length), _p(order), _p(T), _p(w),
+                                      _stream()), 'radial_table_fwd')
+    return w
+
+
+@_timed
+def radial_table_bwd(params, wn, nb, h1, h2, length, T, dw, dr=None, order=None):
+    d = MlpDesc(nb, h1, h2, wn)
+    acc = dr is not None
+    if dr is None:
+        dr = torch.empty(length.shape[0], dtype=torch.float32, device=length.device)
+    check(lib().b200_radial_table_bwd(C.byref(params), C.byref(d), length.shape[0], _p(length), _p(order), _p(T), _p(dw), _p(dr),
+                                      int(acc), _stream()), 'radial_table_bwd')
+    return dr

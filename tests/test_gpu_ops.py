@@ -324,3 +324,41 @@ def test_fused_convolution_fwd_bwd(dev, muls, lout, name, E):
     assert _rel(dr, r.grad) < 2e-5, name
     dx2, dY2, dr2 = ops.fused_conv_bwd(muls, lout, d32, s32, x32, Y32, rad, Ws[2], g32, denom, dY=dY.clone(), dr=dr.clone())
     assert _rel(dr2, 2 * r.grad) < 2e-5 and _rel(dY2[:, 1:], 2 * Yr.grad[:, 1:]) < 2e-5, name
+
+
+@pytest.mark.parametrize('cutoff,wn', [('xplor', 960), ('xplor', 224), ('poly', 384)])
+def test_radial_table_matches_float64_mlp(dev, cutoff, wn):
+    """Tabulated radial weights (b200_radial_table_*): w(r) and sum_k dw_k dw_k/dr against the float64 oracle chain
+    BesselBasis * cutoff -> FullyConnectedNet (edge_embedding.py:114-116,138-173; convolution.py:97-106)."""
+    from oracle import refnn
+    from sevennet_finetuning_b200 import ops
+    from sevennet_finetuning_b200._lib import B200_CUTOFF_POLY, B200_CUTOFF_XPLOR, EdgeParams
+    rng = np.random.default_rng(11)
+    E = 4001
+    r = np.concatenate([rng.uniform(0.6, 4.9999, E - 4), [4.5, 4.5 - 1e-6, 4.5 + 1e-6, 4.99999]])
+    r = r.astype(np.float32).astype(np.float64)   # the kernel sees fp32 lengths
+    torch.set_default_dtype(torch.float64)
+    try:
+        torch.manual_seed(3)
+        env = refnn.XPLORCutoff(5.0, 4.5) if cutoff == 'xplor' else refnn.PolynomialCutoff(5.0, 6)
+        basis = refnn.BesselBasis(5.0, 8).double()
+        net = refnn.FullyConnectedNet([8, 64, 64, wn], 'silu').double()
+        r64 = torch.tensor(r, requires_grad=True)
+        w64 = net(basis(r64) * env(r64).unsqueeze(-1))
+        g64 = torch.tensor(rng.normal(size=(E, wn)))
+        (dr64,) = torch.autograd.grad((w64 * g64).sum(), r64)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    p = EdgeParams(8, B200_CUTOFF_XPLOR if cutoff == 'xplor' else B200_CUTOFF_POLY, 1, 5.0, 4.5, 6.0)
+    Ws = [getattr(net, f'layer{k}').weight.detach().float().to(dev).contiguous() for k in range(3)]
+    T = ops.radial_table_build(p, basis.coeffs.detach().float().to(dev), *Ws)
+    ln = torch.tensor(r, dtype=torch.float32, device=dev)
+    order = torch.argsort((ln * 800).int(), stable=True).to(torch.int32)
+    w = ops.radial_table_fwd(p, wn, 8, 64, 64, ln, T)
+    assert torch.equal(w, ops.radial_table_fwd(p, wn, 8, 64, 64, ln, T, order=order))   # visiting order is not arithmetic
+    # fp32 rounding of r itself moves w by |dw/dr| * ulp(r): compare at that scale
+    assert _rel(w, w64.detach()) < 5e-6
+    dr = ops.radial_table_bwd(p, wn, 8, 64, 64, ln, T, g64.float().to(dev), order=order)
+    assert _rel(dr, dr64) < 1e-5
+    dr2 = ops.radial_table_bwd(p, wn, 8, 64, 64, ln, T, g64.float().to(dev), dr=dr.clone())
+    assert _rel(dr2, 2 * dr64) < 1e-5
