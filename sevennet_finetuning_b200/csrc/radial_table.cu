@@ -148,12 +148,21 @@ radial_table_fwd_kernel(int wn, long long E, float inv_h, int n_grid, const floa
   const int epi = max(1, 256 / q);                   // edges per iteration
   const int sub = threadIdx.x / q, k0 = threadIdx.x % q;
   const long long j0 = (long long)blockIdx.x * kTabEdgesPerCta, j1 = min(E, j0 + kTabEdgesPerCta);
+  // edge id, interval and local coordinate of the CTA's edges, fetched once (two dependent global loads per edge
+  // would otherwise sit in front of every iteration)
+  __shared__ int s_e[kTabEdgesPerCta], s_i[kTabEdgesPerCta];
+  __shared__ float s_t[kTabEdgesPerCta];
+  if (threadIdx.x < kTabEdgesPerCta && j0 + threadIdx.x < j1) {
+    const int e = order ? __ldg(order + j0 + threadIdx.x) : (int)(j0 + threadIdx.x);
+    s_e[threadIdx.x] = e;
+    locate(__ldg(len + e), inv_h, n_grid, s_i[threadIdx.x], s_t[threadIdx.x]);
+  }
+  __syncthreads();
   if (sub >= epi) return;
   for (long long j = j0 + sub; j < j1; j += epi) {
-    const long long e = order ? (long long)__ldg(order + j) : j;
-    int i;
-    float t;
-    locate(__ldg(len + e), inv_h, n_grid, i, t);
+    const long long e = s_e[j - j0];
+    const int i = s_i[j - j0];
+    const float t = s_t[j - j0];
     const float4* row = reinterpret_cast<const float4*>(T + (size_t)i * 4 * wn);
     float4* out = reinterpret_cast<float4*>(w + (size_t)e * wn);
     for (int k4 = k0; k4 < q; k4 += 256) {           // one pass unless wn > 1024
@@ -174,11 +183,18 @@ radial_table_bwd_kernel(int wn, long long E, float inv_h, int n_grid, const floa
                         const float* __restrict__ T, const float* __restrict__ dw, float* __restrict__ dr, int accumulate) {
   const int q = wn >> 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long j0 = (long long)blockIdx.x * kTabEdgesPerCta, j1 = min(E, j0 + kTabEdgesPerCta);
+  __shared__ int s_e[kTabEdgesPerCta], s_i[kTabEdgesPerCta];
+  __shared__ float s_t[kTabEdgesPerCta];
+  if (threadIdx.x < kTabEdgesPerCta && j0 + threadIdx.x < j1) {
+    const int e = order ? __ldg(order + j0 + threadIdx.x) : (int)(j0 + threadIdx.x);
+    s_e[threadIdx.x] = e;
+    locate(__ldg(len + e), inv_h, n_grid, s_i[threadIdx.x], s_t[threadIdx.x]);
+  }
+  __syncthreads();
   for (long long j = j0 + warp; j < j1; j += 8) {
-    const long long e = order ? (long long)__ldg(order + j) : j;
-    int i;
-    float t;
-    locate(__ldg(len + e), inv_h, n_grid, i, t);
+    const long long e = s_e[j - j0];
+    const int i = s_i[j - j0];
+    const float t = s_t[j - j0];
     const float t2 = 2.f * t, t3 = 3.f * t * t;
     const float4* row = reinterpret_cast<const float4*>(T + (size_t)i * 4 * wn);
     const float4* g = reinterpret_cast<const float4*>(dw + (size_t)e * wn);
