@@ -1,5 +1,7 @@
 cd /root/repo
-timeout 900 ncu --profile-from-start off --set full --import-source on --clock-control none -k regex:"irreps_linear_tc_kernel|wgrad_splitk" --launch-skip 20 --launch-count 24 -o /tmp/ft_lin_full python tools/ft_ncu_target.py > gpurun_out/ft_ncu_full.log 2>&1
-echo "ncu rc=$?" > gpurun_out/ft_ncu.err
-ncu -i /tmp/ft_lin_full.ncu-rep --page raw --csv > gpurun_out/ft_lin_full_raw.csv 2>/dev/null
-ls -la /tmp/ft_lin_full.ncu-rep >> gpurun_out/ft_ncu.err
+timeout 1500 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err
+echo "rc=$?" >> gpurun_out/bench_default.err
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_reference.json 2>> gpurun_out/bench_default.err
+timeout 600 python bench.py --impl reference --workload finetune --steps 1 --warmup 1 > gpurun_out/bench_reference_ft.json 2>> gpurun_out/bench_default.err
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/md_launches.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-finetune > gpurun_out/md_ncu.log 2>&1
+echo "ncu rc=$?" >> gpurun_out/bench_default.err
