@@ -223,7 +223,8 @@ template <int... PIDS> struct PL;
 template <> struct PL<> {
   static constexpr int NACC = 0;
   static constexpr int NP = 0;
-  __device__ __forceinline__ static void load_w(const ConvDesc&, const float*, int, float*) {}
+  template <bool TAB> __device__ __forceinline__ static void load_w(const ConvDesc&, const float*, int, float, float*) {}
+  __device__ __forceinline__ static void load_wd(const ConvDesc&, const float*, int, float, float*, float*) {}
   __device__ __forceinline__ static void fwd(const float*, const float*, const float*, float*) {}
   __device__ __forceinline__ static void bwdx(const float*, const float*, const float*, float*) {}
   template <bool DX>
@@ -237,10 +238,27 @@ template <int PID, int... REST> struct PL<PID, REST...> {
   using R = PL<REST...>;
   static constexpr int NACC = P::D3 + R::NACC;
   static constexpr int NP = 1 + sizeof...(REST);
-  // wv[0..NP) <- weights of channel u for this edge
-  __device__ __forceinline__ static void load_w(const ConvDesc& d, const float* __restrict__ wrow, int u, float* wv) {
-    wv[0] = __ldg(wrow + d.woff[PID] + u);
-    R::load_w(d, wrow, u, wv + 1);
+  // wv[0..NP) <- weights of channel u for this edge.  TAB: wrow is the edge's row of the tabulated radial function
+  // ([a | b | c | d][wn], radial_table.cu) and the weight is the cubic a + b t + c t^2 + d t^3 at the edge's coordinate t
+  template <bool TAB>
+  __device__ __forceinline__ static void load_w(const ConvDesc& d, const float* __restrict__ wrow, int u, float t, float* wv) {
+    const int k = d.woff[PID] + u;
+    if constexpr (TAB) {
+      const float a = __ldg(wrow + k), b = __ldg(wrow + d.wn + k), c = __ldg(wrow + 2 * d.wn + k), e = __ldg(wrow + 3 * d.wn + k);
+      wv[0] = fmaf(fmaf(fmaf(e, t, c), t, b), t, a);
+    } else {
+      wv[0] = __ldg(wrow + k);
+    }
+    R::template load_w<TAB>(d, wrow, u, t, wv + 1);
+  }
+  // tabulated weights and their derivative with respect to t
+  __device__ __forceinline__ static void load_wd(const ConvDesc& d, const float* __restrict__ wrow, int u, float t, float* wv,
+                                                 float* wdv) {
+    const int k = d.woff[PID] + u;
+    const float a = __ldg(wrow + k), b = __ldg(wrow + d.wn + k), c = __ldg(wrow + 2 * d.wn + k), e = __ldg(wrow + 3 * d.wn + k);
+    wv[0] = fmaf(fmaf(fmaf(e, t, c), t, b), t, a);
+    wdv[0] = fmaf(fmaf(3.f * e, t, 2.f * c), t, b);
+    R::load_wd(d, wrow, u, t, wv + 1, wdv + 1);
   }
   __device__ __forceinline__ static void store_w(const ConvDesc& d, float* __restrict__ wrow, int u, const float* wv) {
     wrow[d.woff[PID] + u] = wv[0];
@@ -289,9 +307,18 @@ constexpr int kMaxAcc = 22;   // output components a thread accumulates: 3+1+3+3
 
 // ---- staging of one chunk of edges ----------------------------------------------------------------
 // eid: optional indirection (edge ids sorted by source, for the backward-x pass); gidx: row to gather per edge
+struct TabArg {          // tabulated radial weights (radial_table.cu); len == nullptr: per-edge weights come from memory
+  const float* len;      // edge lengths [E]
+  float inv_h;
+  int n_grid;
+  float* dr;             // reverse pass: d E / d r per edge
+  int acc_dr;            // add into dr instead of overwriting
+};
+
 template <int ROLE, int LOUT>
 __device__ __forceinline__ void stage_chunk(float* rec, int* s_e, int* s_g, const float* __restrict__ Y,
-                                            const int* __restrict__ eid, const int* __restrict__ gidx, int c0, int ne) {
+                                            const int* __restrict__ eid, const int* __restrict__ gidx, int c0, int ne,
+                                            const TabArg* targ = nullptr, int* s_ti = nullptr, float* s_tt = nullptr) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int NI = RT::NTAB + 1;
   for (int it = threadIdx.x; it < ne * NI; it += blockDim.x) {
@@ -304,6 +331,12 @@ __device__ __forceinline__ void stage_chunk(float* rec, int* s_e, int* s_g, cons
       for (int b = 0; b < 9; ++b) r[b] = __ldg(Yg + b);
       s_e[k] = e;
       s_g[k] = __ldg(gidx + e);
+      if (targ) {   // interval and local coordinate of the edge in the radial table
+        const float r = __ldg(targ->len + e);
+        const int ti = min((int)(r * targ->inv_h), targ->n_grid - 1);
+        s_ti[k] = ti;
+        s_tt[k] = fmaf(r, targ->inv_h, -(float)ti);
+      }
     } else if constexpr (RT::NTAB > 0) {
       float Yl[9];
 #pragma unroll
@@ -329,9 +362,10 @@ template <int ROLE> __device__ __forceinline__ int role_xoff(const ConvDesc& d) 
 }
 
 // ---- forward ------------------------------------------------------------------------------------
-template <int ROLE, int LOUT, int G>
+template <int ROLE, int LOUT, int G, bool TAB>
 __device__ __forceinline__ void fwd_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
-                                          const float* __restrict__ x, const float* __restrict__ w, int u, float* acc) {
+                                          const float* __restrict__ x, const float* __restrict__ w, int u, float* acc,
+                                          const int* s_ti, const float* s_tt) {
   using L = typename GroupT<ROLE, LOUT, G>::L;
   constexpr int D1 = RoleT<ROLE, LOUT>::D1;
   const int xo = role_xoff<ROLE>(d) + u * D1;
@@ -341,20 +375,23 @@ __device__ __forceinline__ void fwd_group(const ConvDesc& d, const float* rec, c
     const float* xr = x + (size_t)s_g[k] * d.xdim + xo;
 #pragma unroll
     for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
-    L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
+    if constexpr (TAB) L::template load_w<true>(d, w + (size_t)s_ti[k] * 4 * d.wn, u, s_tt[k], wv);
+    else L::template load_w<false>(d, w + (size_t)s_e[k] * d.wn, u, 0.f, wv);
     L::fwd(rec + k * RoleT<ROLE, LOUT>::REC, xv, wv, acc);
   }
 }
 
-template <int ROLE, int LOUT>
+template <int ROLE, int LOUT, bool TAB>
 __global__ void __launch_bounds__(256)
 conv_fwd_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
                 const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w, float denom,
-                float* __restrict__ out) {
+                float* __restrict__ out, TabArg tab) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int TE = te_of<ROLE>();
   __shared__ __align__(16) float rec[TE * RT::REC];
   __shared__ int s_e[TE], s_g[TE];
+  __shared__ int s_ti[TAB ? TE : 1];
+  __shared__ float s_tt[TAB ? TE : 1];
   const int i = blockIdx.x;
   const int e0 = rowptr[i], e1 = rowptr[i + 1];
   const int grp = threadIdx.x / mulpad, u = threadIdx.x % mulpad;
@@ -365,13 +402,13 @@ conv_fwd_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const in
   for (int c0 = e0; c0 < e1; c0 += TE) {
     const int ne = min(TE, e1 - c0);
     __syncthreads();
-    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne);
+    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne, TAB ? &tab : nullptr, s_ti, s_tt);
     __syncthreads();
     if (active) {
-      if (grp == 0) fwd_group<ROLE, LOUT, 0>(d, rec, s_e, s_g, ne, x, w, u, acc);
-      else if (grp == 1) fwd_group<ROLE, LOUT, 1>(d, rec, s_e, s_g, ne, x, w, u, acc);
-      else if (grp == 2) fwd_group<ROLE, LOUT, 2>(d, rec, s_e, s_g, ne, x, w, u, acc);
-      else fwd_group<ROLE, LOUT, 3>(d, rec, s_e, s_g, ne, x, w, u, acc);
+      if (grp == 0) fwd_group<ROLE, LOUT, 0, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
+      else if (grp == 1) fwd_group<ROLE, LOUT, 1, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
+      else if (grp == 2) fwd_group<ROLE, LOUT, 2, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
+      else fwd_group<ROLE, LOUT, 3, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
     }
   }
   if (active) {
@@ -395,7 +432,7 @@ __device__ __forceinline__ void bwdx_group(const ConvDesc& d, const float* rec, 
   for (int k = 0; k < ne; ++k) {
     float gv[L::NACC > 0 ? L::NACC : 1], wv[L::NP > 0 ? L::NP : 1];
     L::load_o(d, gout + (size_t)s_g[k] * d.odim, u, inv_denom, gv);
-    L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
+    L::template load_w<false>(d, w + (size_t)s_e[k] * d.wn, u, 0.f, wv);
     L::bwdx(rec + k * RoleT<ROLE, LOUT>::REC, gv, wv, dx);
   }
 }
@@ -473,11 +510,11 @@ __device__ __forceinline__ float warp_reduce8(float* v, int lane) {
   return v[0];
 }
 
-template <int ROLE, int LOUT, int G, bool DX>
+template <int ROLE, int LOUT, int G, bool DX, bool TAB>
 __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
                                            const float* __restrict__ x, const float* __restrict__ w,
                                            float* __restrict__ dw, const float* gv, int u, bool active, float* s_dY,
-                                           float* __restrict__ dxo) {
+                                           float* __restrict__ dxo, const int* s_ti, const float* s_tt, float* s_dr) {
   using L = typename GroupT<ROLE, LOUT, G>::L;
   constexpr int D1 = RoleT<ROLE, LOUT>::D1;
   const int xo = role_xoff<ROLE>(d) + u * D1;
@@ -486,17 +523,25 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
     float dY[9];
 #pragma unroll
     for (int b = 0; b < 9; ++b) dY[b] = 0.f;
+    float drp = 0.f;   // TAB: this channel's share of d E / d t of the edge
     if (active) {
-      float xv[D1], wv[L::NP > 0 ? L::NP : 1], dwv[L::NP > 0 ? L::NP : 1];
+      constexpr int NPW = L::NP > 0 ? L::NP : 1;
+      float xv[D1], wv[NPW], dwv[NPW], wdv[TAB ? NPW : 1];
       const float* xr = x + (size_t)s_g[k] * d.xdim + xo;
 #pragma unroll
       for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
-      L::load_w(d, w + (size_t)s_e[k] * d.wn, u, wv);
+      if constexpr (TAB) L::load_wd(d, w + (size_t)s_ti[k] * 4 * d.wn, u, s_tt[k], wv, wdv);
+      else L::template load_w<false>(d, w + (size_t)s_e[k] * d.wn, u, 0.f, wv);
       float dxv[D1];
 #pragma unroll
       for (int a = 0; a < D1; ++a) dxv[a] = 0.f;
       L::template bwde<DX>(rec + k * RoleT<ROLE, LOUT>::REC, xv, gv, wv, dwv, dY, dxv);
-      L::store_w(d, dw + (size_t)s_e[k] * d.wn, u, dwv);
+      if constexpr (TAB) {   // the weight gradient never leaves the registers: contract it with d w / d t
+#pragma unroll
+        for (int q = 0; q < L::NP; ++q) drp = fmaf(dwv[q], wdv[q], drp);
+      } else {
+        L::store_w(d, dw + (size_t)s_e[k] * d.wn, u, dwv);
+      }
       if constexpr (DX) {   // scatter to the source atom's row (RED.ADD; the row was zeroed by the launcher)
         float* xr = dxo + (size_t)s_g[k] * d.xdim + xo;
 #pragma unroll
@@ -509,21 +554,28 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
       const float r = warp_reduce8(dY + 1, lane);
       if ((lane & 3) == 0) s_dY[(warp * te_of<ROLE>() + k) * 8 + (lane >> 2)] = r;  // slot lane>>2 == component m
     }
+    if constexpr (TAB) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) drp += __shfl_xor_sync(0xffffffffu, drp, o);
+      if (lane == 0) s_dr[warp * te_of<ROLE>() + k] = drp;
+    }
   }
 }
 
-template <int ROLE, int LOUT, bool DX>
+template <int ROLE, int LOUT, bool DX, bool TAB>
 __global__ void __launch_bounds__(256)
 conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
                  const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w,
                  const float* __restrict__ gout, float inv_denom, float* __restrict__ dw, float* __restrict__ dYo,
-                 int accumulate, float* __restrict__ dxo) {
+                 int accumulate, float* __restrict__ dxo, TabArg tab) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int NG = num_groups<ROLE, LOUT>();
   constexpr int TE = te_of<ROLE>();
   __shared__ __align__(16) float rec[TE * RT::REC];
   __shared__ int s_e[TE], s_g[TE];
-  extern __shared__ float s_dY[];  // [nwarps][TE][8]
+  __shared__ int s_ti[TAB ? TE : 1];
+  __shared__ float s_tt[TAB ? TE : 1];
+  extern __shared__ float s_dY[];  // [nwarps][TE][8], then (TAB) s_dr[nwarps][TE]
   const int i = blockIdx.x;
   const int e0 = rowptr[i], e1 = rowptr[i + 1];
   const int grp = threadIdx.x / mulpad, u = threadIdx.x % mulpad;
@@ -542,14 +594,23 @@ conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const i
   for (int c0 = e0; c0 < e1; c0 += TE) {
     const int ne = min(TE, e1 - c0);
     __syncthreads();
-    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne);
+    stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne, TAB ? &tab : nullptr, s_ti, s_tt);
     __syncthreads();
-    if (grp == 0) bwde_group<ROLE, LOUT, 0, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
-    else if (grp == 1) bwde_group<ROLE, LOUT, 1, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
-    else if (grp == 2) bwde_group<ROLE, LOUT, 2, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
-    else bwde_group<ROLE, LOUT, 3, DX>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo);
+    float* s_dr = s_dY + nwarps * TE * 8;
+    if (grp == 0) bwde_group<ROLE, LOUT, 0, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
+    else if (grp == 1) bwde_group<ROLE, LOUT, 1, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
+    else if (grp == 2) bwde_group<ROLE, LOUT, 2, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
+    else bwde_group<ROLE, LOUT, 3, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
+    if constexpr (TAB || !(LOUT == 0 && ROLE == 0)) __syncthreads();
+    if constexpr (TAB) {   // d E / d r of the chunk's edges: sum over the warps (channels), times d t / d r = 1 / h
+      for (int k = threadIdx.x; k < ne; k += blockDim.x) {
+        float tot = 0.f;
+        for (int wq = 0; wq < nwarps; ++wq) tot += s_dr[wq * TE + k];
+        float* p = tab.dr + (size_t)(c0 + k);
+        *p = tab.acc_dr ? fmaf(tot, tab.inv_h, *p) : tot * tab.inv_h;
+      }
+    }
     if constexpr (!(LOUT == 0 && ROLE == 0)) {
-      __syncthreads();
       for (int it = threadIdx.x; it < ne * 8; it += blockDim.x) {
         const int k = it >> 3, s = it & 7, m = s;
         float tot = 0.f;
@@ -564,12 +625,13 @@ conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const i
 // ---- launchers ------------------------------------------------------------------------------------
 template <int ROLE, int LOUT>
 static void launch_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
-                       const float* w, float denom, float* out, cudaStream_t st) {
+                       const float* w, float denom, float* out, cudaStream_t st, const TabArg* tab = nullptr) {
   const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
   if (mul == 0 || n_dst == 0) return;
   const int mulpad = round_up(mul, 32);
   const int threads = mulpad * num_groups<ROLE, LOUT>();
-  conv_fwd_kernel<ROLE, LOUT><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out);
+  if (tab) conv_fwd_kernel<ROLE, LOUT, true><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out, *tab);
+  else conv_fwd_kernel<ROLE, LOUT, false><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out, TabArg{});
 }
 template <int ROLE, int LOUT>
 static void launch_bwdx(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst,
@@ -585,18 +647,26 @@ static void launch_bwdx(const ConvDesc& d, int n_src, const int* rrowptr, const 
 template <int ROLE, int LOUT>
 static void launch_bwde(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
                         const float* w, const float* gout, float inv_denom, float* dw, float* dY, int accumulate,
-                        float* dx, cudaStream_t st) {
+                        float* dx, cudaStream_t st, const TabArg* tab = nullptr) {
   const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
   if (mul == 0 || n_dst == 0) return;
   const int mulpad = round_up(mul, 32);
   const int threads = mulpad * num_groups<ROLE, LOUT>();
-  const size_t sm = (size_t)(threads / 32) * te_of<ROLE>() * 8 * sizeof(float);
-  if (dx)
-    conv_bwde_kernel<ROLE, LOUT, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
-                                                                    accumulate, dx);
-  else
-    conv_bwde_kernel<ROLE, LOUT, false><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw, dY,
-                                                                     accumulate, nullptr);
+  const size_t sm = (size_t)(threads / 32) * te_of<ROLE>() * (tab ? 9 : 8) * sizeof(float);
+  if (tab) {
+    if (dx)
+      conv_bwde_kernel<ROLE, LOUT, true, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom,
+                                                                            nullptr, dY, accumulate, dx, *tab);
+    else
+      conv_bwde_kernel<ROLE, LOUT, false, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom,
+                                                                             nullptr, dY, accumulate, nullptr, *tab);
+  } else if (dx) {
+    conv_bwde_kernel<ROLE, LOUT, true, false><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw,
+                                                                           dY, accumulate, dx, TabArg{});
+  } else {
+    conv_bwde_kernel<ROLE, LOUT, false, false><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw,
+                                                                            dY, accumulate, nullptr, TabArg{});
+  }
 }
 
 static bool desc_ok(const ConvDesc& d) {
@@ -657,6 +727,46 @@ int conv_bwd_edge_x(const ConvDesc& d, int n_dst, int n_src, int n_edges, const 
     if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
   }
   return check_launch("conv_bwd_edge", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
+}
+
+// ---- the same two passes with the per-edge weights interpolated from the tabulated radial function (radial_table.cu):
+// neither the weights [E, wn] nor their gradient exist in memory; the reverse pass emits d E / d r per edge.
+int conv_fwd_tab(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                 const float* len, const float* table, float inv_h, int n_grid, float denom, float* out, cudaStream_t st) {
+  B200_REQUIRE(desc_ok(d), "conv_fwd_tab: unsupported irreps (m0<=256, m1<=128, m2<=64, lout in {0,2})");
+  const TabArg tab{len, inv_h, n_grid, nullptr, 0};
+  if (d.lout == 2) {
+    launch_fwd<0, 2>(d, n_dst, rowptr, src, x, Y, table, denom, out, st, &tab);
+    launch_fwd<1, 2>(d, n_dst, rowptr, src, x, Y, table, denom, out, st, &tab);
+    launch_fwd<2, 2>(d, n_dst, rowptr, src, x, Y, table, denom, out, st, &tab);
+  } else {
+    launch_fwd<0, 0>(d, n_dst, rowptr, src, x, Y, table, denom, out, st, &tab);
+    launch_fwd<1, 0>(d, n_dst, rowptr, src, x, Y, table, denom, out, st, &tab);
+    launch_fwd<2, 0>(d, n_dst, rowptr, src, x, Y, table, denom, out, st, &tab);
+  }
+  return check_launch("conv_fwd_tab", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
+}
+
+int conv_bwd_tab(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                 const float* Y, const float* len, const float* table, float inv_h, int n_grid, const float* gout, float denom,
+                 float* dY, int accumulate_dY, float* dr, int accumulate_dr, float* dx, cudaStream_t st) {
+  B200_REQUIRE(desc_ok(d), "conv_bwd_tab: unsupported irreps");
+  const float inv = 1.0f / denom;
+  if (dx) cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)n_src * d.xdim, st);
+  int acc = accumulate_dY;
+  TabArg tab{len, inv_h, n_grid, dr, accumulate_dr};
+  if (d.lout == 2) {
+    if (d.m0) { launch_bwde<0, 2>(d, n_dst, rowptr, src, x, Y, table, gout, inv, nullptr, dY, acc, dx, st, &tab); acc = 1; tab.acc_dr = 1; }
+    if (d.m1) { launch_bwde<1, 2>(d, n_dst, rowptr, src, x, Y, table, gout, inv, nullptr, dY, acc, dx, st, &tab); acc = 1; tab.acc_dr = 1; }
+    if (d.m2) { launch_bwde<2, 2>(d, n_dst, rowptr, src, x, Y, table, gout, inv, nullptr, dY, acc, dx, st, &tab); acc = 1; tab.acc_dr = 1; }
+  } else {
+    if (!acc && !d.m1 && !d.m2) cudaMemsetAsync(dY, 0, sizeof(float) * 9 * (size_t)n_edges, st);
+    launch_bwde<0, 0>(d, n_dst, rowptr, src, x, Y, table, gout, inv, nullptr, dY, acc, dx, st, &tab);
+    tab.acc_dr = 1;
+    if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, table, gout, inv, nullptr, dY, acc, dx, st, &tab); acc = 1; }
+    if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, table, gout, inv, nullptr, dY, acc, dx, st, &tab); acc = 1; }
+  }
+  return check_launch("conv_bwd_tab", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
 }
 
 int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x, const float* Y,

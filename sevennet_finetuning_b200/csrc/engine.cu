@@ -86,6 +86,7 @@ struct Layer {
   int lout;
   bool fused;   // radial layer + convolution run as the fused tcgen05 kernels (fused.cu)
   bool table;   // per-edge weights interpolated from the tabulated radial function (radial_table.cu)
+  bool tabconv; // ... inside the convolution kernels: neither the weights nor their gradient are materialised
 };
 
 }  // namespace b200
@@ -183,6 +184,7 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     const bool fused_env = getenv("B200_FUSED") && atoi(getenv("B200_FUSED")) != 0;   // opt-in
     L.fused = fused_env && fused_supported(L.conv, L.mlp);
     L.table = !fused_env && radial_table_supported(L.mlp) && !(getenv("B200_RADIAL_TABLE") && atoi(getenv("B200_RADIAL_TABLE")) == 0);
+    L.tabconv = L.table && !(getenv("B200_TABLE_IN_CONV") && atoi(getenv("B200_TABLE_IN_CONV")) == 0);
     m->layers.push_back(L);
     m->split_bwd_x = getenv("B200_SPLIT_BWD_X") && atoi(getenv("B200_SPLIT_BWD_X")) != 0;
     const std::string s = std::to_string(t);
@@ -266,7 +268,7 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
     maxx = std::max(maxx, L.conv.xdim);
     maxg = std::max(maxg, L.sc.out_dim);
     maxmsg = std::max(maxmsg, L.conv.odim);
-    if (!L.fused) maxwn = std::max(maxwn, L.conv.wn);   // un-fused layers materialise [E, wn] weights and their gradient
+    if (!L.fused && !L.tabconv) maxwn = std::max(maxwn, L.conv.wn);   // these layers materialise [E, wn] weights and their gradient
   }
   maxx = std::max(maxx, m->r1.in_dim);
   const int nb = m->cfg.edge.num_basis;
@@ -290,7 +292,7 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
   b.virial_atom = p.take<float>((size_t)NA * 6);
   b.w.clear(); b.xs.clear(); b.gin.clear(); b.rad.clear();
   for (const Layer& L : m->layers) {
-    b.w.push_back(p.take<float>(L.fused ? 0 : (size_t)E * L.conv.wn));
+    b.w.push_back(p.take<float>((L.fused || L.tabconv) ? 0 : (size_t)E * L.conv.wn));
     b.rad.push_back(reinterpret_cast<float*>(p.take<char>(L.fused ? fused_radial_bytes(E) : 0)));
     b.xs.push_back(p.take<float>((size_t)NA * L.conv.xdim));
     b.gin.push_back(p.take<float>((size_t)N * L.sc.out_dim));
@@ -383,7 +385,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   OP(CAT_EDGE, edge_embed_fwd(c.edge, E, edge_vec, coeffs, b.len, b.Y, b.emb, st));
   OP(CAT_EDGE, csr_transpose(NA, E, src, b.tws, b.rrowptr, b.eid, st));
   bool any_table = false;
-  for (const Layer& L : m->layers) any_table = any_table || L.table;
+  for (const Layer& L : m->layers) any_table = any_table || (L.table && !L.tabconv);
   if (any_table) {   // counting sort of the edges by table interval, once per call for all layers and both passes
     OP(CAT_EDGE, radial_table_order(c.edge, E, b.len, b.tws2, b.rorder, st));
   }
@@ -407,9 +409,15 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       OP(CAT_MLP_FWD, fused_radial(c.edge, L.mlp, E, edge_vec, coeffs, W0, W1, b.rad[t], st));
       OP(CAT_CONV_FWD, fused_conv_fwd(L.conv, N, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, denom[t], b.conv_out, st));
     } else {
-      if (L.table) OP(CAT_MLP_FWD, radial_table_fwd(c.edge, L.mlp, E, b.len, b.rorder, m->tables[t], b.w[t], st));
-      else OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, W0, W1, W2, b.w[t], st));
-      OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
+      if (L.tabconv) {
+        const RadialTableGrid tg = radial_table_grid(c.edge);
+        OP(CAT_CONV_FWD, conv_fwd_tab(L.conv, N, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h), tg.n, denom[t],
+                                      b.conv_out, st));
+      } else {
+        if (L.table) OP(CAT_MLP_FWD, radial_table_fwd(c.edge, L.mlp, E, b.len, b.rorder, m->tables[t], b.w[t], st));
+        else OP(CAT_MLP_FWD, radial_mlp_fwd(L.mlp, E, b.emb, W0, W1, W2, b.w[t], st));
+        OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
+      }
     }
     OP(CAT_NODE, irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
     OP(CAT_NODE, gate_fwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], xn, st));
@@ -443,6 +451,13 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     if (L.fused) {
       OP(CAT_CONV_BWD_EDGE, fused_conv_bwd(L.conv, NA, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, b.g_conv, denom[t], dxs, b.dY,
                                            b.ddr, ddr_written ? 1 : 0, st));
+      dy_written = ddr_written = true;
+    } else if (L.tabconv) {
+      // d Y, d E / d r and (t > 0) d x[src] in one pass; the weight gradient is contracted with d w / d r in registers
+      const RadialTableGrid tg = radial_table_grid(c.edge);
+      OP(CAT_CONV_BWD_EDGE, conv_bwd_tab(L.conv, N, NA, (int)E, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h),
+                                         tg.n, b.g_conv, denom[t], b.dY, dy_written ? 1 : 0, b.ddr, ddr_written ? 1 : 0,
+                                         m->split_bwd_x ? nullptr : dxs, st));
       dy_written = ddr_written = true;
     } else {
       // d weight, d Y and (t > 0) d x[src] in one pass: the source rows are accumulated with RED.ADD

@@ -33,6 +33,12 @@ int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid,
 int conv_bwd_edge_x(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
                     const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
                     float* dx, cudaStream_t st);
+// per-edge weights interpolated from the tabulated radial function inside the kernels (no [E, wn] tensors)
+int conv_fwd_tab(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                 const float* len, const float* table, float inv_h, int n_grid, float denom, float* out, cudaStream_t st);
+int conv_bwd_tab(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                 const float* Y, const float* len, const float* table, float inv_h, int n_grid, const float* gout, float denom,
+                 float* dY, int accumulate_dY, float* dr, int accumulate_dr, float* dx, cudaStream_t st);
 int conv_bwd_edge(const ConvDesc& d, int n_dst, int n_edges, const int* rowptr, const int* src, const float* x,
                   const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
                   cudaStream_t st);
