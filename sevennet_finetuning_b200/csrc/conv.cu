@@ -239,13 +239,13 @@ template <int PID, int... REST> struct PL<PID, REST...> {
   static constexpr int NACC = P::D3 + R::NACC;
   static constexpr int NP = 1 + sizeof...(REST);
   // wv[0..NP) <- weights of channel u for this edge.  TAB: wrow is the edge's row of the tabulated radial function
-  // ([a | b | c | d][wn], radial_table.cu) and the weight is the cubic a + b t + c t^2 + d t^3 at the edge's coordinate t
+  // (float4 {a, b, c, d} per weight, radial_table.cu) and the weight is the cubic a + b t + c t^2 + d t^3 at the edge's t
   template <bool TAB>
   __device__ __forceinline__ static void load_w(const ConvDesc& d, const float* __restrict__ wrow, int u, float t, float* wv) {
     const int k = d.woff[PID] + u;
     if constexpr (TAB) {
-      const float a = __ldg(wrow + k), b = __ldg(wrow + d.wn + k), c = __ldg(wrow + 2 * d.wn + k), e = __ldg(wrow + 3 * d.wn + k);
-      wv[0] = fmaf(fmaf(fmaf(e, t, c), t, b), t, a);
+      const float4 cf = __ldg(reinterpret_cast<const float4*>(wrow) + k);
+      wv[0] = fmaf(fmaf(fmaf(cf.w, t, cf.z), t, cf.y), t, cf.x);
     } else {
       wv[0] = __ldg(wrow + k);
     }
@@ -255,9 +255,9 @@ template <int PID, int... REST> struct PL<PID, REST...> {
   __device__ __forceinline__ static void load_wd(const ConvDesc& d, const float* __restrict__ wrow, int u, float t, float* wv,
                                                  float* wdv) {
     const int k = d.woff[PID] + u;
-    const float a = __ldg(wrow + k), b = __ldg(wrow + d.wn + k), c = __ldg(wrow + 2 * d.wn + k), e = __ldg(wrow + 3 * d.wn + k);
-    wv[0] = fmaf(fmaf(fmaf(e, t, c), t, b), t, a);
-    wdv[0] = fmaf(fmaf(3.f * e, t, 2.f * c), t, b);
+    const float4 cf = __ldg(reinterpret_cast<const float4*>(wrow) + k);
+    wv[0] = fmaf(fmaf(fmaf(cf.w, t, cf.z), t, cf.y), t, cf.x);
+    wdv[0] = fmaf(fmaf(3.f * cf.w, t, 2.f * cf.z), t, cf.y);
     R::load_wd(d, wrow, u, t, wv + 1, wdv + 1);
   }
   __device__ __forceinline__ static void store_w(const ConvDesc& d, float* __restrict__ wrow, int u, const float* wv) {

@@ -96,7 +96,8 @@ __device__ void mlp_hidden_f64(const EdgeParams& p, const MlpDesc& d, double r, 
 // One CTA per interval [r_i, r_i + h]: the MLP at both ends in float64, then the cubic of the interval in the local
 // coordinate t = (r - r_i) / h:  w(t) = a + b t + c t^2 + d t^3 with a = v0, b = m0, c = 3 D - 2 m0 - m1, d = m0 + m1 - 2 D
 // (v = value, m = h dw/dr, D = v1 - v0 formed in float64: the fp32 table never differences two nearly equal values, so
-// the slope (b + 2 c t + 3 d t^2) / h is as accurate as the value).  Row layout: T[i] = [a | b | c | d], wn floats each.
+// the slope (b + 2 c t + 3 d t^2) / h is as accurate as the value).  Row layout: T[i][k] = float4 {a, b, c, d} of weight k:
+// one 16-byte load per weight, consecutive channels read consecutive float4s.
 __global__ void __launch_bounds__(128)
 radial_table_build_kernel(EdgeParams p, MlpDesc d, double h, const float* __restrict__ coeffs, const float* __restrict__ W0,
                           const float* __restrict__ W1, const float* __restrict__ W2, float* __restrict__ T) {
@@ -114,10 +115,8 @@ radial_table_build_kernel(EdgeParams p, MlpDesc d, double h, const float* __rest
       v[1] += a2[1][n] * w2; m[1] += da2[1][n] * w2;
     }
     const double v0 = v[0] * sc, v1 = v[1] * sc, m0 = m[0] * sc * h, m1 = m[1] * sc * h, D = v1 - v0;
-    row[k] = (float)v0;
-    row[d.wn + k] = (float)m0;
-    row[2 * d.wn + k] = (float)(3.0 * D - 2.0 * m0 - m1);
-    row[3 * d.wn + k] = (float)(m0 + m1 - 2.0 * D);
+    reinterpret_cast<float4*>(row)[k] =
+        make_float4((float)v0, (float)m0, (float)(3.0 * D - 2.0 * m0 - m1), (float)(m0 + m1 - 2.0 * D));
   }
 }
 
@@ -166,12 +165,12 @@ radial_table_fwd_kernel(int wn, long long E, float inv_h, int n_grid, const floa
     const float4* row = reinterpret_cast<const float4*>(T + (size_t)i * 4 * wn);
     float4* out = reinterpret_cast<float4*>(w + (size_t)e * wn);
     for (int k4 = k0; k4 < q; k4 += 256) {           // one pass unless wn > 1024
-      const float4 a = __ldg(row + k4), b = __ldg(row + q + k4), c = __ldg(row + 2 * q + k4), d = __ldg(row + 3 * q + k4);
+      const float4 c0 = __ldg(row + 4 * k4), c1 = __ldg(row + 4 * k4 + 1), c2 = __ldg(row + 4 * k4 + 2), c3 = __ldg(row + 4 * k4 + 3);
       float4 o;
-      o.x = fmaf(fmaf(fmaf(d.x, t, c.x), t, b.x), t, a.x);
-      o.y = fmaf(fmaf(fmaf(d.y, t, c.y), t, b.y), t, a.y);
-      o.z = fmaf(fmaf(fmaf(d.z, t, c.z), t, b.z), t, a.z);
-      o.w = fmaf(fmaf(fmaf(d.w, t, c.w), t, b.w), t, a.w);
+      o.x = fmaf(fmaf(fmaf(c0.w, t, c0.z), t, c0.y), t, c0.x);
+      o.y = fmaf(fmaf(fmaf(c1.w, t, c1.z), t, c1.y), t, c1.x);
+      o.z = fmaf(fmaf(fmaf(c2.w, t, c2.z), t, c2.y), t, c2.x);
+      o.w = fmaf(fmaf(fmaf(c3.w, t, c3.z), t, c3.y), t, c3.x);
       __stcs(out + k4, o);
     }
   }
@@ -200,12 +199,12 @@ radial_table_bwd_kernel(int wn, long long E, float inv_h, int n_grid, const floa
     const float4* g = reinterpret_cast<const float4*>(dw + (size_t)e * wn);
     float acc = 0.f;
     for (int k4 = lane; k4 < q; k4 += 32) {
-      const float4 b = __ldg(row + q + k4), c = __ldg(row + 2 * q + k4), d = __ldg(row + 3 * q + k4);
+      const float4 c0 = __ldg(row + 4 * k4), c1 = __ldg(row + 4 * k4 + 1), c2 = __ldg(row + 4 * k4 + 2), c3 = __ldg(row + 4 * k4 + 3);
       const float4 gg = __ldcs(g + k4);
-      acc = fmaf(gg.x, fmaf(d.x, t3, fmaf(c.x, t2, b.x)), acc);
-      acc = fmaf(gg.y, fmaf(d.y, t3, fmaf(c.y, t2, b.y)), acc);
-      acc = fmaf(gg.z, fmaf(d.z, t3, fmaf(c.z, t2, b.z)), acc);
-      acc = fmaf(gg.w, fmaf(d.w, t3, fmaf(c.w, t2, b.w)), acc);
+      acc = fmaf(gg.x, fmaf(c0.w, t3, fmaf(c0.z, t2, c0.y)), acc);
+      acc = fmaf(gg.y, fmaf(c1.w, t3, fmaf(c1.z, t2, c1.y)), acc);
+      acc = fmaf(gg.z, fmaf(c2.w, t3, fmaf(c2.z, t2, c2.y)), acc);
+      acc = fmaf(gg.w, fmaf(c3.w, t3, fmaf(c3.z, t2, c3.y)), acc);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);

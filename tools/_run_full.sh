@@ -1,7 +1,6 @@
 cd /root/repo
-timeout 1500 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err
-echo "rc=$?" >> gpurun_out/bench_default.err
-timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_reference.json 2>> gpurun_out/bench_default.err
-timeout 600 python bench.py --impl reference --workload finetune --steps 1 --warmup 1 > gpurun_out/bench_reference_ft.json 2>> gpurun_out/bench_default.err
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/md_launches.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-finetune > gpurun_out/md_ncu.log 2>&1
-echo "ncu rc=$?" >> gpurun_out/bench_default.err
+timeout 900 ncu --set full --import-source on --clock-control none -k regex:"conv_bwde_kernel|conv_fwd_kernel" --launch-skip 30 --launch-count 18 -o /tmp/conv_tab python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-finetune > gpurun_out/conv_ncu.log 2>&1
+echo "ncu rc=$?" > gpurun_out/conv_ncu.err
+ncu -i /tmp/conv_tab.ncu-rep --page raw --csv > gpurun_out/conv_tab_raw.csv 2>/dev/null
+ncu -i /tmp/conv_tab.ncu-rep --page details --csv > gpurun_out/conv_tab_details.csv 2>/dev/null
+ls -la /tmp/conv_tab.ncu-rep >> gpurun_out/conv_ncu.err
