@@ -118,7 +118,11 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
     tc_fence_before();
   };
 
-  // per-thread gather slots (fixed over the chunks): element it = tid + j * L_T of the [TN][16][D] chunk
+  // per-thread gather slots (fixed over the chunks).  A warp fills one 8-row x 16-byte core matrix group per slot
+  // (lane -> row = lane / 4, k = lane % 4 inside a 4-k unit): its 32 stores land in 128 contiguous bytes of the operand
+  // tile - no bank conflicts (the former mapping, lanes along the contiguous (k, m) index of a node, was 4-way conflicted
+  // and spent 30 % of the kernel on the shared-memory store pipe: profiles/r01n_finetune_linear_tc_ncu_raw.csv).  The four
+  // k-units of the same rows are consecutive slots of the warp, so the 32-byte sectors of the gathered rows are reused from L1.
   const int span = LK * D;
   int gnl[L_GPT];            // node of the slot, -1: unused
   uint32_t goff[L_GPT];      // byte offset of the element in the operand tile
@@ -126,12 +130,14 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
   int gk[L_GPT];
 #pragma unroll
   for (int j = 0; j < L_GPT; ++j) {
-    const int it = threadIdx.x + j * L_T;
-    const int nl = it / span, km = it % span, k = km / D, m = km % D;
-    gnl[j] = it < TN * span ? nl : -1;
+    const int U = warp + j * (L_T / 32);
+    const int kc = U & 3, rb = U >> 2;
+    const int row = rb * 8 + (lane >> 2), k = kc * 4 + (lane & 3);
+    const int nl = row / D, m = row % D;
+    gnl[j] = row < TN * D ? nl : -1;
     gk[j] = k;
-    goff[j] = (uint32_t)(k >> 2) * L_ACH + (uint32_t)(nl * D + m) * 16 + (uint32_t)(k & 3) * 4;
-    gptr[j] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + km;
+    goff[j] = (uint32_t)kc * L_ACH + (uint32_t)row * 16 + (uint32_t)(lane & 3) * 4;
+    gptr[j] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + k * D + m;
   }
   auto gload = [&](int c, int j) -> float {
     return (gnl[j] >= 0 && gnl[j] < nn && c * LK + gk[j] < b.K) ? __ldg(gptr[j] + (size_t)c * span) : 0.f;
