@@ -6,13 +6,14 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libsevennet_b200.so')
+DRIVER = os.path.join(HERE, 'b200_pair_driver')   # stand-alone C++ caller of the C-ABI (csrc/pair_driver.cpp)
 SOURCES = ['capi.cu', 'conv.cu', 'edge.cu', 'radial.cu', 'radial_tc.cu', 'radial_table.cu', 'fused.cu', 'linear.cu', 'linear_tc.cu', 'node.cu', 'graph.cu', 'engine.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '--use_fast_math=false', '-Xcompiler', '-fPIC', '-Xcompiler', '-O2']
 
 
 def _stale():
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(DRIVER):
         return True
     t = os.path.getmtime(LIB)
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [
@@ -43,6 +44,9 @@ def build(force=False, verbose=False):
         raise RuntimeError('nvcc failed')
     subprocess.check_call([nvcc, '-shared', '-o', LIB] + objs + ['-gencode', 'arch=compute_100a,code=sm_100a',
                                                                    '-lcudart'])
+    # the native caller: plain C++ against include/sevennet_b200.h, no torch, no Python
+    subprocess.check_call([nvcc, '-O2', '-std=c++17', os.path.join(CSRC, 'pair_driver.cpp'), '-o', DRIVER, '-L' + HERE,
+                           '-lsevennet_b200', '-lcudart', '-Xlinker', '-rpath', '-Xlinker', '$ORIGIN'])
     return LIB
 
 

@@ -20,6 +20,8 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(h, name), f'{name} declared in include/sevennet_b200.h but not exported'
     assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
     assert h.b200_version() >= 1
+    # the stand-alone C++ caller (csrc/pair_driver.cpp) is built and linked against the same library
+    assert os.path.exists(build.DRIVER) and os.access(build.DRIVER, os.X_OK)
 
 
 def test_struct_layouts_match_header():

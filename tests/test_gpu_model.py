@@ -177,3 +177,54 @@ def test_open_cluster_with_isolated_atom(model, weights):
     assert np.abs(f - f64).max() <= 1e-5 * max(1.0, float(np.abs(f64).max()) / 5.0)
     assert (f[-1] == 0).all()
     assert np.abs(out['atomic_energy'].cpu().numpy().ravel() - ae64).max() <= 1e-5
+
+
+def _write_driver_inputs(tmp, g, weights, cutoff=5.0):
+    """binary inputs of sevennet_finetuning_b200/csrc/pair_driver.cpp (formats in its header comment)"""
+    import struct
+    from sevennet_finetuning_b200 import ops
+    from sevennet_finetuning_b200.model import SEVENNET0_CONFIG as cfg
+    n = len(g['pos'])
+    with open(tmp / 'structure.bin', 'wb') as f:
+        f.write(struct.pack('<i3id', n, 1, 1, 1, cutoff))
+        f.write(np.asarray(g['cell'], np.float64).tobytes())
+        f.write(np.asarray(g['pos'], np.float64).tobytes())
+        f.write(np.asarray(g['types'], np.int32).tobytes())
+    nl = cfg['num_convolution_layer']
+    with open(tmp / 'weights.bin', 'wb') as f:
+        f.write(struct.pack('<ii', nl, cfg['num_species']))
+        for ir in cfg['irreps_manual']:
+            f.write(struct.pack('<3i', *ops.muls_of(ir)))
+        f.write(struct.pack('<2i', *cfg['weight_nn_hidden_neurons']))
+        f.write(struct.pack('<iiii', ops.muls_of(cfg['irreps_manual'][-1])[0] // 2, 1, 1, cfg['bessel_basis_num']))   # XPLOR, species-wise
+        f.write(struct.pack('<fff', cfg['cutoff'], cfg['cutoff_function']['cutoff_on'], 6.0))
+        f.write(struct.pack('<i', len(weights)))
+        for k, v in weights.items():
+            a = np.ascontiguousarray(v, np.float32).reshape(-1)
+            f.write(struct.pack('<i', len(k)) + k.encode() + struct.pack('<q', a.size) + a.tobytes())
+
+
+def test_native_pair_driver(gold, weights, tmp_path):
+    """The C++ caller of the C-ABI (no Python, no torch on its path): what PairE3GNN::compute does per step
+    (pair_e3gnn.cpp:72-275) - neighbour list, model call, energy / forces / virial back - on Si-216, against the float64
+    oracle values of the golden file."""
+    import subprocess
+    from sevennet_finetuning_b200 import build
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    g = gold('si216.npz')
+    _write_driver_inputs(tmp_path, g, weights)
+    r = subprocess.run([build.DRIVER, str(tmp_path / 'structure.bin'), str(tmp_path / 'weights.bin'), str(tmp_path / 'out.bin'), '3'],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(tmp_path / 'out.bin', 'rb').read()
+    n = len(g['pos'])
+    n_edges = np.frombuffer(raw, np.int64, 1, 0)[0]
+    vals = np.frombuffer(raw, np.float32, 1 + n + 3 * n + 6, 16)
+    e, ae, f, vir = float(vals[0]), vals[1:1 + n], vals[1 + n:1 + 4 * n].reshape(n, 3), vals[1 + 4 * n:]
+    assert n_edges == g['edge_index'].shape[1] if 'edge_index' in g else n_edges == 6048
+    assert abs(e - float(g['o64_energy'])) / n <= 1e-6
+    assert np.abs(ae - g['o64_atomic_energy'].reshape(-1)).max() <= 1e-5
+    assert np.abs(f - g['o64_force']).max() <= 1e-5
+    vol = abs(np.linalg.det(g['cell']))
+    assert np.abs(-vir / vol - g['o64_stress'].reshape(-1)).max() <= 1e-4 * np.abs(g['o64_stress']).max()

@@ -1,3 +1,2 @@
 cd /root/repo
-timeout 900 python bench.py --no-cpu-baseline --steps 4 > gpurun_out/md_bench.json 2> gpurun_out/md_bench.err
-echo "rc=$?" >> gpurun_out/md_bench.err
+timeout 900 python -m pytest tests/test_gpu_model.py -q -m gpu -k "native or efs" 2>&1 | tail -12 > gpurun_out/t_all.log
