@@ -76,13 +76,11 @@ __global__ void linear_prepack_kernel(LinTcPlan pl, const float* __restrict__ W,
 // round-to-nearest adds; the two small cross products (lo*hi, hi*lo) of the step are issued first into the same
 // accumulator, so the large product is added (one truncation) to a sum that is 2^-11 of its size.  Four accumulators
 // of 64 columns = 256 TMEM columns per CTA: two CTAs share an SM and hide each other's gather and drain latency.
-__global__ void __launch_bounds__(L_T, 2)
-irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, const float* __restrict__ pack,
-                        float* __restrict__ y, int accumulate) {
-  extern __shared__ __align__(128) uint8_t smem_raw[];
-  LinTcSmem& s = *reinterpret_cast<LinTcSmem*>(smem_raw);
-  const LinTcBlock b = pl.p[blockIdx.y];
-  const int D = b.D, TN = 128 / D;               // nodes per tile
+template <int D>
+__device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, const LinTcBlock& b, int n_nodes,
+                                         const float* __restrict__ x, const float* __restrict__ pack,
+                                         float* __restrict__ y, int accumulate) {
+  constexpr int TN = 128 / D;                    // nodes per tile
   const int n0 = blockIdx.x * TN;
   if (n0 >= n_nodes) return;
   const int nn = min(TN, n_nodes - n0);
@@ -118,33 +116,35 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
     tc_fence_before();
   };
 
-  // per-thread gather slots (fixed over the chunks).  A warp fills one 8-row x 16-byte core matrix group per slot
-  // (lane -> row = lane / 4, k = lane % 4 inside a 4-k unit): its 32 stores land in 128 contiguous bytes of the operand
-  // tile - no bank conflicts (the former mapping, lanes along the contiguous (k, m) index of a node, was 4-way conflicted
-  // and spent 30 % of the kernel on the shared-memory store pipe: profiles/r01n_finetune_linear_tc_ncu_raw.csv).  The four
-  // k-units of the same rows are consecutive slots of the warp, so the 32-byte sectors of the gathered rows are reused from L1.
-  const int span = LK * D;
-  int gnl[L_GPT];            // node of the slot, -1: unused
-  uint32_t goff[L_GPT];      // byte offset of the element in the operand tile
-  const float* gptr[L_GPT];  // its address in chunk 0
-  int gk[L_GPT];
+  // Gather mapping: thread -> one row (node, m) of the tile and 8 of the chunk's 16 k (two 4-k units).  A warp covers 32
+  // consecutive rows, so its 16-byte operand stores are one contiguous 512-byte run (no bank conflicts) and the loop
+  // carries one pointer: 8 loads at compile-time offsets j*D, 8 hi/lo splits and 4 vector stores per chunk (the first
+  // version kept 8 independent slots per thread with per-slot predicates and addresses: 41 instructions per element,
+  // 590 per chunk, and the kernel was issue bound with the tensor pipe idle).  Rows past the last node of the tile (the
+  // 128 - TN*D spare rows, or a short last tile) re-read the last valid node: tile rows are independent in the product
+  // and those rows are never stored.
+  const int row = threadIdx.x & 127, kp = threadIdx.x >> 7;
+  const float* gp = x + (size_t)(n0 + min(row / D, nn - 1)) * pl.ldx + b.xoff + (kp * 8) * D + row % D;
+  const uint32_t aoff = (uint32_t)(2 * kp) * L_ACH + (uint32_t)row * 16;
+  const bool vec = D == 1 && ((pl.ldx | b.xoff) & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+  auto gload = [&](int c, float (&v)[8]) {
+    const int left = b.K - c * LK - kp * 8;      // valid k of this thread's half chunk
+    if (left >= 8) {
+      if (vec) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(gp)), bq = __ldg(reinterpret_cast<const float4*>(gp) + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = bq.x; v[5] = bq.y; v[6] = bq.z; v[7] = bq.w;
+      } else {
 #pragma unroll
-  for (int j = 0; j < L_GPT; ++j) {
-    const int U = warp + j * (L_T / 32);
-    const int kc = U & 3, rb = U >> 2;
-    const int row = rb * 8 + (lane >> 2), k = kc * 4 + (lane & 3);
-    const int nl = row / D, m = row % D;
-    gnl[j] = row < TN * D ? nl : -1;
-    gk[j] = k;
-    goff[j] = (uint32_t)kc * L_ACH + (uint32_t)row * 16 + (uint32_t)(lane & 3) * 4;
-    gptr[j] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + k * D + m;
-  }
-  auto gload = [&](int c, int j) -> float {
-    return (gnl[j] >= 0 && gnl[j] < nn && c * LK + gk[j] < b.K) ? __ldg(gptr[j] + (size_t)c * span) : 0.f;
+        for (int j = 0; j < 8; ++j) v[j] = __ldg(gp + j * D);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] = j < left ? __ldg(gp + j * D) : 0.f;
+    }
+    gp += LK * D;
   };
-  float gv[L_GPT];
-#pragma unroll
-  for (int j = 0; j < L_GPT; ++j) gv[j] = gload(0, j);
+  float gv[8];
+  gload(0, gv);
 
   for (int c = 0; c < b.nchunk; ++c) {
     const int st = c & 1;
@@ -159,26 +159,17 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
       bulk_copy_g2s(s.B[st], src, bpart, &s.full_b[st]);
       bulk_copy_g2s(s.B[st] + L_BPART, src + bpart / 4, bpart, &s.full_b[st]);
     }
-    // gather the A chunk: element (node nl, k, m) -> row nl*D+m, column k; lanes run along the contiguous (k, m) index.
-    // The values of the NEXT chunk are requested before this chunk's are split and stored (one round trip hidden).
-#pragma unroll
-    for (int j = 0; j < L_GPT; ++j) {
-      const float v = gv[j];
-      if (c + 1 < b.nchunk) gv[j] = gload(c + 1, j);
-      if (gnl[j] >= 0) {
-        float hi, lo;
-        split_tf32(v, hi, lo);
-        *reinterpret_cast<float*>(s.A[st] + goff[j]) = hi;
-        *reinterpret_cast<float*>(s.A[st] + L_APART + goff[j]) = lo;
-      }
-    }
-    if (TN * D < 128) {   // rows of the tile that belong to no node (128 is not a multiple of 2l+1)
-      for (int it = threadIdx.x; it < (128 - TN * D) * LK; it += L_T) {
-        const int r = TN * D + it / LK, k = it % LK;
-        const uint32_t off = (uint32_t)(k >> 2) * L_ACH + (uint32_t)r * 16 + (uint32_t)(k & 3) * 4;
-        *reinterpret_cast<float*>(s.A[st] + off) = 0.f;
-        *reinterpret_cast<float*>(s.A[st] + L_APART + off) = 0.f;
-      }
+    // split this chunk's values and store them; the NEXT chunk's loads are issued first (one round trip hidden)
+    {
+      float4 h0, l0, h1, l1;
+      split4(make_float4(gv[0], gv[1], gv[2], gv[3]), h0, l0);
+      split4(make_float4(gv[4], gv[5], gv[6], gv[7]), h1, l1);
+      if (c + 1 < b.nchunk) gload(c + 1, gv);
+      uint8_t* a = s.A[st] + aoff;
+      *reinterpret_cast<float4*>(a) = h0;
+      *reinterpret_cast<float4*>(a + L_ACH) = h1;
+      *reinterpret_cast<float4*>(a + L_APART) = l0;
+      *reinterpret_cast<float4*>(a + L_APART + L_ACH) = l1;
     }
     fence_proxy_async();
     tc_fence_before();
@@ -224,6 +215,19 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem, 256);
+}
+
+__global__ void __launch_bounds__(L_T, 2)
+irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, const float* __restrict__ pack,
+                        float* __restrict__ y, int accumulate) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  LinTcSmem& s = *reinterpret_cast<LinTcSmem*>(smem_raw);
+  const LinTcBlock& b = pl.p[blockIdx.y];
+  switch (b.D) {   // 2l+1 as a compile-time constant: row <-> (node, m) without integer division
+    case 1: lin_tile<1>(s, pl, b, n_nodes, x, pack, y, accumulate); break;
+    case 3: lin_tile<3>(s, pl, b, n_nodes, x, pack, y, accumulate); break;
+    default: lin_tile<5>(s, pl, b, n_nodes, x, pack, y, accumulate); break;
+  }
 }
 
 // plan: one pass per (block, <=256 output columns); returns false when a block is too small for the tensor-core path
