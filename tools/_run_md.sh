@@ -1,4 +1,4 @@
 cd /root/repo
-timeout 1500 python -m pytest tests -q -m gpu -x 2>&1 | tail -5 > gpurun_out/t_all.log
-timeout 600 python bench.py --no-finetune > gpurun_out/b_md.json 2> gpurun_out/b_md.err
-timeout 600 python bench.py --workload finetune > gpurun_out/b_ft.json 2> gpurun_out/b_ft.err
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_ops.py -q -m gpu -x -k "linear" 2>&1 | tail -5 > gpurun_out/t_all.log
+timeout 300 python tools/lin_time.py > gpurun_out/lin_time.log 2>&1
