@@ -10,7 +10,7 @@ import torch
 import torch.nn as nn
 
 from .refnn import (BesselBasis, EdgeEmbedding, EquivariantGate, IrrepsConvolution,
-                    IrrepsLinear, PolynomialCutoff, SelfConnectionLinearIntro,
+                    IrrepsLinear, PolynomialCutoff, SelfConnectionIntro, SelfConnectionLinearIntro,
                     SelfConnectionOutro, SphericalEncoding, XPLORCutoff, irreps_str,
                     parse_irreps, sh_irreps)
 
@@ -234,7 +234,10 @@ def build_model(config=None, force_from='edge'):
         irreps_out_tp = [(1, l, p) for l, p in tp_target]
         gate = EquivariantGate(irreps_out, cfg['act_scalar'], cfg['act_gate'])
         gin = gate.get_gate_irreps_in()
-        L[f'{t}_self_connection_intro'] = SelfConnectionLinearIntro(irreps_x, gin)
+        if cfg['self_connection_type'] == 'nequip':   # model_build.py:45-56
+            L[f'{t}_self_connection_intro'] = SelfConnectionIntro(irreps_x, f'{nsp}x0e', gin)
+        else:
+            L[f'{t}_self_connection_intro'] = SelfConnectionLinearIntro(irreps_x, gin)
         L[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, 'x')
         conv = IrrepsConvolution(irreps_x, irreps_filter, irreps_out_tp,
                                  [cfg['radial_basis']['bessel_basis_num']] + cfg['weight_nn_hidden_neurons'],

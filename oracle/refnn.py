@@ -394,6 +394,53 @@ class SelfConnectionLinearIntro(nn.Module):
         return data
 
 
+class SelfConnectionIntro(nn.Module):
+    """``sevenn/nn/self_connection.py:11-38`` ('nequip' self connection): e3nn
+    ``FullyConnectedTensorProduct(irreps_x, irreps_operand, irreps_out)`` of the node features with
+    the one-hot species vector (``irreps_operand = '{n_species}x0e'``, ``interaction_blocks.py:43-52``).
+    e3nn is not vendored; the arithmetic follows the frozen graph of the reference's own example
+    model (``example_inputs/md_serial_example/deployed_serial.pt``, forward() lines 331-356):
+    per l-block ``out[n,w,m] = sum_{u,v} x[n,u,m] onehot[n,v] W[u,v,w] / sqrt(mul_in n_species)``
+    (the Wigner 3j of (l,0,l) and the component normalisation cancel), flat weight = concat of
+    W.flatten() over the blocks in input order.  Pinned by tests/golden/fctp_hfo.npz."""
+
+    def __init__(self, irreps_x, irreps_operand, irreps_out, data_key_x='x',
+                 data_key_operand='node_attr', **kw):
+        super().__init__()
+        self.irreps_x, self.irreps_out = parse_irreps(irreps_x), parse_irreps(irreps_out)
+        self.nsp = parse_irreps(irreps_operand)[0][0]
+        self.key_x, self.key_operand = data_key_x, data_key_operand
+        self.instr = [(i, j) for i, (_, l1, p1) in enumerate(self.irreps_x)
+                      for j, (_, l2, p2) in enumerate(self.irreps_out) if (l1, p1) == (l2, p2)]
+        fan = {}
+        for i, j in self.instr:
+            fan[j] = fan.get(j, 0) + self.irreps_x[i][0] * self.nsp
+        self.path_weight = [1.0 / math.sqrt(fan[j]) for _, j in self.instr]
+        n = sum(self.irreps_x[i][0] * self.nsp * self.irreps_out[j][0] for i, j in self.instr)
+        holder = nn.Module()
+        holder.weight = nn.Parameter(torch.randn(n))
+        self.fc_tensor_product = holder
+
+    def forward(self, data):
+        x, onehot = data[self.key_x], data[self.key_operand].to(data[self.key_x].dtype)
+        N = x.shape[0]
+        offs_in = np.cumsum([0] + [m * (2 * l + 1) for m, l, _ in self.irreps_x])
+        outs = [None] * len(self.irreps_out)
+        w_off = 0
+        for (i, j), pw in zip(self.instr, self.path_weight):
+            mi, l, _ = self.irreps_x[i]
+            mo = self.irreps_out[j][0]
+            W = self.fc_tensor_product.weight[w_off:w_off + mi * self.nsp * mo].view(mi, self.nsp, mo)
+            w_off += mi * self.nsp * mo
+            xi = x[:, offs_in[i]:offs_in[i + 1]].reshape(N, mi, 2 * l + 1)
+            y = torch.einsum('num,nv,uvw->nwm', xi, onehot, W) * pw
+            outs[j] = y if outs[j] is None else outs[j] + y
+        res = [x.new_zeros(N, mo * (2 * l + 1)) if outs[j] is None else outs[j].reshape(N, mo * (2 * l + 1))
+               for j, (mo, l, _) in enumerate(self.irreps_out)]
+        data['self_cont_tmp'] = torch.cat(res, -1)
+        return data
+
+
 class SelfConnectionOutro(nn.Module):
     """``sevenn/nn/self_connection.py:93-109``."""
 

@@ -44,6 +44,9 @@ class B200SevenNet:
         cfg = dict(SEVENNET0_CONFIG)
         cfg.update(config or {})
         self.config = cfg
+        if cfg.get('self_connection_type', 'linear') != 'linear':
+            raise RuntimeError("B200SevenNet: the fused engine implements the 'linear' self connection (SevenNet-0); "
+                               "'nequip' models run through the module API (nn.build_E3_equivariant_model)")
         self.device = torch.device(device)
         mc = ModelConfig()
         nl = cfg['num_convolution_layer']

@@ -333,6 +333,58 @@ class SelfConnectionLinearIntro(nn.Module):
         return data
 
 
+def _species_groups(data):
+    """[(species, node indices)] of the batch and the permutation that undoes their concatenation; one host sync per
+    forward (cached in the dict, all layers share it)."""
+    g = data.get('_b200_species_groups')
+    if g is None:
+        t = data['atom_type']
+        order = torch.argsort(t, stable=True)
+        counts = torch.bincount(t).tolist()
+        groups, o = [], 0
+        for sp, c in enumerate(counts):
+            if c > 0:
+                groups.append((sp, order[o:o + c]))
+                o += c
+        inv = torch.empty_like(order)
+        inv[order] = torch.arange(order.numel(), device=order.device)
+        g = data['_b200_species_groups'] = (groups, inv)
+    return g
+
+
+class SelfConnectionIntro(nn.Module):
+    """sevenn/nn/self_connection.py:11-38 ('nequip' self connection): FullyConnectedTensorProduct of the node features
+    with the one-hot species vector, parameter ``fc_tensor_product.weight`` = concat over the l-blocks of
+    W[mul_in, n_species, mul_out].  With a one-hot operand this is an irreps linear whose weight matrix is chosen by the
+    node's species, W[:, type_n, :] / sqrt(mul_in n_species): the nodes are grouped by species and each group runs the
+    irreps-linear kernels (and their closed reverse / second-order family) with its slice of the weight."""
+
+    def __init__(self, irreps_x, irreps_operand, irreps_out, data_key_x='x', data_key_operand='node_attr', **kwargs):
+        super().__init__()
+        self.irreps_x, self.irreps_out, self.key_x, self.key_operand = irreps_x, irreps_out, data_key_x, data_key_operand
+        self.nsp = ops.muls_of(irreps_operand)[0]
+        self.desc, self.numel = ops.make_lin_desc(irreps_x, irreps_out)
+        self.fc_tensor_product = IrrepsLinear._Holder(self.numel * self.nsp)
+        # position of W_b[u, s, w] in the flat FCTP weight for every position (b, u, w) of the linear's flat weight
+        sel = torch.empty(self.nsp, self.numel, dtype=torch.long)
+        for k in range(self.desc.nblk):
+            b = self.desc.blk[k]
+            u = torch.arange(b.mul_in).view(-1, 1)
+            w = torch.arange(b.mul_out).view(1, -1)
+            for sp in range(self.nsp):
+                sel[sp, b.w_off:b.w_off + b.mul_in * b.mul_out] = (self.nsp * b.w_off + (u * self.nsp + sp) * b.mul_out + w).reshape(-1)
+        self.register_buffer('_sel', sel, persistent=False)
+
+    def forward(self, data):
+        x = data[self.key_x]
+        groups, inv = _species_groups(data)
+        fn = ho.LinF if _second_order(self) else _LinearFn
+        W = self.fc_tensor_product.weight * (1.0 / math.sqrt(self.nsp))
+        ys = [fn.apply(x.index_select(0, idx), W.index_select(0, self._sel[sp]), self.desc, self.numel) for sp, idx in groups]
+        data['self_cont_tmp'] = torch.cat(ys, 0).index_select(0, inv)
+        return data
+
+
 class SelfConnectionOutro(nn.Module):
     """sevenn/nn/self_connection.py:93-109."""
 
@@ -559,7 +611,7 @@ class AtomGraphSequential(nn.Sequential):
 
 
 def build_E3_equivariant_model(config=None):
-    """The module chain of ``sevenn/model_build.py:186-445`` ('nequip' interaction, 'linear' self connection,
+    """The module chain of ``sevenn/model_build.py:186-445`` ('nequip' interaction, 'linear' or 'nequip' self connection,
     ``irreps_manual``) with the reference's module names, built from the B200 twins."""
     from .model import SEVENNET0_CONFIG
     cfg = dict(SEVENNET0_CONFIG)
@@ -584,7 +636,10 @@ def build_E3_equivariant_model(config=None):
         tp_out = '+'.join(f'1x{l}e' for l in range(lmax_node + 1))
         gate = EquivariantGate(irreps_out)
         gin = gate.get_gate_irreps_in()
-        L[f'{t}_self_connection_intro'] = SelfConnectionLinearIntro(irreps_x, gin)
+        if cfg.get('self_connection_type', 'linear') == 'nequip':   # model_build.py:45-56
+            L[f'{t}_self_connection_intro'] = SelfConnectionIntro(irreps_x, f'{nsp}x0e', gin)
+        else:
+            L[f'{t}_self_connection_intro'] = SelfConnectionLinearIntro(irreps_x, gin)
         L[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, 'x')
         conv = IrrepsConvolution(irreps_x, '1x0e+1x1e+1x2e', tp_out,
                                  [cfg['bessel_basis_num']] + list(cfg['weight_nn_hidden_neurons']), 'silu', den[t])
@@ -614,7 +669,7 @@ def build_E3_equivariant_model(config=None):
     return AtomGraphSequential(L, cutoff)
 
 
-_TWINS = ('EdgeEmbedding', 'OnehotEmbedding', 'IrrepsLinear', 'SelfConnectionLinearIntro', 'SelfConnectionOutro',
+_TWINS = ('EdgeEmbedding', 'OnehotEmbedding', 'IrrepsLinear', 'SelfConnectionLinearIntro', 'SelfConnectionIntro', 'SelfConnectionOutro',
           'IrrepsConvolution', 'EquivariantGate', 'Rescale', 'SpeciesWiseRescale', 'AtomReduce', 'ForceStressOutputFromEdge')
 
 

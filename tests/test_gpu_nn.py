@@ -368,3 +368,91 @@ def test_rehearsal_ewc_step(weights):
     fish, opt, cnt = tr.compute_fisher_matrix([ft.collate(graphs[:1], dev), ft.collate(graphs[1:2], dev)])
     assert cnt == 2 and set(fish) == set(dict(tr.model.named_parameters()))
     assert all(torch.isfinite(v).all() and float(v.min()) >= 0 for v in fish.values())
+
+
+def test_nequip_self_connection_twin(gold):
+    """SelfConnectionIntro twin ('nequip' self connection): values against the frozen-graph golden
+    vectors (multiplicities below the tensor-core kernel's minimum: FFMA kernel) and, at SevenNet-0 widths with all three
+    l-blocks, values, first and second derivatives against the float64 oracle."""
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    from oracle.refnn import SelfConnectionIntro as Ref
+    from sevennet_finetuning_b200 import nn as b200nn
+    dev = torch.device('cuda:0')
+    g = gold('fctp_hfo.npz')
+    m = b200nn.SelfConnectionIntro('4x0e+4x1e', '2x0e', '12x0e+4x1e').to(dev).eval()
+    with torch.no_grad():
+        m.fc_tensor_product.weight.copy_(torch.tensor(np.concatenate([g['w0'].reshape(-1), g['w1'].reshape(-1)])))
+    t = torch.tensor(g['types'], device=dev)
+    out = m({'x': torch.tensor(g['x'], device=dev), 'atom_type': t})['self_cont_tmp']
+    assert np.abs(out.detach().cpu().numpy() - g['out']).max() <= 2e-6
+
+    ir_x, ir_o, nsp, n = '128x0e+64x1e+32x2e', '224x0e+64x1e+32x2e', 5, 700
+    gen = torch.Generator().manual_seed(3)
+    x = torch.randn(n, 480, generator=gen, dtype=torch.float64)
+    types = torch.randint(0, nsp, (n,), generator=gen)
+    types[types == 3] = 1                                   # one species absent from the batch
+    ref = Ref(ir_x, f'{nsp}x0e', ir_o).double()
+    tw = b200nn.SelfConnectionIntro(ir_x, f'{nsp}x0e', ir_o).to(dev)
+    tw.load_state_dict({k: v.float() for k, v in ref.state_dict().items()}, strict=True)
+    probe = torch.randn(n, 576, generator=gen, dtype=torch.float64)
+    v = torch.randn(n, 480, generator=gen, dtype=torch.float64)
+
+    def run(mod, xx, tt, pr, vv, dt):
+        mod.train()
+        xx = xx.to(dt).requires_grad_(True)
+        d = {'x': xx, 'atom_type': tt, 'node_attr': torch.nn.functional.one_hot(tt, nsp).to(dt)}
+        y = mod(d)['self_cont_tmp']
+        gx, = torch.autograd.grad((y * pr.to(dt)).sum() + (y * y).sum() * 0.5, xx, create_graph=True)
+        W = mod.fc_tensor_product.weight
+        gW, = torch.autograd.grad((gx * vv.to(dt)).sum(), W)          # second order: d/dW of a contraction of dL/dx
+        return y.detach(), gx.detach(), gW
+
+    y0, gx0, gW0 = run(ref, x, types, probe, v, torch.float64)
+    y1, gx1, gW1 = run(tw, x.to(dev), types.to(dev), probe.to(dev), v.to(dev), torch.float32)
+    for a, b_, name in ((y0, y1, 'y'), (gx0, gx1, 'dx'), (gW0, gW1, 'dW')):
+        err = (a - b_.double().cpu()).abs().max() / a.abs().max()
+        assert err <= 2e-5, (name, float(err))
+    assert float(gW1.reshape(-1)[tw._sel[3].to(dev)].abs().max()) == 0.0   # the absent species' slice gets no gradient
+
+
+def test_nequip_self_connection_model(gold, weights):
+    """A whole 'nequip' self-connection model (self_connection_type='nequip', model_build.py:45-56) on HfO2-96 through the
+    module chain: energy, forces, stress against the float64 oracle model with the same (seeded) parameters."""
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    from oracle.refmodel import build_model
+    from sevennet_finetuning_b200 import nn as b200nn
+    cfg = dict(self_connection_type='nequip', num_species=4, num_convolution_layer=3,
+               irreps_manual=['64x0e', '64x0e+32x1e+32x2e', '64x0e+32x1e+32x2e', '64x0e'],
+               shift=[-1.0, -2.0, 0.5, 0.0], scale=[1.0, 1.5, 0.7, 1.0], conv_denominator=30.0)
+    torch.manual_seed(11)
+    ref = build_model(cfg).double()
+    tw = b200nn.build_E3_equivariant_model(cfg)
+    res = tw.load_state_dict({k: v.float() for k, v in ref.state_dict().items()}, strict=True)
+    assert not res.missing_keys and not res.unexpected_keys
+    assert any(k.endswith('self_connection_intro.fc_tensor_product.weight') for k in tw.state_dict())
+    tw = tw.cuda().eval()
+    tw.set_is_batch_data(False)
+    ref.eval()
+    ref.set_is_batch_data(False)
+    g = gold('hfo2_96.npz')
+    dev = torch.device('cuda:0')
+    data, ei, D = _data(g, dev)
+    types = torch.tensor(g['types']) % 2 + torch.arange(len(g['types'])) % 2 * 2    # four species
+    data['x'] = types.to(dev)
+    out = tw(data)
+    d64 = {'x': types.clone(), 'edge_index': torch.tensor(ei), 'edge_vec': torch.tensor(D, dtype=torch.float32).double().requires_grad_(True),
+           'num_atoms': torch.tensor(len(types)), 'cell_volume': torch.tensor(abs(np.linalg.det(g['cell'])), dtype=torch.float64),
+           'batch': torch.zeros(len(types), dtype=torch.long)}
+    torch.set_default_dtype(torch.float64)   # the oracle builds its tables and one-hot rows in the default dtype
+    try:
+        o64 = ref(d64)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    n = len(types)
+    assert abs(float(out['inferred_total_energy']) - float(o64['inferred_total_energy'])) / n <= 2e-6
+    fe = (out['inferred_force'].detach().cpu().double() - o64['inferred_force'].detach()).abs().max()
+    assert fe <= 2e-5 * max(1.0, float(o64['inferred_force'].abs().max())), float(fe)
+    se = (out['inferred_stress'].detach().cpu().double() - o64['inferred_stress'].detach()).abs().max()
+    assert se <= 1e-4 * float(o64['inferred_stress'].abs().max()), float(se)

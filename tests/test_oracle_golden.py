@@ -104,3 +104,17 @@ def test_oracle_segment_intermediates(weights, gold):
                     ref = seg[f'x_after_seg{t - 1}']
                     got = d['x'].numpy()[rows]
                     assert np.abs(got - ref).max() <= 2e-5 * max(1.0, np.abs(ref).max()), name
+
+
+def test_nequip_self_connection_matches_frozen_graph(gold):
+    """oracle SelfConnectionIntro (FullyConnectedTensorProduct with the one-hot species vector, self_connection.py:11-38)
+    against the reference example model's own frozen-graph arithmetic and weights (oracle/make_golden_fctp.py)."""
+    from oracle.refnn import SelfConnectionIntro
+    g = gold('fctp_hfo.npz')
+    m = SelfConnectionIntro('4x0e+4x1e', '2x0e', '12x0e+4x1e')
+    with torch.no_grad():
+        m.fc_tensor_product.weight.copy_(torch.tensor(np.concatenate([g['w0'].reshape(-1), g['w1'].reshape(-1)])))
+    onehot = torch.nn.functional.one_hot(torch.tensor(g['types']), 2)
+    out = m({'x': torch.tensor(g['x']), 'node_attr': onehot})['self_cont_tmp']
+    assert out.shape == (len(g['x']), 24)
+    assert np.abs(out.detach().numpy() - g['out']).max() <= 1e-6
