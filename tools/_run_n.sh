@@ -1,6 +1,5 @@
 cd /root/repo
+mkdir -p gpurun_out
 N=$1
-timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/md_bench_n$N.json 2> gpurun_out/md_bench_n$N.err
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/md_bench_n$N.json 2> gpurun_out/md_bench_n$N.err
 echo "md rc=$?" >> gpurun_out/md_bench_n$N.err
-timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29535 bench.py --gpus $N --steps 3 --warmup 3 --atoms-per-gpu 262144 > gpurun_out/md_bench_n${N}_2M.json 2> gpurun_out/md_bench_n${N}_2M.err
-echo "md2M rc=$?" >> gpurun_out/md_bench_n${N}_2M.err
