@@ -245,7 +245,7 @@ int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W,
   if (n_nodes == 0) return B200_OK;
   // dense channel mixing belongs on the tensor cores (linear_tc.cu); tiny blocks and tiny inputs stay on the FFMA kernel
   static const bool force_ffma = getenv("B200_LINEAR_FFMA") && atoi(getenv("B200_LINEAR_FFMA")) != 0;
-  if (!force_ffma && n_nodes >= 64 && irreps_linear_tc_supported(d, transpose))
+  if (!force_ffma && n_nodes >= 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && irreps_linear_tc_supported(d, transpose))
     return irreps_linear_tc(d, n_nodes, x, W, y, transpose, accumulate, st);
   int maxn = 0;
   for (int i = 0; i < d.nblk; ++i) maxn = max(maxn, transpose ? d.blk[i].mul_in : d.blk[i].mul_out);

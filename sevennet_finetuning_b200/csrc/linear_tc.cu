@@ -21,8 +21,10 @@ constexpr int L_ACH = 128 * 16;        // bytes of one 16-byte K-chunk column of
 constexpr int L_APART = (LK / 4) * L_ACH;   // 8 KB (hi or lo)
 constexpr int L_MAXN = 64;             // output columns per pass
 constexpr int L_BPART = (LK / 4) * L_MAXN * 16;   // 4 KB (hi or lo)
-constexpr int L_T = 256;
-constexpr int L_GPT = (128 * LK + L_T - 1) / L_T;   // gather slots per thread
+constexpr int L_T = 256;               // worker threads
+constexpr int L_TT = L_T + 32;         // + the issuer warp
+constexpr int L_NS = 4;                // raw row staging slots (three chunks in flight)
+constexpr int L_SFLOATS = 128 * (LK + 4);   // floats of one slot: TN nodes x (16 (2l+1) + 4) <= 2560
 
 struct LinTcBlock {
   int D, K, N, Npad;          // 2l+1, contraction length, real / padded (multiple of 16) output columns of this pass
@@ -41,8 +43,9 @@ struct LinTcPlan {
 struct LinTcSmem {
   uint8_t A[2][2 * L_APART];
   uint8_t B[2][2 * L_BPART];
-  float T[L_T / 32][32][33];   // per-warp transposition scratch of the epilogue
-  uint64_t full_b[2], mma_done[2];
+  float S[L_NS][L_SFLOATS];    // raw fp32 rows of the coming chunks, filled by cp.async (the epilogue's per-warp
+                               // transposition scratch, 8 x 32 x 33 floats, reuses A and B)
+  uint64_t full_b[2], mma_done[2], a_full[2];
   uint32_t tmem_base;
 };
 
@@ -90,7 +93,7 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
 
   if (warp == 0) tmem_alloc(&s.tmem_base, 256);
   if (threadIdx.x == 32) {
-    for (int k = 0; k < 2; ++k) { mbar_init(&s.full_b[k], 1); mbar_init(&s.mma_done[k], 1); }
+    for (int k = 0; k < 2; ++k) { mbar_init(&s.full_b[k], 1); mbar_init(&s.mma_done[k], 1); mbar_init(&s.a_full[k], L_T / 32); }
     fence_mbar_init();
   }
   tc_fence_before();
@@ -98,6 +101,42 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
   tc_fence_after();
   const uint32_t tmem = s.tmem_base;
   const uint32_t idesc = make_idesc_tf32(128, b.Npad);
+  // Warp 8 is the issuer: one elected thread requests the weight chunks, waits for the operand stage the eight worker warps
+  // fill, and issues the MMAs.  The workers never wait for it (no CTA-wide barrier in the loop): a cycle-counter trace of the
+  // first version, where warp 0 both worked and issued, showed the whole CTA running at warp 0's pace - its own gather and
+  // drain (990 cycles) plus the wait for the weights and the issue of six MMAs behind the other CTA's (710 cycles) per chunk,
+  // with the other seven warps parked at the barrier for 840 of every 1850 cycles.
+  if (warp == L_T / 32) {
+    if (elect_one()) {
+      for (int c = 0; c < b.nchunk; ++c) {
+        const int st = c & 1;
+        if (c >= 2) mbar_wait(&s.mma_done[st], ((c - 2) >> 1) & 1);   // the weight stage is free
+        mbar_expect_tx(&s.full_b[st], 2 * bpart);
+        const float* src = pack + b.pack_off + (size_t)c * (2 * bpart / 4);
+        bulk_copy_g2s(s.B[st], src, bpart, &s.full_b[st]);
+        bulk_copy_g2s(s.B[st] + L_BPART, src + bpart / 4, bpart, &s.full_b[st]);
+        mbar_wait(&s.a_full[st], (c >> 1) & 1);    // operand written, accumulators of this stage drained
+        mbar_wait(&s.full_b[st], (c >> 1) & 1);
+        tc_fence_after();
+        const uint32_t ah = smem_u32(s.A[st]), al = ah + L_APART, bh = smem_u32(s.B[st]), bl = bh + L_BPART;
+        const uint32_t bch = (uint32_t)b.Npad * 16;
+        const uint32_t dmain = tmem + (uint32_t)(2 * (c & 1) * L_MAXN);
+#pragma unroll
+        for (int kk = 0; kk < LK / 8; ++kk) {
+          const uint64_t dah = make_desc(ah + kk * 2 * L_ACH, L_ACH, 128), dal = make_desc(al + kk * 2 * L_ACH, L_ACH, 128);
+          const uint64_t dbh = make_desc(bh + kk * 2 * bch, bch, 128), dbl = make_desc(bl + kk * 2 * bch, bch, 128);
+          mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dal, dbh, idesc, 0u);
+          mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbl, idesc, 1u);
+          mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbh, idesc, 1u);
+        }
+        mma_commit(&s.mma_done[st]);
+      }
+    }
+    __syncwarp();
+    tc_fence_before();
+    __syncthreads();      // the workers' last barrier (before the TMEM is released)
+    return;
+  }
   const uint32_t tlane = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(32 * half);
   const bool have_cols = 32 * half < b.Npad;
   float acc[32];
@@ -116,35 +155,48 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
     tc_fence_before();
   };
 
-  // Gather mapping: thread -> one row (node, m) of the tile and 8 of the chunk's 16 k (two 4-k units).  A warp covers 32
-  // consecutive rows, so its 16-byte operand stores are one contiguous 512-byte run (no bank conflicts) and the loop
-  // carries one pointer: 8 loads at compile-time offsets j*D, 8 hi/lo splits and 4 vector stores per chunk (the first
-  // version kept 8 independent slots per thread with per-slot predicates and addresses: 41 instructions per element,
-  // 590 per chunk, and the kernel was issue bound with the tensor pipe idle).  Rows past the last node of the tile (the
-  // 128 - TN*D spare rows, or a short last tile) re-read the last valid node: tile rows are independent in the product
-  // and those rows are never stored.
-  const int row = threadIdx.x & 127, kp = threadIdx.x >> 7;
-  const float* gp = x + (size_t)(n0 + min(row / D, nn - 1)) * pl.ldx + b.xoff + (kp * 8) * D + row % D;
-  const uint32_t aoff = (uint32_t)(2 * kp) * L_ACH + (uint32_t)row * 16;
-  const bool vec = D == 1 && ((pl.ldx | b.xoff) & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
-  auto gload = [&](int c, float (&v)[8]) {
-    const int left = b.K - c * LK - kp * 8;      // valid k of this thread's half chunk
-    if (left >= 8) {
-      if (vec) {
-        const float4 a = __ldg(reinterpret_cast<const float4*>(gp)), bq = __ldg(reinterpret_cast<const float4*>(gp) + 1);
-        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = bq.x; v[5] = bq.y; v[6] = bq.z; v[7] = bq.w;
-      } else {
+  // Operand A.  (1) Raw rows: the chunk's 16 (2l+1) floats of a node are contiguous, 4 (2l+1) pieces of 16 bytes; the
+  // tile's <= 512 pieces are two cp.async per worker thread, issued three chunks ahead into a 4-slot ring (node stride
+  // padded by 4 floats so that the reads below spread over the banks).  Pieces past the block's K are zero-filled
+  // (src-size operand); nodes past the end of a short last tile re-read the last valid node (tile rows are independent in
+  // the product and those rows are never stored).  Direct 4-byte loads of (row, k) elements, the former scheme, cost the
+  // L1 data pipe one sector per lane and load: 128M sector reads for 39M sectors of data, 72 % of the L1 cycles
+  // (profiles/r01q_linear_tc_raw.csv); the pieces move every sector once.
+  // (2) Split: thread -> one row (node, m) and 8 of the 16 k; a warp covers 32 consecutive rows, so its 16-byte operand
+  // stores are one contiguous 512-byte run.
+  constexpr int RS = LK * D + 4;                 // floats per node in a slot
+  constexpr int PPN = 4 * D;                     // 16-byte pieces per node and chunk
+  const float* psrc[2];
+  uint32_t pdst[2];
+  int pfl[2];                                    // float offset of the piece inside the node's chunk (huge: no piece)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = __ldg(gp + j * D);
+  for (int u = 0; u < 2; ++u) {
+    const int id = threadIdx.x + u * L_T, nl = id / PPN, p = id % PPN;
+    pfl[u] = id < TN * PPN ? p * 4 : (1 << 20);
+    psrc[u] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + p * 4;
+    pdst[u] = smem_u32(&s.S[0][0]) + (uint32_t)(nl * RS + p * 4) * 4;
+  }
+  auto stage = [&](int c) {                      // request chunk c (nothing past the last chunk; the group is still committed)
+    if (c < b.nchunk) {
+      const int kfl = min(LK, b.K - c * LK) * D; // valid floats of a node's chunk
+      const uint32_t slot = (uint32_t)(c % L_NS) * (L_SFLOATS * 4);
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int nb = min(16, max(0, (kfl - pfl[u]) * 4));
+        if (pfl[u] < (1 << 20))
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(pdst[u] + slot), "l"(psrc[u] + (size_t)c * (LK * D)), "r"(nb) : "memory");
       }
-    } else {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[j] = j < left ? __ldg(gp + j * D) : 0.f;
     }
-    gp += LK * D;
+    asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  float gv[8];
-  gload(0, gv);
+  const int row = threadIdx.x & 127, kp = threadIdx.x >> 7;
+  const int soff = min(row / D, TN - 1) * RS + kp * 8 * D + row % D;   // this thread's first element inside a slot
+  const uint32_t aoff = (uint32_t)(2 * kp) * L_ACH + (uint32_t)row * 16;
+  stage(0);
+  stage(1);
+  stage(2);
+  asm volatile("cp.async.wait_group 2;" ::: "memory");
+  bar_sync(1, L_T);
 
   for (int c = 0; c < b.nchunk; ++c) {
     const int st = c & 1;
@@ -153,18 +205,19 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
       tc_fence_after();
       drain(c - 2);
     }
-    if (warp == 0 && elect_one()) {
-      mbar_expect_tx(&s.full_b[st], 2 * bpart);
-      const float* src = pack + b.pack_off + (size_t)c * (2 * bpart / 4);
-      bulk_copy_g2s(s.B[st], src, bpart, &s.full_b[st]);
-      bulk_copy_g2s(s.B[st] + L_BPART, src + bpart / 4, bpart, &s.full_b[st]);
-    }
-    // split this chunk's values and store them; the NEXT chunk's loads are issued first (one round trip hidden)
+    stage(c + L_NS - 1);   // into the slot chunk c-1 was read from (all workers are past that iteration's barrier)
     {
-      float4 h0, l0, h1, l1;
-      split4(make_float4(gv[0], gv[1], gv[2], gv[3]), h0, l0);
-      split4(make_float4(gv[4], gv[5], gv[6], gv[7]), h1, l1);
-      if (c + 1 < b.nchunk) gload(c + 1, gv);
+      const float* sp = &s.S[c % L_NS][soff];
+      float4 v0, v1, h0, l0, h1, l1;
+      if (D == 1) {
+        v0 = *reinterpret_cast<const float4*>(sp);
+        v1 = *reinterpret_cast<const float4*>(sp + 4);
+      } else {
+        v0 = make_float4(sp[0], sp[D], sp[2 * D], sp[3 * D]);
+        v1 = make_float4(sp[4 * D], sp[5 * D], sp[6 * D], sp[7 * D]);
+      }
+      split4(v0, h0, l0);
+      split4(v1, h1, l1);
       uint8_t* a = s.A[st] + aoff;
       *reinterpret_cast<float4*>(a) = h0;
       *reinterpret_cast<float4*>(a + L_ACH) = h1;
@@ -173,23 +226,9 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
     }
     fence_proxy_async();
     tc_fence_before();
-    __syncthreads();
-    if (warp == 0 && elect_one()) {
-      mbar_wait(&s.full_b[st], (c >> 1) & 1);
-      tc_fence_after();
-      const uint32_t ah = smem_u32(s.A[st]), al = ah + L_APART, bh = smem_u32(s.B[st]), bl = bh + L_BPART;
-      const uint32_t bch = (uint32_t)b.Npad * 16;
-      const uint32_t dmain = tmem + (uint32_t)(2 * (c & 1) * L_MAXN);
-#pragma unroll
-      for (int kk = 0; kk < LK / 8; ++kk) {
-        const uint64_t dah = make_desc(ah + kk * 2 * L_ACH, L_ACH, 128), dal = make_desc(al + kk * 2 * L_ACH, L_ACH, 128);
-        const uint64_t dbh = make_desc(bh + kk * 2 * bch, bch, 128), dbl = make_desc(bl + kk * 2 * bch, bch, 128);
-        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dal, dbh, idesc, 0u);
-        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbl, idesc, 1u);
-        mma_tf32(dmain + (uint32_t)(kk * L_MAXN), dah, dbh, idesc, 1u);
-      }
-      mma_commit(&s.mma_done[st]);
-    }
+    warp_arrive(&s.a_full[st]);
+    asm volatile("cp.async.wait_group 2;" ::: "memory");   // own pieces of chunk c+1 have landed ...
+    bar_sync(1, L_T);                                       // ... and every worker's: the slot may be read
   }
   // the last two chunks (MMAs retire in order)
   for (int c = max(0, b.nchunk - 2); c < b.nchunk; ++c) {
@@ -198,7 +237,9 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
     drain(c);
   }
   // transpose the warp's 32x32 block so that the stores run along the output channels of one (node, m) row
-  float (*T)[33] = s.T[warp];
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  // the scratch lies over the operand stages: every MMA that reads them has retired (the waits above)
+  float (*T)[33] = reinterpret_cast<float (*)[33]>(&s.A[0][0]) + warp * 32;
 #pragma unroll
   for (int j = 0; j < 32; ++j) T[lane][j] = acc[j];
   __syncwarp();
@@ -217,7 +258,7 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
   if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
-__global__ void __launch_bounds__(L_T, 2)
+__global__ void __launch_bounds__(L_TT, 2)
 irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, const float* __restrict__ pack,
                         float* __restrict__ y, int accumulate) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -240,6 +281,7 @@ static bool build_lin_plan(const LinDesc& d, int transpose, LinTcPlan& pl, size_
     const LinBlock& lb = d.blk[i];
     const int K = transpose ? lb.mul_out : lb.mul_in, N = transpose ? lb.mul_in : lb.mul_out;
     if (K < 16 || N < 16) return false;
+    if ((pl.ldx & 3) || ((transpose ? lb.out_off : lb.in_off) & 3)) return false;   // 16-byte cp.async pieces of the rows
     const int npass = (N + L_MAXN - 1) / L_MAXN;
     const int per = ((N + npass - 1) / npass + 15) / 16 * 16;
     for (int p = 0; p < npass; ++p) {
@@ -291,7 +333,7 @@ int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float*
   for (int p = 0; p < pl.npass; ++p) maxd = pl.p[p].D > maxd ? pl.p[p].D : maxd;
   const int tn = 128 / maxd;   // the widest irrep has the fewest nodes per tile; surplus CTAs of the others exit
   dim3 grid((n_nodes + tn - 1) / tn, pl.npass);
-  irreps_linear_tc_kernel<<<grid, L_T, sizeof(LinTcSmem), st>>>(pl, n_nodes, x, pack, y, accumulate);
+  irreps_linear_tc_kernel<<<grid, L_TT, sizeof(LinTcSmem), st>>>(pl, n_nodes, x, pack, y, accumulate);
   cudaFreeAsync(pack, st);
   return check_launch("irreps_linear_tc", 2);
 }
