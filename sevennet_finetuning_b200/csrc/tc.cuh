@@ -165,20 +165,6 @@ __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
   hi = to_tf32(x);
   lo = to_tf32(x - hi);
 }
-// The same split in three instructions for finite x: hi rounded to tf32 on the bit pattern (ties away from zero, as
-// cvt.rna), lo = x - hi (exact) left as fp32 - the tensor core reads the upper 19 bits of a tf32 operand, i.e. truncates lo,
-// an error of at most 2^-10 |lo| <= 2^-21 |x| whose sign follows lo's (no bias).  cvt.rna.tf32 compiles to ~5 instructions
-// (it also handles inf / nan), twice per element.
-__device__ __forceinline__ void split_tf32_fast(float x, float& hi, float& lo) {
-  hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
-  lo = x - hi;
-}
-__device__ __forceinline__ void split4_fast(const float4& v, float4& hi, float4& lo) {
-  split_tf32_fast(v.x, hi.x, lo.x);
-  split_tf32_fast(v.y, hi.y, lo.y);
-  split_tf32_fast(v.z, hi.z, lo.z);
-  split_tf32_fast(v.w, hi.w, lo.w);
-}
 __device__ __forceinline__ void split4(const float4& v, float4& hi, float4& lo) {
   split_tf32(v.x, hi.x, lo.x);
   split_tf32(v.y, hi.y, lo.y);
