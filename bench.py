@@ -57,29 +57,38 @@ class ClockSampler:
     def __init__(self, index):
         self.rows, self.stop, self.index = [], False, index
         self.t = threading.Thread(target=self._run, daemon=True)
-
-    def _run(self):
         # NVML in-process (the same counters nvidia-smi prints): spawning nvidia-smi from a process that maps >100 GB
-        # of device memory stalls the launching thread for tens of milliseconds per sample
+        # of device memory stalls the launching thread for tens of milliseconds per sample.  The library is loaded and
+        # initialised HERE, before the timed region (nvmlInit inside it cost one timed step 6-23 ms); the thread only queries.
+        self.nv = None
         try:
             import pynvml as nv
             nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            self.h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+            self.get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            self.get_reasons(self.h)
+            self.nv = nv
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        if self.nv is not None:
+            nv, h, mx = self.nv, self.h, self.mx
             bits = [(getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8), 0), (getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40), 1),
                     (getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20), 2), (getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4), 3)]
-            get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
-            while not self.stop:
-                r = get_reasons(h)
-                flags = ['Not Active'] * 4
-                for bit, k in bits:
-                    if r & bit:
-                        flags[k] = 'Active'
-                self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx)] + flags)
-                time.sleep(0.05)
-            return
-        except Exception:
-            pass
+            try:
+                while not self.stop:
+                    r = self.get_reasons(h)
+                    flags = ['Not Active'] * 4
+                    for bit, k in bits:
+                        if r & bit:
+                            flags[k] = 'Active'
+                    self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx)] + flags)
+                    time.sleep(0.05)
+                return
+            except Exception:
+                pass
         q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
         while not self.stop:
