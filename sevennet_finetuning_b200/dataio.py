@@ -1,0 +1,151 @@
+"""Reading the reference's training inputs without ASE: ``structure_list`` files and VASP OUTCARs
+-> per-structure labelled graphs for ``finetune.collate``; the neighbour lists come from the CUDA cell list
+(``ops.radius_graph``), not from ``ase.neighborlist``.
+
+Reference: ``sevenn/train/dataload.py:223-300`` (``structure_list_reader``: ``[label]`` headers, brace-expanded file
+patterns, an index expression per line; every ionic step of an OUTCAR parsed by ASE's ``outcarchunks`` with the
+``PositionsAndForces, Stress, Energy, Cell`` parsers) and ``:71-154`` (``atoms_to_graph``: labels taken from the ASE atoms).
+ASE is not installed in this environment, so the conventions below restate what those ASE parsers deliver and what the
+reference does with it (parity with ASE itself is unpinned; the shipped OUTCARs parse, see tests/test_dataio_cpu.py):
+  * energy  = "free  energy   TOTEN" (``get_potential_energy(force_consistent=True)``, dataload.py:94-97), eV
+  * forces  = columns 4-6 of the "POSITION ... TOTAL-FORCE (eV/Angst)" block, positions = columns 1-3
+  * cell    = the "direct lattice vectors" block nearest before the positions of the step
+  * stress  = the "in kB" line (XX YY ZZ XY YZ ZX, VASP's sign) x 0.1 GPa in eV/A^3: ASE stores minus that in Voigt order,
+              the reference negates and reorders it back (dataload.py:99-106), so the label is VASP's own six numbers, in
+              eV/A^3, order xx yy zz xy yz zx; NaN when the step prints no stress
+  * species = "VRHFIN =El:" per POTCAR, repeated by "ions per type"
+"""
+import os
+import re
+
+import numpy as np
+import torch
+
+KB_TO_EV_A3 = 1.0 / 1602.1766208     # 0.1 GPa in eV/A^3 (ase.units.GPa, CODATA 2014, as sevenn/error_recorder.py:37)
+
+CHEMICAL_SYMBOLS = ('X H He Li Be B C N O F Ne Na Mg Al Si P S Cl Ar K Ca Sc Ti V Cr Mn Fe Co Ni Cu Zn Ga Ge As Se Br Kr '
+                    'Rb Sr Y Zr Nb Mo Tc Ru Rh Pd Ag Cd In Sn Sb Te I Xe Cs Ba La Ce Pr Nd Pm Sm Eu Gd Tb Dy Ho Er Tm Yb Lu '
+                    'Hf Ta W Re Os Ir Pt Au Hg Tl Pb Bi Po At Rn Fr Ra Ac Th Pa U Np Pu Am Cm Bk Cf Es Fm Md No Lr Rf Db Sg '
+                    'Bh Hs Mt Ds Rg Cn Nh Fl Mc Lv Ts Og').split()
+ATOMIC_NUMBER = {s: z for z, s in enumerate(CHEMICAL_SYMBOLS)}
+
+
+def braceexpand(expr):
+    """The subset of shell brace expansion structure_list files use: ``{a..b}`` integer ranges (zero padding kept) and
+    ``{x,y,z}`` lists, nested / repeated braces expanded left to right."""
+    m = re.search(r'\{([^{}]*)\}', expr)
+    if not m:
+        return [expr]
+    body, out = m.group(1), []
+    rng = re.fullmatch(r'(-?\d+)\.\.(-?\d+)(?:\.\.(-?\d+))?', body)
+    if rng:
+        a, b = int(rng.group(1)), int(rng.group(2))
+        step = abs(int(rng.group(3))) if rng.group(3) else 1
+        width = max(len(rng.group(1)), len(rng.group(2))) if (rng.group(1).startswith('0') or rng.group(2).startswith('0')) else 0
+        items = [str(v).zfill(width) for v in (range(a, b + 1, step) if a <= b else range(a, b - 1, -step))]
+    else:
+        items = body.split(',')
+    for it in items:
+        out.extend(braceexpand(expr[:m.start()] + it + expr[m.end():]))
+    return out
+
+
+def string2index(s):
+    """ase.io.formats.string2index: 'i' -> int, 'a:b:c' -> slice."""
+    s = s.strip()
+    if ':' not in s:
+        return int(s)
+    parts = [int(p) if p.strip() else None for p in s.split(':')]
+    return slice(*parts)
+
+
+def read_outcar(path, index=slice(None)):
+    """Every ionic step of a VASP OUTCAR as dict(numbers[N], pos[N,3], cell[3,3], energy, forces[N,3], stress[6], pbc)."""
+    symbols, counts = [], None
+    cell = stress = pos_force = None
+    steps = []
+    with open(path, 'r') as f:
+        lines = f.readlines()
+    i, n = 0, len(lines)
+    while i < n:
+        ln = lines[i]
+        if 'VRHFIN =' in ln:
+            symbols.append(ln.split('=')[1].split(':')[0].strip())
+        elif 'ions per type =' in ln:
+            counts = [int(t) for t in ln.split('=')[1].split()]
+        elif 'direct lattice vectors' in ln:
+            cell = np.array([[float(t) for t in lines[i + k].replace('-', ' -').split()[:3]] for k in (1, 2, 3)])
+            i += 3
+        elif ln.lstrip().startswith('in kB'):
+            try:
+                stress = np.array([float(t) for t in ln.split()[2:8]]) * KB_TO_EV_A3
+            except ValueError:      # '******' overflow fields
+                stress = np.full(6, np.nan)
+        elif 'POSITION' in ln and 'TOTAL-FORCE' in ln:
+            nat = sum(counts)
+            rows = np.array([[float(t) for t in lines[i + 2 + k].split()[:6]] for k in range(nat)])
+            pos_force = (rows[:, :3], rows[:, 3:6])
+            i += 2 + nat
+        elif 'free  energy   TOTEN' in ln:
+            if pos_force is None or cell is None:
+                raise RuntimeError(f'{path}: energy line {i + 1} without positions / cell before it')
+            numbers = np.repeat([ATOMIC_NUMBER[s] for s in symbols[:len(counts)]], counts)
+            steps.append({'numbers': numbers, 'pos': pos_force[0], 'cell': cell.copy(), 'forces': pos_force[1],
+                          'energy': float(ln.split('=')[1].split()[0]),
+                          'stress': stress if stress is not None else np.full(6, np.nan), 'pbc': (True, True, True),
+                          'info': {'data_from': 'user_OUTCAR', 'file': os.path.abspath(path), 'ionic_step': len(steps)}})
+            pos_force = stress = None
+        i += 1
+    return steps[index] if isinstance(index, slice) else [steps[index]]
+
+
+def structure_list_reader(filename):
+    """dataload.py:223-300: {label: [structures]}; relative file patterns are resolved against the list's directory as the
+    reference resolves them against the working directory it is started in."""
+    base = os.path.dirname(os.path.abspath(filename))
+    out, label = {}, None
+    with open(filename, 'r') as f:
+        for raw in f:
+            line = raw.strip()
+            if not line:
+                continue
+            if line.startswith('['):
+                if not line.endswith(']'):
+                    raise ValueError('wrong structure_list title format')
+                label = line[1:-1]
+                out[label] = []
+                continue
+            if label is None:
+                raise ValueError('wrong structure_list format')
+            tok = line.split()
+            if len(tok) == 1:
+                tok.append(':')
+            elif len(tok) != 2:
+                raise ValueError('wrong structure_list format')
+            index = string2index(tok[1])
+            if isinstance(index, slice) and any(v is not None and v < 0 for v in (index.start, index.stop)):
+                raise ValueError('Negative index is not supported yet')   # dataload.py:281-284
+            for name in braceexpand(tok[0]):
+                out[label].extend(read_outcar(name if os.path.isabs(name) else os.path.join(base, name), index))
+    return out
+
+
+def to_graphs(structures, cutoff, chemical_species, device):
+    """``atoms_to_graph`` (dataload.py:71-154) + the one-hot index map of ``AtomGraphDataset.x_to_one_hot_idx``
+    (dataset.py:203-217): per-structure dicts for ``finetune.collate``.  ``chemical_species``: the model's species list
+    (symbols, in the model's order); the neighbour list is the CUDA cell list."""
+    from . import ops
+    type_of = {ATOMIC_NUMBER[s]: k for k, s in enumerate(chemical_species)}
+    graphs = []
+    for st in structures:
+        try:
+            types = np.array([type_of[int(z)] for z in st['numbers']])
+        except KeyError as e:
+            raise ValueError(f'atomic number {e} is not among the model species') from None
+        g = ops.radius_graph(torch.tensor(st['pos'], dtype=torch.float64, device=device), st['cell'], st['pbc'], cutoff)
+        graphs.append({'x': torch.tensor(types), 'edge_index': torch.stack([g['dst'], g['src']]).long().cpu(),
+                       'edge_vec': g['edge_vec'].cpu(), 'cell_volume': abs(float(np.linalg.det(st['cell']))),
+                       'num_atoms': len(types), 'total_energy': st['energy'],
+                       'force_of_atoms': torch.tensor(st['forces'], dtype=torch.float32),
+                       'stress': torch.tensor(st['stress'], dtype=torch.float32), 'info': st['info']})
+    return graphs
