@@ -25,7 +25,7 @@ constexpr int L_MAXN = 64;             // output columns per pass
 constexpr int L_BPART = (LK / 4) * L_MAXN * 16;   // 4 KB (hi or lo)
 constexpr int L_T = 256;               // worker threads
 constexpr int L_TT = L_T + 32;         // + the issuer warp
-constexpr int L_NS = 4;                // raw row staging slots (three chunks in flight)
+constexpr int L_NS = 3;                // raw row staging slots (two chunks in flight)
 constexpr int L_SFLOATS = 128 * (LK + 4);   // floats of one slot: TN nodes x (16 (2l+1) + 4) <= 2560
 
 struct LinTcBlock {
@@ -39,14 +39,15 @@ struct LinTcBlock {
 struct LinTcPlan {
   int npass;
   int ldx, ldy;
+  int nblk, blk_first[16], blk_npass[16];   // groups of consecutive passes of one l-block: one CTA runs a group back to back
   LinTcBlock p[16];
 };
 
 struct LinTcSmem {
   uint8_t A[2][2 * L_APART];
   uint8_t B[2][2 * L_BPART];
-  float S[L_NS][L_SFLOATS];    // raw fp32 rows of the coming chunks, filled by cp.async (the epilogue's per-warp
-                               // transposition scratch, 8 x 32 x 33 floats, reuses A and B)
+  float S[L_NS][L_SFLOATS];    // raw fp32 rows of the coming chunks, filled by cp.async
+  float T[L_T / 32][32][33];   // per-warp transposition scratch of the pass epilogues
   uint64_t full_b[2], mma_done[2], a_full[2];
   uint32_t tmem_base;
 };
@@ -82,7 +83,7 @@ __global__ void linear_prepack_kernel(LinTcPlan pl, const float* __restrict__ W,
 // accumulator, so the large product is added (one truncation) to a sum that is 2^-11 of its size.  Four accumulators
 // of 64 columns = 256 TMEM columns per CTA: two CTAs share an SM and hide each other's gather and drain latency.
 template <int D>
-__device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, const LinTcBlock& b, int n_nodes,
+__device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, int first, int npass, int n_nodes,
                                          const float* __restrict__ x, const float* __restrict__ pack,
                                          float* __restrict__ y, int accumulate) {
   constexpr int TN = 128 / D;                    // nodes per tile
@@ -91,7 +92,8 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
   const int nn = min(TN, n_nodes - n0);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = warp & 3, half = warp >> 2;      // TMEM lane quarter, 32-column half of the pass
-  const uint32_t bpart = (uint32_t)(LK / 4) * b.Npad * 16;   // bytes of one part (hi or lo) of a B chunk
+  const LinTcBlock& b = pl.p[first];             // K, offsets and chunk count are the block's; N, o0, pack_off the pass's
+  const int nchunk = b.nchunk, G = npass * nchunk;   // the CTA's chunk stream: pass after pass, no pipeline refill between
 
   if (warp == 0) tmem_alloc(&s.tmem_base, 256);
   if (threadIdx.x == 32) {
@@ -102,7 +104,6 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = s.tmem_base;
-  const uint32_t idesc = make_idesc_tf32(128, b.Npad);
   // Warp 8 is the issuer: one elected thread requests the weight chunks, waits for the operand stage the eight worker warps
   // fill, and issues the MMAs.  The workers never wait for it (no CTA-wide barrier in the loop): a cycle-counter trace of the
   // first version, where warp 0 both worked and issued, showed the whole CTA running at warp 0's pace - its own gather and
@@ -110,19 +111,22 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
   // with the other seven warps parked at the barrier for 840 of every 1850 cycles.
   if (warp == L_T / 32) {
     if (elect_one()) {
-      for (int c = 0; c < b.nchunk; ++c) {
-        const int st = c & 1;
-        if (c >= 2) mbar_wait(&s.mma_done[st], ((c - 2) >> 1) & 1);   // the weight stage is free
+      for (int g = 0; g < G; ++g) {
+        const int st = g & 1, ps = g / nchunk, c = g - ps * nchunk;
+        const LinTcBlock& bp = pl.p[first + ps];
+        const uint32_t bpart = (uint32_t)(LK / 4) * bp.Npad * 16;   // bytes of one part (hi or lo) of a B chunk
+        if (g >= 2) mbar_wait(&s.mma_done[st], ((g - 2) >> 1) & 1);   // the weight stage is free
         mbar_expect_tx(&s.full_b[st], 2 * bpart);
-        const float* src = pack + b.pack_off + (size_t)c * (2 * bpart / 4);
+        const float* src = pack + bp.pack_off + (size_t)c * (2 * bpart / 4);
         bulk_copy_g2s(s.B[st], src, bpart, &s.full_b[st]);
         bulk_copy_g2s(s.B[st] + L_BPART, src + bpart / 4, bpart, &s.full_b[st]);
-        mbar_wait(&s.a_full[st], (c >> 1) & 1);    // operand written, accumulators of this stage drained
-        mbar_wait(&s.full_b[st], (c >> 1) & 1);
+        mbar_wait(&s.a_full[st], (g >> 1) & 1);    // operand written, accumulators of this stage drained
+        mbar_wait(&s.full_b[st], (g >> 1) & 1);
         tc_fence_after();
+        const uint32_t idesc = make_idesc_tf32(128, bp.Npad);
         const uint32_t ah = smem_u32(s.A[st]), al = ah + L_APART, bh = smem_u32(s.B[st]), bl = bh + L_BPART;
-        const uint32_t bch = (uint32_t)b.Npad * 16;
-        const uint32_t dmain = tmem + (uint32_t)(2 * (c & 1) * L_MAXN);
+        const uint32_t bch = (uint32_t)bp.Npad * 16;
+        const uint32_t dmain = tmem + (uint32_t)(2 * st * L_MAXN);
 #pragma unroll
         for (int kk = 0; kk < LK / 8; ++kk) {
           const uint64_t dah = make_desc(ah + kk * 2 * L_ACH, L_ACH, 128), dal = make_desc(al + kk * 2 * L_ACH, L_ACH, 128);
@@ -140,30 +144,52 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
     return;
   }
   const uint32_t tlane = tmem + ((uint32_t)(32 * q) << 16) + (uint32_t)(32 * half);
-  const bool have_cols = 32 * half < b.Npad;
   float acc[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) acc[j] = 0.f;
-  auto drain = [&](int c) {   // add the two accumulators of chunk c (its MMAs have retired) into the registers
-    if (have_cols) {
+  float (*T)[33] = s.T[warp];
+  // add the two accumulators of stream position g (its MMAs have retired) into the registers; at the last chunk of a
+  // pass, write the pass out: the warp transposes its 32x32 block through shared memory so that its stores run along the
+  // output channels of one (node, m) row
+  auto drain = [&](int g) {
+    const int ps = g / nchunk;
+    const LinTcBlock& bp = pl.p[first + ps];
+    if (32 * half < bp.Npad) {
       float v[32];
 #pragma unroll
       for (int kk = 0; kk < 2; ++kk) {
-        tmem_ld32(tlane + (uint32_t)((2 * (c & 1) + kk) * L_MAXN), v);
+        tmem_ld32(tlane + (uint32_t)((2 * (g & 1) + kk) * L_MAXN), v);
 #pragma unroll
         for (int j = 0; j < 32; ++j) acc[j] += v[j];
       }
     }
     tc_fence_before();
+    if (g - ps * nchunk == nchunk - 1) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) { T[lane][j] = acc[j]; acc[j] = 0.f; }
+      __syncwarp();
+      const int o = 32 * half + lane;
+      if (o < bp.N) {
+        for (int r = 0; r < 32; ++r) {
+          const int orow = 32 * q + r, nl = orow / D, m = orow % D;
+          if (nl >= nn) break;
+          float* p = y + (size_t)(n0 + nl) * pl.ldy + bp.yoff + (size_t)(bp.o0 + o) * D + m;
+          const float val = T[r][lane] * bp.scale;
+          *p = accumulate ? (*p + val) : val;
+        }
+      }
+      __syncwarp();
+    }
   };
 
   // Operand A.  (1) Raw rows: the chunk's 16 (2l+1) floats of a node are contiguous, 4 (2l+1) pieces of 16 bytes; the
-  // tile's <= 512 pieces are two cp.async per worker thread, issued three chunks ahead into a 4-slot ring (node stride
+  // tile's <= 512 pieces are two cp.async per worker thread, issued two chunks ahead into a 3-slot ring (node stride
   // padded by 4 floats so that the reads below spread over the banks).  Pieces past the block's K are zero-filled
   // (src-size operand); nodes past the end of a short last tile re-read the last valid node (tile rows are independent in
   // the product and those rows are never stored).  Direct 4-byte loads of (row, k) elements, the former scheme, cost the
   // L1 data pipe one sector per lane and load: 128M sector reads for 39M sectors of data, 72 % of the L1 cycles
-  // (profiles/r01q_linear_tc_raw.csv); the pieces move every sector once.
+  // (profiles/r01q_linear_tc_raw.csv); the pieces move every sector once.  Every pass of the block re-reads the tile's rows
+  // (L1 / L2 hits after the first).
   // (2) Split: thread -> one row (node, m) and 8 of the 16 k; a warp covers 32 consecutive rows, so its 16-byte operand
   // stores are one contiguous 512-byte run.
   constexpr int RS = LK * D + 4;                 // floats per node in a slot
@@ -178,10 +204,11 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
     psrc[u] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + p * 4;
     pdst[u] = smem_u32(&s.S[0][0]) + (uint32_t)(nl * RS + p * 4) * 4;
   }
-  auto stage = [&](int c) {                      // request chunk c (nothing past the last chunk; the group is still committed)
-    if (c < b.nchunk) {
+  auto stage = [&](int g) {                      // request stream position g (nothing past the end; the group is still committed)
+    if (g < G) {
+      const int c = g % nchunk;
       const int kfl = min(LK, b.K - c * LK) * D; // valid floats of a node's chunk
-      const uint32_t slot = (uint32_t)(c % L_NS) * (L_SFLOATS * 4);
+      const uint32_t slot = (uint32_t)(g % L_NS) * (L_SFLOATS * 4);
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         const int nb = min(16, max(0, (kfl - pfl[u]) * 4));
@@ -196,20 +223,19 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
   const uint32_t aoff = (uint32_t)(2 * kp) * L_ACH + (uint32_t)row * 16;
   stage(0);
   stage(1);
-  stage(2);
-  asm volatile("cp.async.wait_group 2;" ::: "memory");
+  asm volatile("cp.async.wait_group 1;" ::: "memory");
   bar_sync(1, L_T);
 
-  for (int c = 0; c < b.nchunk; ++c) {
-    const int st = c & 1;
-    if (c >= 2) {   // the MMAs of chunk c-2 have consumed the operand stage and filled its two accumulators
-      mbar_wait(&s.mma_done[st], ((c - 2) >> 1) & 1);
+  for (int g = 0; g < G; ++g) {
+    const int st = g & 1;
+    if (g >= 2) {   // the MMAs of position g-2 have consumed the operand stage and filled its two accumulators
+      mbar_wait(&s.mma_done[st], ((g - 2) >> 1) & 1);
       tc_fence_after();
-      drain(c - 2);
+      drain(g - 2);
     }
-    stage(c + L_NS - 1);   // into the slot chunk c-1 was read from (all workers are past that iteration's barrier)
+    stage(g + L_NS - 1);   // into the slot position g-1 was read from (all workers are past that iteration's barrier)
     {
-      const float* sp = &s.S[c % L_NS][soff];
+      const float* sp = &s.S[g % L_NS][soff];
       float4 v0, v1, h0, l0, h1, l1;
       if (D == 1) {
         v0 = *reinterpret_cast<const float4*>(sp);
@@ -229,32 +255,16 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, cons
     fence_proxy_async();
     tc_fence_before();
     warp_arrive(&s.a_full[st]);
-    asm volatile("cp.async.wait_group 2;" ::: "memory");   // own pieces of chunk c+1 have landed ...
+    asm volatile("cp.async.wait_group 1;" ::: "memory");   // own pieces of position g+1 have landed ...
     bar_sync(1, L_T);                                       // ... and every worker's: the slot may be read
   }
-  // the last two chunks (MMAs retire in order)
-  for (int c = max(0, b.nchunk - 2); c < b.nchunk; ++c) {
-    mbar_wait(&s.mma_done[c & 1], (c >> 1) & 1);
+  // the last two positions (MMAs retire in order)
+  for (int g = max(0, G - 2); g < G; ++g) {
+    mbar_wait(&s.mma_done[g & 1], (g >> 1) & 1);
     tc_fence_after();
-    drain(c);
+    drain(g);
   }
-  // transpose the warp's 32x32 block so that the stores run along the output channels of one (node, m) row
   asm volatile("cp.async.wait_group 0;" ::: "memory");
-  // the scratch lies over the operand stages: every MMA that reads them has retired (the waits above)
-  float (*T)[33] = reinterpret_cast<float (*)[33]>(&s.A[0][0]) + warp * 32;
-#pragma unroll
-  for (int j = 0; j < 32; ++j) T[lane][j] = acc[j];
-  __syncwarp();
-  const int o = 32 * half + lane;
-  if (o < b.N) {
-    for (int r = 0; r < 32; ++r) {
-      const int row = 32 * q + r, nl = row / D, m = row % D;
-      if (nl >= nn) break;
-      float* p = y + (size_t)(n0 + nl) * pl.ldy + b.yoff + (size_t)(b.o0 + o) * D + m;
-      const float val = T[r][lane] * b.scale;
-      *p = accumulate ? (*p + val) : val;
-    }
-  }
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem, 256);
@@ -265,17 +275,18 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
                         float* __restrict__ y, int accumulate) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   LinTcSmem& s = *reinterpret_cast<LinTcSmem*>(smem_raw);
-  const LinTcBlock& b = pl.p[blockIdx.y];
-  switch (b.D) {   // 2l+1 as a compile-time constant: row <-> (node, m) without integer division
-    case 1: lin_tile<1>(s, pl, b, n_nodes, x, pack, y, accumulate); break;
-    case 3: lin_tile<3>(s, pl, b, n_nodes, x, pack, y, accumulate); break;
-    default: lin_tile<5>(s, pl, b, n_nodes, x, pack, y, accumulate); break;
+  const int first = pl.blk_first[blockIdx.y], npass = pl.blk_npass[blockIdx.y];
+  switch (pl.p[first].D) {   // 2l+1 as a compile-time constant: row <-> (node, m) without integer division
+    case 1: lin_tile<1>(s, pl, first, npass, n_nodes, x, pack, y, accumulate); break;
+    case 3: lin_tile<3>(s, pl, first, npass, n_nodes, x, pack, y, accumulate); break;
+    default: lin_tile<5>(s, pl, first, npass, n_nodes, x, pack, y, accumulate); break;
   }
 }
 
 // plan: one pass per (block, <=256 output columns); returns false when a block is too small for the tensor-core path
-static bool build_lin_plan(const LinDesc& d, int transpose, LinTcPlan& pl, size_t* pack_floats) {
+static bool build_lin_plan(const LinDesc& d, int transpose, int n_nodes, LinTcPlan& pl, size_t* pack_floats) {
   pl.npass = 0;
+  pl.nblk = 0;
   pl.ldx = transpose ? d.out_dim : d.in_dim;
   pl.ldy = transpose ? d.in_dim : d.out_dim;
   size_t off = 0;
@@ -285,6 +296,18 @@ static bool build_lin_plan(const LinDesc& d, int transpose, LinTcPlan& pl, size_
     if (K < 16 || N < 16) return false;
     if ((pl.ldx & 3) || ((transpose ? lb.out_off : lb.in_off) & 3)) return false;   // 16-byte cp.async pieces of the rows
     const int npass = (N + L_MAXN - 1) / L_MAXN;
+    // One CTA streams several passes of its tile (no TMEM allocation, pipeline refill and barrier setup per pass: with
+    // K = 32 a pass is two chunks long) as long as that leaves at least two CTAs per resident slot; small inputs (the
+    // 3,200-node batches of fine-tuning) keep one pass per CTA and their parallelism.
+    const int tiles = (n_nodes + 128 / lb.d - 1) / (128 / lb.d);
+    const long long want = (long long)tiles * npass / (2 * 2 * 148);
+    const int gp = (int)(want < 1 ? 1 : (want > npass ? npass : want));
+    for (int p0 = 0; p0 < npass; p0 += gp) {
+      if (pl.nblk >= 16) return false;
+      pl.blk_first[pl.nblk] = pl.npass + p0;
+      pl.blk_npass[pl.nblk] = gp < npass - p0 ? gp : npass - p0;
+      ++pl.nblk;
+    }
     const int per = ((N + npass - 1) / npass + 15) / 16 * 16;
     for (int p = 0; p < npass; ++p) {
       if (pl.npass >= 16) return false;
@@ -312,14 +335,14 @@ bool irreps_linear_tc_supported(const LinDesc& d, int transpose) {
   LinTcPlan pl;
   size_t n;
   if (d.nblk < 1 || d.nblk > 4) return false;
-  return build_lin_plan(d, transpose, pl, &n);
+  return build_lin_plan(d, transpose, 1 << 30, pl, &n);
 }
 
 int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
                      cudaStream_t st) {
   LinTcPlan pl;
   size_t pack_floats;
-  B200_REQUIRE(build_lin_plan(d, transpose, pl, &pack_floats), "irreps_linear_tc: unsupported shape");
+  B200_REQUIRE(build_lin_plan(d, transpose, n_nodes, pl, &pack_floats), "irreps_linear_tc: unsupported shape");
   if (n_nodes == 0) return B200_OK;
   float* pack;
   keep_async_pool();
@@ -334,7 +357,7 @@ int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float*
   int maxd = 1;
   for (int p = 0; p < pl.npass; ++p) maxd = pl.p[p].D > maxd ? pl.p[p].D : maxd;
   const int tn = 128 / maxd;   // the widest irrep has the fewest nodes per tile; surplus CTAs of the others exit
-  dim3 grid((n_nodes + tn - 1) / tn, pl.npass);
+  dim3 grid((n_nodes + tn - 1) / tn, pl.nblk);
   irreps_linear_tc_kernel<<<grid, L_TT, sizeof(LinTcSmem), st>>>(pl, n_nodes, x, pack, y, accumulate);
   cudaFreeAsync(pack, st);
   return check_launch("irreps_linear_tc", 2);

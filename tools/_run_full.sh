@@ -1,4 +1,5 @@
 cd /root/repo
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_dataio.py tests/test_gpu_stats.py -q -m gpu -x 2>&1 | tail -12 > gpurun_out/t_io.log
-timeout 600 python bench.py > gpurun_out/r_bench.json 2> gpurun_out/r_bench.err
+timeout 900 python -m pytest tests -q -m gpu -x 2>&1 | tail -4 > gpurun_out/t_all.log
+timeout 200 python tools/lin_time.py > gpurun_out/lin_time.log 2>&1
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/s_bench.json 2> gpurun_out/s_bench.err
