@@ -29,29 +29,48 @@ TO_KB = 1602.1766208   # eV/A^3 -> kbar (loss.py:199)
 
 # ---- loss definitions (sevenn/train/loss.py) ---------------------------------------------------------------------------
 class LossDefinition:
-    def __init__(self, name=None, unit=None, criterion=None, ref_key=None, pred_key=None, use_weight=False,
-                 delete_unlabled=True):
-        self.name, self.unit, self.criterion = name, unit, criterion
+    """loss.py:10-93.  ``use_weight``: per-structure data weights (``load_dataset_with_weights``, dataset.py:430-450):
+    ``batch_data['data_weight'][weight_key]`` holds one weight per structure, the criterion must have reduction 'none' and the
+    loss is mean(criterion * weight).  (The reference's own weighted branch trips over ``assert isinstance(weights, list)``
+    at loss.py:88 whenever unlabelled entries are filtered, i.e. always with its defaults; this is the computation it
+    describes, with the weights filtered like the values.)"""
+
+    def __init__(self, name=None, unit=None, criterion=None, ref_key=None, pred_key=None, vdim=1, use_weight=False,
+                 weight_key=None, delete_unlabled=True):
+        if criterion is not None and hasattr(criterion, 'reduction'):
+            if use_weight:
+                assert criterion.reduction == 'none' and weight_key is not None
+            else:
+                assert criterion.reduction != 'none'
+        self.name, self.unit, self.criterion, self.vdim = name, unit, criterion, vdim
         self.ref_key, self.pred_key, self.use_weight, self.delete_unlabeled = ref_key, pred_key, use_weight, delete_unlabled
-        if use_weight:
-            raise NotImplementedError('per-structure data weights (load_dataset_with_weights) are not mirrored')
+        self.weight_key = weight_key
 
     def _preprocess(self, batch_data, model=None):
         return batch_data[self.pred_key].reshape(-1), batch_data[self.ref_key].reshape(-1)
 
+    def _get_data_weight(self, batch_data):   # loss.py:60-63: one weight per structure, repeated over the components
+        return torch.repeat_interleave(batch_data['data_weight'][self.weight_key], self.vdim)
+
     def get_loss(self, batch_data, model=None):
         pred, ref = self._preprocess(batch_data, model)
+        weights = self._get_data_weight(batch_data) if self.use_weight else None
         if self.delete_unlabeled:
             unl = torch.isnan(ref)
             pred, ref = pred[~unl], ref[~unl]
             if len(pred) == 0:
                 return torch.zeros(1, device=pred.device)
+            if weights is not None:
+                weights = weights[~unl]
+        if weights is not None:
+            return torch.mean(self.criterion(pred, ref) * weights)
         return self.criterion(pred, ref)
 
 
 class PerAtomEnergyLoss(LossDefinition):
     def __init__(self, criterion=None, **kw):
-        super().__init__('Energy', 'eV/atom', criterion, 'total_energy', 'inferred_total_energy', **kw)
+        super().__init__('Energy', 'eV/atom', criterion, 'total_energy', 'inferred_total_energy', vdim=1,
+                         weight_key='per_atom_energy', **kw)
 
     def _preprocess(self, batch_data, model=None):
         n = batch_data['num_atoms']
@@ -60,12 +79,16 @@ class PerAtomEnergyLoss(LossDefinition):
 
 class ForceLoss(LossDefinition):
     def __init__(self, criterion=None, **kw):
-        super().__init__('Force', 'eV/A', criterion, 'force_of_atoms', 'inferred_force', **kw)
+        super().__init__('Force', 'eV/A', criterion, 'force_of_atoms', 'inferred_force', vdim=3, weight_key='force_of_atoms', **kw)
+
+    def _get_data_weight(self, batch_data):   # loss.py:172-175: the structure's weight for each of its atoms
+        w = batch_data['data_weight'][self.weight_key][batch_data['batch']]
+        return torch.repeat_interleave(w, self.vdim)
 
 
 class StressLoss(LossDefinition):
     def __init__(self, criterion=None, **kw):
-        super().__init__('Stress', 'kbar', criterion, 'stress', 'inferred_stress', **kw)
+        super().__init__('Stress', 'kbar', criterion, 'stress', 'inferred_stress', vdim=6, weight_key='stress', **kw)
 
     def _preprocess(self, batch_data, model=None):
         return (batch_data[self.pred_key] * TO_KB).reshape(-1), (batch_data[self.ref_key] * TO_KB).reshape(-1)
@@ -109,12 +132,15 @@ class EWCLoss(LossDefinition):
 
 
 def get_loss_functions(loss='huber', loss_param=None, force_loss_weight=1.0, is_train_stress=True, stress_loss_weight=0.01,
-                       fisher_dict=None, opt_params_dict=None, ewc_lambda=0.0, device=None):
-    """[(definition, weight)] as ``get_loss_functions_from_config`` builds it (loss.py:268-307); EWC enters as lambda/2."""
-    crit = {'mse': torch.nn.MSELoss, 'huber': torch.nn.HuberLoss, 'l1': torch.nn.L1Loss}[loss.lower()](**(loss_param or {}))
-    out = [(PerAtomEnergyLoss(crit), 1.0), (ForceLoss(crit), float(force_loss_weight))]
+                       fisher_dict=None, opt_params_dict=None, ewc_lambda=0.0, device=None, use_weight=False):
+    """[(definition, weight)] as ``get_loss_functions_from_config`` builds it (loss.py:268-307); EWC enters as lambda/2;
+    ``use_weight`` = the config carries ``load_dataset_with_weights`` (reduction 'none' + per-structure weights)."""
+    crit = {'mse': torch.nn.MSELoss, 'huber': torch.nn.HuberLoss, 'l1': torch.nn.L1Loss}[loss.lower()](
+        reduction='none' if use_weight else 'mean', **(loss_param or {}))
+    common = dict(criterion=crit, use_weight=use_weight)
+    out = [(PerAtomEnergyLoss(**common), 1.0), (ForceLoss(**common), float(force_loss_weight))]
     if is_train_stress:
-        out.append((StressLoss(crit), float(stress_loss_weight)))
+        out.append((StressLoss(**common), float(stress_loss_weight)))
     if fisher_dict is not None and opt_params_dict is not None:
         out.append((EWCLoss(fisher_dict, opt_params_dict, device=device), float(ewc_lambda) / 2.0))
     return out
@@ -146,8 +172,11 @@ def collate(graphs, device=None, pin=False):
         out['total_energy'] = torch.tensor([float(g['total_energy']) for g in graphs], dtype=torch.float32)
         out['force_of_atoms'] = torch.cat([torch.as_tensor(g['force_of_atoms'], dtype=torch.float32) for g in graphs])
         out['stress'] = torch.stack([torch.as_tensor(g['stress'], dtype=torch.float32).reshape(6) for g in graphs])
+    if 'data_weight' in graphs[0]:   # dataset.py:430-450: {'per_atom_energy': w, 'force_of_atoms': w, 'stress': w} per structure
+        out['data_weight'] = {k: torch.tensor([float(g['data_weight'][k]) for g in graphs], dtype=torch.float32)
+                              for k in graphs[0]['data_weight']}
     if pin:
-        out = {k: v.pin_memory() for k, v in out.items()}
+        out = {k: ({kk: vv.pin_memory() for kk, vv in v.items()} if isinstance(v, dict) else v.pin_memory()) for k, v in out.items()}
     # edges of every structure sorted by their centre atom (what ase / the CUDA cell list emit) stay sorted under the
     # node offsets: let the convolution skip its sortedness check (nn._graph_of)
     if all(bool((torch.as_tensor(g['edge_index'])[0][1:] >= torch.as_tensor(g['edge_index'])[0][:-1]).all()) for g in graphs):
@@ -160,7 +189,8 @@ def collate(graphs, device=None, pin=False):
 def to_device(batch, device):
     """``batch.to(device, non_blocking=True)`` (trainer.py:176) + the requires_grad the dataset sets on edge_vec
     (``sevenn/train/dataload.py`` via ``AtomGraphData``; ``util.py:243``)."""
-    out = {k: (v.to(device, non_blocking=True) if torch.is_tensor(v) else v) for k, v in batch.items()}
+    out = {k: (v.to(device, non_blocking=True) if torch.is_tensor(v) else
+               {kk: vv.to(device, non_blocking=True) for kk, vv in v.items()} if isinstance(v, dict) else v) for k, v in batch.items()}
     out['edge_vec'].requires_grad_(True)
     return out
 

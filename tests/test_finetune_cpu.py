@@ -60,6 +60,35 @@ def test_loss_definitions_match_reference_formulas():
     assert got.shape == (1,) and abs(float(got) - float(want)) <= 1e-6 * abs(float(want))
 
 
+def test_per_structure_data_weights():
+    """load_dataset_with_weights (loss.py:23-93,172-175): mean(criterion * weight), the weight of a structure repeated over
+    its components (energy 1, stress 6) or over its atoms' components (forces)."""
+    graphs = [_graph(4 + s, 10, s) for s in range(3)]
+    for s, g in enumerate(graphs):
+        g['data_weight'] = {'per_atom_energy': 1.0 + s, 'force_of_atoms': 0.5 * (s + 1), 'stress': 2.0 - 0.5 * s}
+    graphs[1]['stress'] = torch.full((6,), float('nan'))          # an unlabelled stress: dropped together with its weights
+    b = ft.to_device(ft.collate(graphs), 'cpu')
+    r = np.random.default_rng(1)
+    n = int(b['num_atoms'].sum())
+    b['inferred_total_energy'] = torch.tensor(r.normal(size=3), dtype=torch.float32)
+    b['inferred_force'] = torch.tensor(r.normal(size=(n, 3)), dtype=torch.float32)
+    b['inferred_stress'] = torch.tensor(r.normal(size=(3, 6)), dtype=torch.float32)
+    lf = ft.get_loss_functions('huber', {'delta': 0.01}, 1.0, True, 0.01, use_weight=True)
+    h = torch.nn.HuberLoss(reduction='none', delta=0.01)
+    na = b['num_atoms'].float()
+    we = torch.tensor([1.0, 2.0, 3.0])
+    want_e = (h(b['inferred_total_energy'] / na, b['total_energy'] / na) * we).mean()
+    wf = torch.tensor([0.5, 1.0, 1.5])[b['batch']][:, None].expand(n, 3)
+    want_f = (h(b['inferred_force'], b['force_of_atoms']) * wf).mean()
+    ws = torch.tensor([2.0, 1.5, 1.0])[:, None].expand(3, 6)
+    ok = ~torch.isnan(b['stress'])
+    want_s = (h(b['inferred_stress'] * ft.TO_KB, b['stress'] * ft.TO_KB)[ok] * ws[ok]).mean()
+    got = [float(ld.get_loss(b)) for ld, _ in lf]
+    assert np.allclose(got, [float(want_e), float(want_f), float(want_s)], rtol=1e-6)
+    with pytest.raises(AssertionError):
+        ft.PerAtomEnergyLoss(torch.nn.MSELoss(), use_weight=True)   # weighted losses need reduction='none' (loss.py:27-30)
+
+
 def test_shard_indices_is_distributed_sampler_split():
     for n, w in [(100, 8), (37, 4), (5, 8)]:
         parts = [ft.shard_indices(n, r, w, seed=3, epoch=1) for r in range(w)]
