@@ -4,11 +4,12 @@
 //   y[n, o, m] = scale * sum_k x[n, k, m] W[k, o]     per l-block, scale = 1/sqrt(mul_in)
 // GEMM view: rows = (node, m) pairs, K = mul_in, N = mul_out.  One CTA owns 128 rows of one block:
 //   A = x tile (rows, K-major): the raw fp32 rows of a 16-k chunk ([mul, 2l+1], m fastest: 16 (2l+1) contiguous floats
-//       per node) arrive by cp.async three chunks ahead; the eight worker warps read them back in (row, k) order, split
+//       per node) arrive by cp.async two chunks ahead; the eight worker warps read them back in (row, k) order, split
 //       them into tf32 hi/lo and write the canonical operand layout (two operand stages),
 //   B = W^T (rows = output channel, K-major): prepacked hi/lo per 16-k chunk, streamed with cp.async.bulk by the issuer
 //       warp, whose elected thread also issues the MMAs (the workers never wait for it),
-//   D = 128 lanes (rows) x N columns in TMEM (N <= 64 per pass, four accumulators per CTA, two CTAs per SM).
+//   D = 128 lanes (rows) x N columns in TMEM (N <= 64 per pass, four accumulators per CTA, two CTAs per SM); a CTA
+//       streams the passes of its tile one after the other,
 // Epilogue: a warp transposes 32x32 blocks of D through shared memory so that its stores run along the output
 // channels of one (node, m) row.  transpose = 1 is the x-gradient (roles of in/out swapped, W read transposed).
 #include "common.cuh"
