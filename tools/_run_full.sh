@@ -1,5 +1,3 @@
 cd /root/repo
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -q -m gpu -x 2>&1 | tail -4 > gpurun_out/t_all.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1
-timeout 300 python bench.py --workload finetune --no-cpu-baseline > gpurun_out/ft.json 2> gpurun_out/ft.err
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/s_launches.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-finetune > gpurun_out/s_ncu.log 2>&1
