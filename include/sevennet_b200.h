@@ -190,6 +190,15 @@ int b200_graph_fill(int n_atoms, const double* pos, const double* cell_host, con
 size_t b200_transpose_workspace_bytes(int n_nodes, int64_t n_edges);
 int b200_csr_transpose(int n_nodes, int64_t n_edges, const int32_t* src, void* workspace, int32_t* rrowptr,
                        int32_t* eid_by_src, void* stream);
+/* Allocation-free variant of b200_csr_transpose.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, serving loops).  The scratch (two per-node
+ * counter arrays) is a static device array inside the library, held by every GPU that loads it (about 2 MiB); the call
+ * allocates nothing.  Limit: n_nodes <= b200_csr_transpose_static_max_nodes() (262,143), otherwise B200_ERR_INVALID.
+ * All calls on a device share the scratch: calls that overlap on the GPU race; back-to-back calls on one stream are fine
+ * (the counters are cleared at the start of every call).  Same outputs as b200_csr_transpose, bit for bit. */
+int b200_csr_transpose_static_max_nodes(void);
+int b200_csr_transpose_static(int n_nodes, int64_t n_edges, const int32_t* src, int32_t* rrowptr, int32_t* eid_by_src,
+                              void* stream);
 
 /* ---- whole-model E+F+S: the call PairE3GNN::compute makes (pair_e3gnn.cpp:205-266) and
  *      SevenNetCalculator.calculate (sevennet_calculator.py:119-157) ---------------------------------- */

@@ -82,6 +82,8 @@ SIGNATURES = {
     'b200_graph_fill': (_i, [_i, _vp, _P(C.c_double), _P(_i), C.c_double, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_transpose_workspace_bytes': (_sz, [_i, _i64]),
     'b200_csr_transpose': (_i, [_i, _i64, _vp, _vp, _vp, _vp, _vp]),
+    'b200_csr_transpose_static_max_nodes': (_i, []),
+    'b200_csr_transpose_static': (_i, [_i, _i64, _vp, _vp, _vp, _vp]),
     'b200_model_create': (_i, [_P(ModelConfig), _P(_vp)]),
     'b200_model_set_param': (_i, [_vp, C.c_char_p, _vp, _i64]),
     'b200_model_destroy': (None, [_vp]),

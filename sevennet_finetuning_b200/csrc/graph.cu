@@ -423,4 +423,53 @@ int csr_transpose(int n, long long E, const int* src, void* ws, int* rrowptr, in
   return check_launch("csr_transpose", E > 0 ? 4 : 1);
 }
 
+// ---- allocation-free variant of csr_transpose -----------------------------------------------------------
+// The two per-node counter arrays live in a file-scope device array instead of a caller workspace, so the call makes
+// no cudaMalloc / cudaFree (CUDA-graph capture, serving loops, harnesses that forbid allocation).  Every GPU that
+// loads the library holds the array (2 x 1 MiB + padding) until exit.  All calls on a device share it: calls that
+// overlap on the GPU (two streams, two threads) race.  It keeps the previous call's contents, so both counter arrays
+// are cleared (memset on the caller's stream, not an allocation) at the start of every call.
+constexpr int kStaticTransposeMaxNodes = 262143;   // (n + 1) counters per array <= 2^18
+constexpr size_t kStaticTransposeBytes = 2 * (((size_t)kStaticTransposeMaxNodes + 1) * sizeof(int)) + 256;
+static __device__ __align__(256) unsigned char g_transpose_scratch[kStaticTransposeBytes];
+
+// In host code `g_transpose_scratch` is only a stand-in for the symbol: the device address is looked up once per device
+// (with that device current) and cached.
+static int transpose_scratch_ptr(void** out) {
+  static void* ptr[64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("csr_transpose_static: cudaGetDevice failed");
+    return B200_ERR_CUDA;
+  }
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t rc = cudaGetSymbolAddress(&p, g_transpose_scratch);
+    if (rc != cudaSuccess || !p) {
+      set_error("csr_transpose_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(rc));
+      return B200_ERR_CUDA;
+    }
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return B200_OK;
+}
+
 }  // namespace b200
+
+extern "C" int b200_csr_transpose_static_max_nodes(void) { return b200::kStaticTransposeMaxNodes; }
+
+extern "C" int b200_csr_transpose_static(int n, int64_t E, const int32_t* src, int32_t* rrowptr, int32_t* eid,
+                                         void* stream) {
+  using namespace b200;
+  B200_REQUIRE(n >= 0 && E >= 0 && rrowptr && (E == 0 || (src && eid)), "csr_transpose_static: null or negative argument");
+  B200_REQUIRE(n <= kStaticTransposeMaxNodes,
+               "csr_transpose_static: %d nodes exceed the static scratch limit of %d; use b200_csr_transpose with a "
+               "caller workspace", n, kStaticTransposeMaxNodes);
+  B200_REQUIRE(E < (1LL << 31), "csr_transpose_static: more than 2^31 edges");
+  B200_REQUIRE(transpose_workspace_bytes(n, E) <= kStaticTransposeBytes, "csr_transpose_static: scratch too small");
+  void* ws = nullptr;
+  const int rc = transpose_scratch_ptr(&ws);
+  if (rc != B200_OK) return rc;
+  return csr_transpose(n, E, src, ws, rrowptr, eid, (cudaStream_t)stream);
+}
