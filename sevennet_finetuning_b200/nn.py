@@ -296,6 +296,8 @@ class IrrepsLinear(nn.Module):
 
     def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, is_embed=False, **e3nn_linear_params):
         super().__init__()
+        if e3nn_linear_params.get('biases', False):
+            raise ValueError('B200 path: IrrepsLinear with biases=True (use_bias_in_linear) is not supported')
         self.key_input = data_key_in
         self.key_output = data_key_in if data_key_out is None else data_key_out
         self.irreps_in, self.irreps_out, self.is_embed = irreps_in, irreps_out, is_embed
@@ -616,6 +618,8 @@ def build_E3_equivariant_model(config=None):
     from .model import SEVENNET0_CONFIG
     cfg = dict(SEVENNET0_CONFIG)
     cfg.update(config or {})
+    if cfg.get('use_bias_in_linear', False):
+        raise ValueError('B200 path: use_bias_in_linear is not supported')
     cutoff, nsp = cfg['cutoff'], cfg['num_species']
     man = cfg['irreps_manual']
     nconv = cfg['num_convolution_layer']
@@ -642,7 +646,8 @@ def build_E3_equivariant_model(config=None):
             L[f'{t}_self_connection_intro'] = SelfConnectionLinearIntro(irreps_x, gin)
         L[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, 'x')
         conv = IrrepsConvolution(irreps_x, '1x0e+1x1e+1x2e', tp_out,
-                                 [cfg['bessel_basis_num']] + list(cfg['weight_nn_hidden_neurons']), 'silu', den[t])
+                                 [cfg['bessel_basis_num']] + list(cfg['weight_nn_hidden_neurons']), 'silu', den[t],
+                                 train_denominator=bool(cfg.get('train_denominator', False)))
         L[f'{t}_convolution'] = conv
         m = ops.muls_of(irreps_x)
         msg = {0: [0, 0, 0]}[0]
@@ -658,12 +663,13 @@ def build_E3_equivariant_model(config=None):
     L['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, f'{mid // 2}x0e', 'x')
     L['reduce_hidden_to_energy'] = IrrepsLinear(f'{mid // 2}x0e', '1x0e', 'x', 'scaled_atomic_energy')
     shift, scale = cfg.get('shift', 0.0), cfg.get('scale', 1.0)
+    train_ss = bool(cfg.get('train_shift_scale', False))   # model_build.py:400-437
     if cfg['use_species_wise_shift_scale']:
         shift = shift if isinstance(shift, (list, tuple)) else [float(shift)] * nsp
         scale = scale if isinstance(scale, (list, tuple)) else [float(scale)] * nsp
-        L['rescale_atomic_energy'] = SpeciesWiseRescale(list(shift), list(scale))
+        L['rescale_atomic_energy'] = SpeciesWiseRescale(list(shift), list(scale), train_shift_scale=train_ss)
     else:
-        L['rescale_atomic_energy'] = Rescale(shift, scale)
+        L['rescale_atomic_energy'] = Rescale(shift, scale, train_shift_scale=train_ss)
     L['reduce_total_enegy'] = AtomReduce('atomic_energy', 'inferred_total_energy')
     L['force_output'] = ForceStressOutputFromEdge()
     return AtomGraphSequential(L, cutoff)
@@ -678,9 +684,19 @@ def substitute(model, config=None):
     (``replace_module``, ``sevenn/nn/sequential.py:61-62``), and copy the parameters (names and shapes are identical)."""
     twin = build_E3_equivariant_model(config)
     ref_sd = model.state_dict()
-    twin.load_state_dict({k: v for k, v in ref_sd.items() if k in twin.state_dict()}, strict=False)
+    twin_sd = twin.state_dict()
+    replaced = [key for key in twin._modules if key in model._modules and type(model._modules[key]).__name__ in _TWINS]
+    # every parameter of a replaced module must have a twin parameter (e.g. a `linear.bias` of use_bias_in_linear has none)
+    orphan = [k for k in ref_sd if k.split('.')[0] in replaced and k not in twin_sd]
+    if orphan:
+        raise ValueError(f'B200 path: reference parameters without a twin (biases are not supported): {orphan}')
+    twin.load_state_dict({k: v for k, v in ref_sd.items() if k in twin_sd}, strict=False)
+    # trainability follows the module being replaced (train_denominator / train_shift_scale of the reference config)
+    ref_grad = {k: p.requires_grad for k, p in model.named_parameters()}
+    for k, p in twin.named_parameters():
+        if k in ref_grad:
+            p.requires_grad_(ref_grad[k])
     dev = next(model.parameters()).device
-    for key, mod in twin._modules.items():
-        if key in model._modules and type(model._modules[key]).__name__ in _TWINS:
-            model.replace_module(key, mod.to(dev))
+    for key in replaced:
+        model.replace_module(key, twin._modules[key].to(dev))
     return model
