@@ -457,7 +457,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       const RadialTableGrid tg = radial_table_grid(c.edge);
       OP(CAT_CONV_BWD_EDGE, conv_bwd_tab(L.conv, N, NA, (int)E, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h),
                                          tg.n, b.g_conv, denom[t], b.dY, dy_written ? 1 : 0, b.ddr, ddr_written ? 1 : 0,
-                                         m->split_bwd_x ? nullptr : dxs, st));
+                                         dxs, st));   // split_bwd_x does not apply: there is no [E, wn] weight tensor to re-read
       dy_written = ddr_written = true;
     } else {
       // d weight, d Y and (t > 0) d x[src] in one pass: the source rows are accumulated with RED.ADD
@@ -475,7 +475,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     if (t > 0) {
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
       OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
-      if (!L.fused && m->split_bwd_x)
+      if (!L.fused && !L.tabconv && m->split_bwd_x)
         OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
       OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
