@@ -144,7 +144,11 @@ def generate_header():
     out = ['// GENERATED by `python -m sevennet_finetuning_b200.cg` - do not edit.',
            '// Coupling tables C[m1,m2,m3]*sqrt(2 l3+1) of the uvu tensor product, unrolled.',
            '// Y is the 9-vector (l=0 | l=1 | l=2) of an edge; M is row-major [2l1+1][2l3+1].',
-           '#pragma once', '']
+           '#pragma once', '',
+           '__device__ __forceinline__ float cg_fma(float c, float g, float acc) { return fmaf(c, g, acc); }',
+           '__device__ __forceinline__ float2 cg_fma(float c, float2 g, float2 acc) {',
+           '  return __ffma2_rn(make_float2(c, c), g, acc);',
+           '}', '']
     yoff = (0, 1, 4)
     for (l1, l2, l3) in ALL_PATHS:
         C = coupling(l1, l2, l3)
@@ -158,12 +162,13 @@ def generate_header():
                          if abs(C[a, b, c]) > 1e-9]
                 out.append(f'  M[{a * d3 + c}] = {" + ".join(terms) if terms else "0.0f"};')
         out.append('}')
-        out.append(f'__device__ __forceinline__ void cg_dY_{tag}(const float* G, float* dY) {{')
+        # T = float (one channel) or float2 (a channel pair, packed FFMA2 arithmetic of sm_100a)
+        out.append(f'template <class T> __device__ __forceinline__ void cg_dY_{tag}(const T* G, T* dY) {{')
         for b in range(d2):
-            terms = [f'{_fmt(C[a, b, c])} * G[{a * d3 + c}]' for a in range(d1) for c in range(d3)
-                     if abs(C[a, b, c]) > 1e-9]
-            if terms:
-                out.append(f'  dY[{yoff[l2] + b}] += {" + ".join(terms)};')
+            for a in range(d1):
+                for c in range(d3):
+                    if abs(C[a, b, c]) > 1e-9:
+                        out.append(f'  dY[{yoff[l2] + b}] = cg_fma({_fmt(C[a, b, c])}, G[{a * d3 + c}], dY[{yoff[l2] + b}]);')
         out.append('}')
         out.append('')
     return '\n'.join(out)

@@ -53,6 +53,18 @@ size_t radial_table_floats(const EdgeParams& p, const MlpDesc& d);
 bool radial_table_supported(const MlpDesc& d);
 int radial_table_build(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
                        const float* W2, float* T, cudaStream_t st);
+// packed table (12 bytes per weight) read by the channel-pair convolution kernels (conv_pair.cu)
+constexpr float kTabCDScale = 4096.0f;
+size_t radial_table_packed_bytes(const EdgeParams& p, const MlpDesc& d);
+int radial_table_build_packed(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
+                              const float* W2, void* T, cudaStream_t st);
+bool conv_pair_supported(const ConvDesc& d);
+int conv_pair_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                  const float* len, const void* packed_table, float inv_h, int n_grid, float denom, float* out, cudaStream_t st);
+// d Y and d E / d r are ADDED into dY / dr (the caller zeroes them once per reverse pass); d x is overwritten
+int conv_pair_bwd(const ConvDesc& d, int n_dst, int n_src, const int* rowptr, const int* src, const float* x, const float* Y,
+                  const float* len, const void* packed_table, float inv_h, int n_grid, const float* gout, float denom,
+                  float* dY, float* dr, float* dx, cudaStream_t st);
 size_t radial_table_order_bytes(long long E);
 int radial_table_order(const EdgeParams& p, long long E, const float* len, void* ws, int* order, cudaStream_t st);   // edge ids sorted by interval
 // order: edge ids sorted by interval (nullptr = natural order)

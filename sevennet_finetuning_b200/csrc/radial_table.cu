@@ -13,6 +13,7 @@
 // Training keeps the explicit MLP (its parameters change every step and need gradients).
 #include <algorithm>
 
+#include <cuda_fp16.h>
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
@@ -117,6 +118,47 @@ radial_table_build_kernel(EdgeParams p, MlpDesc d, double h, const float* __rest
     const double v0 = v[0] * sc, v1 = v[1] * sc, m0 = m[0] * sc * h, m1 = m[1] * sc * h, D = v1 - v0;
     reinterpret_cast<float4*>(row)[k] =
         make_float4((float)v0, (float)m0, (float)(3.0 * D - 2.0 * m0 - m1), (float)(m0 + m1 - 2.0 * D));
+  }
+}
+
+// Packed layout for the channel-pair convolution kernels (conv_pair.cu): the same interval cubics, 12 bytes per weight
+// instead of 16.  Per interval i and weight PAIR q = (2q, 2q+1):  AB[i][q] = float4 {a0, a1, b0, b1} (fp32) and
+// CD[i][q] = 4 x fp16 {c0, c1, d0, d1} scaled by kTabCDScale.  a and b carry the value and the first-order term and stay
+// fp32; c (second order in h) and d (third order) are about 1e-5 and 1e-8 of the weight, so 11 mantissa bits bound their
+// contribution to w at 1e-8 relative and to dw/dr at 1e-6 relative (the scale keeps the c and d of small weights out of
+// the fp16 subnormals).  The convolution kernels are bound by these reads from L2 (960 weights per edge per pass).
+__global__ void __launch_bounds__(128)
+radial_table_build_packed_kernel(EdgeParams p, MlpDesc d, double h, const float* __restrict__ coeffs,
+                                 const float* __restrict__ W0, const float* __restrict__ W1, const float* __restrict__ W2,
+                                 float4* __restrict__ AB, uint2* __restrict__ CD) {
+  __shared__ double e[32], de[32], a1[kTabMaxHidden], da1[kTabMaxHidden], a2[2][kTabMaxHidden], da2[2][kTabMaxHidden];
+  const int i = blockIdx.x;
+  for (int end = 0; end < 2; ++end)
+    mlp_hidden_f64(p, d, (double)(i + end) * h, coeffs, W0, W1, e, de, a1, da1, a2[end], da2[end]);
+  const double sc = 1.0 / sqrt((double)d.h2);
+  const int np = d.wn / 2;
+  for (int q = threadIdx.x; q < np; q += blockDim.x) {
+    float a[2], b[2], c[2], dd[2];
+    for (int s = 0; s < 2; ++s) {
+      const int k = 2 * q + s;
+      double v[2] = {0.0, 0.0}, m[2] = {0.0, 0.0};
+      for (int n = 0; n < d.h2; ++n) {
+        const double w2 = (double)W2[(size_t)n * d.wn + k];
+        v[0] += a2[0][n] * w2; m[0] += da2[0][n] * w2;
+        v[1] += a2[1][n] * w2; m[1] += da2[1][n] * w2;
+      }
+      const double v0 = v[0] * sc, v1 = v[1] * sc, m0 = m[0] * sc * h, m1 = m[1] * sc * h, D = v1 - v0;
+      a[s] = (float)v0;
+      b[s] = (float)m0;
+      c[s] = (float)((3.0 * D - 2.0 * m0 - m1) * (double)kTabCDScale);
+      dd[s] = (float)((m0 + m1 - 2.0 * D) * (double)kTabCDScale);
+    }
+    AB[(size_t)i * np + q] = make_float4(a[0], a[1], b[0], b[1]);
+    const __half2 ch = __floats2half2_rn(c[0], c[1]), dh = __floats2half2_rn(dd[0], dd[1]);
+    uint2 u;
+    u.x = *reinterpret_cast<const unsigned*>(&ch);
+    u.y = *reinterpret_cast<const unsigned*>(&dh);
+    CD[(size_t)i * np + q] = u;
   }
 }
 
@@ -235,6 +277,19 @@ size_t radial_table_floats(const EdgeParams& p, const MlpDesc& d) {
 bool radial_table_supported(const MlpDesc& d) {
   return d.nb >= 1 && d.nb <= 32 && d.h1 >= 1 && d.h1 <= kTabMaxHidden && d.h2 >= 1 && d.h2 <= kTabMaxHidden && d.wn >= 4 &&
          d.wn % 4 == 0;
+}
+
+size_t radial_table_packed_bytes(const EdgeParams& p, const MlpDesc& d) {   // AB plane then CD plane
+  return (size_t)radial_table_grid(p).n * (d.wn / 2) * (sizeof(float4) + sizeof(uint2));
+}
+int radial_table_build_packed(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
+                              const float* W2, void* T, cudaStream_t st) {
+  B200_REQUIRE(radial_table_supported(d) && d.wn % 2 == 0, "radial_table_build_packed: unsupported weight_nn shape");
+  const RadialTableGrid g = radial_table_grid(p);
+  float4* AB = reinterpret_cast<float4*>(T);
+  uint2* CD = reinterpret_cast<uint2*>(AB + (size_t)g.n * (d.wn / 2));
+  radial_table_build_packed_kernel<<<g.n, 128, 0, st>>>(p, d, g.h, coeffs, W0, W1, W2, AB, CD);
+  return check_launch("radial_table_build_packed");
 }
 
 int radial_table_build(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
