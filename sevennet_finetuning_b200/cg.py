@@ -146,8 +146,12 @@ def generate_header():
            '// Y is the 9-vector (l=0 | l=1 | l=2) of an edge; M is row-major [2l1+1][2l3+1].',
            '#pragma once', '',
            '__device__ __forceinline__ float cg_fma(float c, float g, float acc) { return fmaf(c, g, acc); }',
-           '__device__ __forceinline__ float2 cg_fma(float c, float2 g, float2 acc) {',
-           '  return __ffma2_rn(make_float2(c, c), g, acc);',
+           '// a channel pair packed in one 64-bit register: both halves with one FFMA2 (fma.rn.f32x2)',
+           '__device__ __forceinline__ unsigned long long cg_fma(float c, unsigned long long g, unsigned long long acc) {',
+           '  unsigned long long r, cc;',
+           '  asm("mov.b64 %0, {%1, %1};" : "=l"(cc) : "f"(c));',
+           '  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(cc), "l"(g), "l"(acc));',
+           '  return r;',
            '}', '']
     yoff = (0, 1, 4)
     for (l1, l2, l3) in ALL_PATHS:

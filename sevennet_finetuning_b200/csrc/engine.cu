@@ -87,6 +87,7 @@ struct Layer {
   bool fused;   // radial layer + convolution run as the fused tcgen05 kernels (fused.cu)
   bool table;   // per-edge weights interpolated from the tabulated radial function (radial_table.cu)
   bool tabconv; // ... inside the convolution kernels: neither the weights nor their gradient are materialised
+  bool pair;    // ... by the channel-pair kernels (conv_pair.cu): packed table, pair-interleaved source rows
 };
 
 }  // namespace b200
@@ -185,6 +186,7 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.fused = fused_env && fused_supported(L.conv, L.mlp);
     L.table = !fused_env && radial_table_supported(L.mlp) && !(getenv("B200_RADIAL_TABLE") && atoi(getenv("B200_RADIAL_TABLE")) == 0);
     L.tabconv = L.table && !(getenv("B200_TABLE_IN_CONV") && atoi(getenv("B200_TABLE_IN_CONV")) == 0);
+    L.pair = L.tabconv && conv_pair_supported(L.conv) && !(getenv("B200_CONV_PAIR") && atoi(getenv("B200_CONV_PAIR")) == 0);
     m->layers.push_back(L);
     m->split_bwd_x = getenv("B200_SPLIT_BWD_X") && atoi(getenv("B200_SPLIT_BWD_X")) != 0;
     const std::string s = std::to_string(t);
@@ -370,13 +372,19 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       const Layer& L = m->layers[t];
       if (!L.table) continue;
       const std::string s = std::to_string(t);
-      if (!m->tables[t] && cudaMalloc(&m->tables[t], sizeof(float) * radial_table_floats(c.edge, L.mlp)) != cudaSuccess) {
+      const size_t tbytes = L.pair ? radial_table_packed_bytes(c.edge, L.mlp) : sizeof(float) * radial_table_floats(c.edge, L.mlp);
+      if (!m->tables[t] && cudaMalloc(&m->tables[t], tbytes) != cudaSuccess) {
         set_error("model_compute: cudaMalloc of the radial table failed");
         return B200_ERR_CUDA;
       }
-      OP(CAT_MLP_FWD, radial_table_build(c.edge, L.mlp, coeffs, P(m, s + "_convolution.weight_nn.layer0.weight"),
-                                         P(m, s + "_convolution.weight_nn.layer1.weight"),
-                                         P(m, s + "_convolution.weight_nn.layer2.weight"), m->tables[t], st));
+      if (L.pair)
+        OP(CAT_MLP_FWD, radial_table_build_packed(c.edge, L.mlp, coeffs, P(m, s + "_convolution.weight_nn.layer0.weight"),
+                                                  P(m, s + "_convolution.weight_nn.layer1.weight"),
+                                                  P(m, s + "_convolution.weight_nn.layer2.weight"), m->tables[t], st));
+      else
+        OP(CAT_MLP_FWD, radial_table_build(c.edge, L.mlp, coeffs, P(m, s + "_convolution.weight_nn.layer0.weight"),
+                                           P(m, s + "_convolution.weight_nn.layer1.weight"),
+                                           P(m, s + "_convolution.weight_nn.layer2.weight"), m->tables[t], st));
     }
     m->tables_dirty = false;
   }
@@ -401,6 +409,8 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     // layer 0: ghost rows are recomputed from their types (model_build.py:134-172 "ghost_" modules);
     // later layers: the owners' rows are fetched through the halo hook
     OP(CAT_NODE, irreps_linear(L.si1, t == 0 ? NA : N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+    // the channel-pair kernels read pair-interleaved rows; ghost rows arrive from their owners already interleaved
+    if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, t == 0 ? NA : N, b.xs[t], 0, st));
     if (t > 0) HALO(B200_HALO_FWD_X, t, b.xs[t], L.conv.xdim);
     const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
     const float* W1 = P(m, s + "_convolution.weight_nn.layer1.weight");
@@ -409,7 +419,11 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       OP(CAT_MLP_FWD, fused_radial(c.edge, L.mlp, E, edge_vec, coeffs, W0, W1, b.rad[t], st));
       OP(CAT_CONV_FWD, fused_conv_fwd(L.conv, N, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, denom[t], b.conv_out, st));
     } else {
-      if (L.tabconv) {
+      if (L.pair) {
+        const RadialTableGrid tg = radial_table_grid(c.edge);
+        OP(CAT_CONV_FWD, conv_pair_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h), tg.n, denom[t],
+                                       b.conv_out, st));
+      } else if (L.tabconv) {
         const RadialTableGrid tg = radial_table_grid(c.edge);
         OP(CAT_CONV_FWD, conv_fwd_tab(L.conv, N, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h), tg.n, denom[t],
                                       b.conv_out, st));
@@ -438,6 +452,15 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   float* gp = b.g_x[1];
   OP(CAT_NODE, irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
   bool dy_written = false, ddr_written = false, demb_written = false;   // which per-edge gradient buffers hold a sum already
+  {   // the channel-pair kernels ADD their d Y and d E / d r into the per-edge buffers
+    bool any_pair = false;
+    for (const Layer& L : m->layers) any_pair = any_pair || L.pair;
+    if (any_pair && E > 0) {
+      cudaMemsetAsync(b.dY, 0, sizeof(float) * 9 * (size_t)E, st);
+      cudaMemsetAsync(b.ddr, 0, sizeof(float) * (size_t)E, st);
+      dy_written = ddr_written = true;
+    }
+  }
   for (int t = nl - 1; t >= 0; --t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
@@ -452,6 +475,10 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       OP(CAT_CONV_BWD_EDGE, fused_conv_bwd(L.conv, NA, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, b.g_conv, denom[t], dxs, b.dY,
                                            b.ddr, ddr_written ? 1 : 0, st));
       dy_written = ddr_written = true;
+    } else if (L.pair) {
+      const RadialTableGrid tg = radial_table_grid(c.edge);
+      OP(CAT_CONV_BWD_EDGE, conv_pair_bwd(L.conv, N, NA, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h), tg.n,
+                                          b.g_conv, denom[t], b.dY, b.ddr, dxs, st));
     } else if (L.tabconv) {
       // d Y, d E / d r and (t > 0) d x[src] in one pass; the weight gradient is contracted with d w / d r in registers
       const RadialTableGrid tg = radial_table_grid(c.edge);
@@ -478,6 +505,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       if (!L.fused && !L.tabconv && m->split_bwd_x)
         OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
+      if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, N, b.conv_out, 1, st));   // back to the standard row layout
       OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
       std::swap(g, gp);
     }

@@ -59,6 +59,7 @@ size_t radial_table_packed_bytes(const EdgeParams& p, const MlpDesc& d);
 int radial_table_build_packed(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
                               const float* W2, void* T, cudaStream_t st);
 bool conv_pair_supported(const ConvDesc& d);
+int conv_pair_interleave(const ConvDesc& d, long long n_rows, float* x, int inverse, cudaStream_t st);
 int conv_pair_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
                   const float* len, const void* packed_table, float inv_h, int n_grid, float denom, float* out, cudaStream_t st);
 // d Y and d E / d r are ADDED into dY / dr (the caller zeroes them once per reverse pass); d x is overwritten

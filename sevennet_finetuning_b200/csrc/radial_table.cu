@@ -123,14 +123,15 @@ radial_table_build_kernel(EdgeParams p, MlpDesc d, double h, const float* __rest
 
 // Packed layout for the channel-pair convolution kernels (conv_pair.cu): the same interval cubics, 12 bytes per weight
 // instead of 16.  Per interval i and weight PAIR q = (2q, 2q+1):  AB[i][q] = float4 {a0, a1, b0, b1} (fp32) and
-// CD[i][q] = 4 x fp16 {c0, c1, d0, d1} scaled by kTabCDScale.  a and b carry the value and the first-order term and stay
+// C[i][q] = 2 x fp16 {c0, c1}, D[i][q] = 2 x fp16 {d0, d1}, both scaled by kTabCDScale (three planes: the forward pass
+// does not read D, whose term is 4e-8 of the weight; the reverse pass needs it for dw/dr).  a and b carry the value and the first-order term and stay
 // fp32; c (second order in h) and d (third order) are about 1e-5 and 1e-8 of the weight, so 11 mantissa bits bound their
 // contribution to w at 1e-8 relative and to dw/dr at 1e-6 relative (the scale keeps the c and d of small weights out of
 // the fp16 subnormals).  The convolution kernels are bound by these reads from L2 (960 weights per edge per pass).
 __global__ void __launch_bounds__(128)
 radial_table_build_packed_kernel(EdgeParams p, MlpDesc d, double h, const float* __restrict__ coeffs,
                                  const float* __restrict__ W0, const float* __restrict__ W1, const float* __restrict__ W2,
-                                 float4* __restrict__ AB, uint2* __restrict__ CD) {
+                                 float4* __restrict__ AB, unsigned* __restrict__ Cp, unsigned* __restrict__ Dp) {
   __shared__ double e[32], de[32], a1[kTabMaxHidden], da1[kTabMaxHidden], a2[2][kTabMaxHidden], da2[2][kTabMaxHidden];
   const int i = blockIdx.x;
   for (int end = 0; end < 2; ++end)
@@ -155,10 +156,8 @@ radial_table_build_packed_kernel(EdgeParams p, MlpDesc d, double h, const float*
     }
     AB[(size_t)i * np + q] = make_float4(a[0], a[1], b[0], b[1]);
     const __half2 ch = __floats2half2_rn(c[0], c[1]), dh = __floats2half2_rn(dd[0], dd[1]);
-    uint2 u;
-    u.x = *reinterpret_cast<const unsigned*>(&ch);
-    u.y = *reinterpret_cast<const unsigned*>(&dh);
-    CD[(size_t)i * np + q] = u;
+    Cp[(size_t)i * np + q] = *reinterpret_cast<const unsigned*>(&ch);
+    Dp[(size_t)i * np + q] = *reinterpret_cast<const unsigned*>(&dh);
   }
 }
 
@@ -279,16 +278,17 @@ bool radial_table_supported(const MlpDesc& d) {
          d.wn % 4 == 0;
 }
 
-size_t radial_table_packed_bytes(const EdgeParams& p, const MlpDesc& d) {   // AB plane then CD plane
-  return (size_t)radial_table_grid(p).n * (d.wn / 2) * (sizeof(float4) + sizeof(uint2));
+size_t radial_table_packed_bytes(const EdgeParams& p, const MlpDesc& d) {   // AB plane, C plane, D plane
+  return (size_t)radial_table_grid(p).n * (d.wn / 2) * (sizeof(float4) + 2 * sizeof(unsigned));
 }
 int radial_table_build_packed(const EdgeParams& p, const MlpDesc& d, const float* coeffs, const float* W0, const float* W1,
                               const float* W2, void* T, cudaStream_t st) {
   B200_REQUIRE(radial_table_supported(d) && d.wn % 2 == 0, "radial_table_build_packed: unsupported weight_nn shape");
   const RadialTableGrid g = radial_table_grid(p);
   float4* AB = reinterpret_cast<float4*>(T);
-  uint2* CD = reinterpret_cast<uint2*>(AB + (size_t)g.n * (d.wn / 2));
-  radial_table_build_packed_kernel<<<g.n, 128, 0, st>>>(p, d, g.h, coeffs, W0, W1, W2, AB, CD);
+  unsigned* Cp = reinterpret_cast<unsigned*>(AB + (size_t)g.n * (d.wn / 2));
+  unsigned* Dp = Cp + (size_t)g.n * (d.wn / 2);
+  radial_table_build_packed_kernel<<<g.n, 128, 0, st>>>(p, d, g.h, coeffs, W0, W1, W2, AB, Cp, Dp);
   return check_launch("radial_table_build_packed");
 }
 
