@@ -173,6 +173,11 @@ int b200_rescale_fwd(int n_nodes, const int32_t* types, const float* scaled, con
                      int species_wise, float* atomic_energy, void* stream);
 /* out[c] = sum_n in[n, c], c < ncol <= 8 (fp64 accumulation, deterministic) */
 int b200_colsum(int n_rows, int ncol, const float* in, float* out, void* stream);
+/* Halo exchange of the spatially decomposed call: pack_forward_init / unpack_forward_init (index_select of the rows a
+ * peer asked for, pair_e3gnn_parallel.cpp:803-866) and pack_reverse / unpack_reverse (index_add of the returned gradient
+ * rows into their owners, :867-933).  rows: [n, width] fp32; idx: int32 row numbers; out / in: packed [m, width]. */
+int b200_halo_pack(int64_t n_send, int width, const float* rows, const int32_t* idx, float* out, void* stream);
+int b200_halo_unpack_add(int64_t n_recv, int width, float* rows, const int32_t* idx, const float* in, void* stream);
 
 /* ---- forces / virial: sevenn/nn/force_output.py:158-215 (ForceStressOutputFromEdge) ----------------- */
 int b200_force_virial(int n_atoms, const int32_t* rowptr, const int32_t* rrowptr, const int32_t* eid_by_src,

@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libsevennet_b200.so')
+LIB_PATH = os.environ.get('B200_LIB_PATH') or os.path.join(HERE, 'libsevennet_b200.so')   # override: kernel experiments
 
 B200_CUTOFF_POLY, B200_CUTOFF_XPLOR = 0, 1
 
@@ -76,6 +76,8 @@ SIGNATURES = {
     'b200_embed_fwd': (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     'b200_rescale_fwd': (_i, [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     'b200_colsum': (_i, [_i, _i, _vp, _vp, _vp]),
+    'b200_halo_pack': (_i, [_i64, _i, _vp, _vp, _vp, _vp]),
+    'b200_halo_unpack_add': (_i, [_i64, _i, _vp, _vp, _vp, _vp]),
     'b200_force_virial': (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_graph_workspace_bytes': (_sz, [_i]),
     'b200_graph_count': (_i, [_i, _vp, _P(C.c_double), _P(_i), C.c_double, _vp, _vp, _P(_i64), _vp]),

@@ -155,6 +155,14 @@ int b200_rescale_fwd(int n, const int32_t* types, const float* scaled, const flo
                      int species_wise, float* out, void* stream) {
   return rescale_fwd(n, types, scaled, scale, shift, species_wise, out, ST(stream));
 }
+int b200_halo_pack(int64_t n_send, int width, const float* rows, const int32_t* idx, float* out, void* stream) {
+  B200_REQUIRE(n_send >= 0 && width >= 0 && (n_send == 0 || (rows && idx && out)), "halo_pack: null argument");
+  return halo_pack(n_send, width, rows, idx, out, ST(stream));
+}
+int b200_halo_unpack_add(int64_t n_recv, int width, float* rows, const int32_t* idx, const float* in, void* stream) {
+  B200_REQUIRE(n_recv >= 0 && width >= 0 && (n_recv == 0 || (rows && idx && in)), "halo_unpack_add: null argument");
+  return halo_unpack_add(n_recv, width, rows, idx, in, ST(stream));
+}
 int b200_colsum(int n_rows, int ncol, const float* in, float* out, void* stream) {
   return colsum(n_rows, ncol, in, out, ST(stream));
 }

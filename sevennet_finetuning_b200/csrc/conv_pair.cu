@@ -26,7 +26,23 @@
 namespace b200 {
 namespace pairk {
 
-constexpr int TE = 8;          // edges per chunk
+#ifndef B200_PAIR_TE
+#define B200_PAIR_TE 8
+#endif
+#ifndef B200_PAIR_FWD_UNROLL
+#define B200_PAIR_FWD_UNROLL 2
+#endif
+#ifndef B200_PAIR_BWD_UNROLL
+#define B200_PAIR_BWD_UNROLL 2
+#endif
+#ifndef B200_PAIR_FWD_MINB
+#define B200_PAIR_FWD_MINB 3
+#endif
+#ifndef B200_PAIR_BWD_MINB
+#define B200_PAIR_BWD_MINB 2
+#endif
+constexpr int kFwdUnroll = B200_PAIR_FWD_UNROLL, kBwdUnroll = B200_PAIR_BWD_UNROLL;   // the two edges of a pair: unrolled or looped
+constexpr int TE = B200_PAIR_TE;          // edges per chunk (even, <= 8)
 constexpr float kInvSqrt3 = 0.5773502691896258f;
 constexpr float kInvSqrt5 = 0.4472135954999579f;
 
@@ -437,6 +453,7 @@ template <int WARP, int LOUT>
 __device__ __forceinline__ void stage_store(const WarpSmem<WARP>& sm, const Tab& tb, int lane, const StageIn& in) {
   constexpr int REC = WarpSmem<WARP>::REC;
   const int k = lane >> 2, j = lane & 3;
+  if (k >= TE) return;
   float* r = sm.rec + k * REC;
   if (j == 0) {
 #pragma unroll
@@ -530,7 +547,7 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
     for (int kk = 0; kk < ne; kk += 2) {   // pairs of edges; a zero record / zero row stands behind an odd end
       if constexpr (MAIN) {
         // warp A takes both edges of the pair, the half-warps of warp B one each
-#pragma unroll
+#pragma unroll kFwdUnroll
         for (int s2 = 0; s2 < (WARP == 0 ? 2 : 1); ++s2) {
           const int k = kk + (WARP == 0 ? s2 : lm.half);
           const float t = sm.tt[k], st = t * (1.0f / kTabCDScale);
@@ -541,7 +558,7 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
           LM::fwd(sm.rec + k * REC, X, e, t, st, accM);
         }
       }
-#pragma unroll
+#pragma unroll kFwdUnroll
       for (int s2 = 0; s2 < 2; ++s2) {
         const int k = kk + s2;
         const float t = sm.tt[k], st = t * (1.0f / kTabCDScale);
@@ -569,12 +586,17 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
   if (lm.act0) L0::store_o(d, orow, lm.q0, a.scale, acc0);
 }
 
-template <int LOUT, bool MAIN>
-__global__ void __launch_bounds__(64) conv_pair_fwd_kernel(ConvDesc d, Args a) {
+// One kernel per warp type: all warps of a launch run the same loop, which then fits the instruction cache (with both
+// types in one kernel 30 % of the issue slots were lost to instruction fetch, ncu stall_no_inst).  Warp w of a CTA owns
+// destination row blockIdx.x * WPC + w and its own slice of the dynamic shared memory.
+constexpr int WPC = 4;
+template <int WT, int LOUT, bool MAIN>
+__global__ void __launch_bounds__(32 * WPC, B200_PAIR_FWD_MINB) conv_pair_fwd_kernel(ConvDesc d, Args a, int n_dst) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp == 0) fwd_warp<0, LOUT, MAIN>(d, a, smem, blockIdx.x, lane);
-  else fwd_warp<1, LOUT, MAIN>(d, a, smem + WarpSmem<0>::bytes(Seg<0>(d).xw), blockIdx.x, lane);
+  const int row = blockIdx.x * WPC + warp;
+  if (row >= n_dst) return;
+  fwd_warp<WT, LOUT, MAIN>(d, a, smem + warp * WarpSmem<WT>::bytes(Seg<WT>(d).xw), row, lane);
 }
 
 // ---- reverse pass ------------------------------------------------------------------------------------------------
@@ -666,7 +688,7 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = 0.f;
       if constexpr (MAIN) {
-#pragma unroll
+#pragma unroll kBwdUnroll
         for (int s2 = 0; s2 < (WARP == 0 ? 2 : 1); ++s2) {
           const int k = kk + (WARP == 0 ? s2 : lm.half);
           const float t = sm.tt[k], st = t * (1.0f / kTabCDScale);
@@ -684,7 +706,11 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
           }
           if constexpr (WARP == 0) {
 #pragma unroll
-            for (int m = 0; m < 8; ++m) v[8 * s2 + m] = hsum(dY[1 + m]);
+            for (int m = 0; m < 8; ++m) {   // (no v[8 * s2 + m]: the loop over s2 may stay rolled)
+              const float s = hsum(dY[1 + m]);
+              if (s2 == 0) v[m] = s;
+              else v[8 + m] = s;
+            }
             if (s2 == 0) r0 = hsum(drp);
             else r1 = hsum(drp);
           } else {   // half-warp h holds edge kk + h
@@ -700,7 +726,7 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
           }
         }
       }
-#pragma unroll
+#pragma unroll kBwdUnroll
       for (int s2 = 0; s2 < 2; ++s2) {
         const int k = kk + s2;
         const float t = sm.tt[k], st = t * (1.0f / kTabCDScale);
@@ -717,7 +743,11 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
         }
         if constexpr (LOUT == 2) {
 #pragma unroll
-          for (int m = 0; m < 8; ++m) v[8 * s2 + m] += hsum(dY[1 + m]);
+          for (int m = 0; m < 8; ++m) {
+            const float s = hsum(dY[1 + m]);
+            if (s2 == 0) v[m] += s;
+            else v[8 + m] += s;
+          }
         }
         if (s2 == 0) r0 += hsum(drp);
         else r1 += hsum(drp);
@@ -739,12 +769,13 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
   }
 }
 
-template <int LOUT, bool MAIN, bool DX>
-__global__ void __launch_bounds__(64) conv_pair_bwd_kernel(ConvDesc d, Args a) {
+template <int WT, int LOUT, bool MAIN, bool DX>
+__global__ void __launch_bounds__(32 * WPC, B200_PAIR_BWD_MINB) conv_pair_bwd_kernel(ConvDesc d, Args a, int n_dst) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp == 0) bwd_warp<0, LOUT, MAIN, DX>(d, a, smem, blockIdx.x, lane);
-  else bwd_warp<1, LOUT, MAIN, DX>(d, a, smem + WarpSmem<0>::bytes(Seg<0>(d).xw), blockIdx.x, lane);
+  const int row = blockIdx.x * WPC + warp;
+  if (row >= n_dst) return;
+  bwd_warp<WT, LOUT, MAIN, DX>(d, a, smem + warp * WarpSmem<WT>::bytes(Seg<WT>(d).xw), row, lane);
 }
 
 }  // namespace pairk
@@ -765,8 +796,8 @@ int conv_pair_interleave(const ConvDesc& d, long long n_rows, float* x, int inve
   return check_launch("conv_pair_interleave");
 }
 
-static size_t pair_smem_bytes(const ConvDesc& d) {
-  return pairk::WarpSmem<0>::bytes(pairk::Seg<0>(d).xw) + pairk::WarpSmem<1>::bytes(pairk::Seg<1>(d).xw);
+template <int WT> static size_t pair_smem_bytes(const ConvDesc& d) {
+  return pairk::WPC * pairk::WarpSmem<WT>::bytes(pairk::Seg<WT>(d).xw);
 }
 
 static pairk::Tab make_tab(const ConvDesc& d, const void* packed, float inv_h, int n_grid) {
@@ -780,15 +811,21 @@ static pairk::Tab make_tab(const ConvDesc& d, const void* packed, float inv_h, i
   return t;
 }
 
-template <class K> static int launch_pair(K kernel, const ConvDesc& d, const pairk::Args& a, int n_dst, cudaStream_t st) {
-  const size_t sm = pair_smem_bytes(d);
+template <int WT, class K> static int launch_pair(K kernel, const ConvDesc& d, const pairk::Args& a, int n_dst, cudaStream_t st) {
+  const size_t sm = pair_smem_bytes<WT>(d);
   if (sm > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess) {
     set_error("conv_pair: cannot reserve %zu bytes of shared memory", sm);
     return B200_ERR_CUDA;
   }
-  kernel<<<n_dst, 64, sm, st>>>(d, a);
+  kernel<<<(n_dst + pairk::WPC - 1) / pairk::WPC, 32 * pairk::WPC, sm, st>>>(d, a, n_dst);
   return B200_OK;
 }
+// both warp types, one launch each
+#define B200_PAIR_BOTH(KERNEL, ...)                                                     \
+  do {                                                                                  \
+    rc = launch_pair<0>(pairk::KERNEL<0, __VA_ARGS__>, d, a, n_dst, st);                \
+    if (rc == B200_OK) rc = launch_pair<1>(pairk::KERNEL<1, __VA_ARGS__>, d, a, n_dst, st); \
+  } while (0)
 
 int conv_pair_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
                   const float* len, const void* packed_table, float inv_h, int n_grid, float denom, float* out,
@@ -802,12 +839,15 @@ int conv_pair_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* sr
   a.out = out;
   const bool main = d.m1 > 0;
   int rc;
-  if (d.lout == 2) rc = main ? launch_pair(pairk::conv_pair_fwd_kernel<2, true>, d, a, n_dst, st)
-                             : launch_pair(pairk::conv_pair_fwd_kernel<2, false>, d, a, n_dst, st);
-  else rc = main ? launch_pair(pairk::conv_pair_fwd_kernel<0, true>, d, a, n_dst, st)
-                 : launch_pair(pairk::conv_pair_fwd_kernel<0, false>, d, a, n_dst, st);
+  if (d.lout == 2) {
+    if (main) B200_PAIR_BOTH(conv_pair_fwd_kernel, 2, true);
+    else B200_PAIR_BOTH(conv_pair_fwd_kernel, 2, false);
+  } else {
+    if (main) B200_PAIR_BOTH(conv_pair_fwd_kernel, 0, true);
+    else B200_PAIR_BOTH(conv_pair_fwd_kernel, 0, false);
+  }
   if (rc != B200_OK) return rc;
-  return check_launch("conv_pair_fwd");
+  return check_launch("conv_pair_fwd", 2);
 }
 
 int conv_pair_bwd(const ConvDesc& d, int n_dst, int n_src, const int* rowptr, const int* src, const float* x, const float* Y,
@@ -823,16 +863,18 @@ int conv_pair_bwd(const ConvDesc& d, int n_dst, int n_src, const int* rowptr, co
   a.gout = gout; a.dY = dY; a.dr = dr; a.dx = dx;
   const bool main = d.m1 > 0;
   int rc;
-#define B200_PAIR_BWD(LOUT)                                                                                            \
-  (main ? (dx ? launch_pair(pairk::conv_pair_bwd_kernel<LOUT, true, true>, d, a, n_dst, st)                             \
-              : launch_pair(pairk::conv_pair_bwd_kernel<LOUT, true, false>, d, a, n_dst, st))                           \
-        : (dx ? launch_pair(pairk::conv_pair_bwd_kernel<LOUT, false, true>, d, a, n_dst, st)                            \
-              : launch_pair(pairk::conv_pair_bwd_kernel<LOUT, false, false>, d, a, n_dst, st)))
-  if (d.lout == 2) rc = B200_PAIR_BWD(2);
-  else rc = B200_PAIR_BWD(0);
+#define B200_PAIR_BWD(LOUT)                                                        \
+  do {                                                                             \
+    if (main && dx) B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, true, true);        \
+    else if (main) B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, true, false);        \
+    else if (dx) B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, false, true);          \
+    else B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, false, false);                 \
+  } while (0)
+  if (d.lout == 2) B200_PAIR_BWD(2);
+  else B200_PAIR_BWD(0);
 #undef B200_PAIR_BWD
   if (rc != B200_OK) return rc;
-  return check_launch("conv_pair_bwd");
+  return check_launch("conv_pair_bwd", 2);
 }
 
 }  // namespace b200

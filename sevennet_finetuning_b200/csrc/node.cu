@@ -194,4 +194,47 @@ int colsum(int n_rows, int ncol, const float* in, float* out, cudaStream_t st) {
   return check_launch("colsum");
 }
 
+// ---- halo exchange: pack the rows a peer asked for / add the rows a peer returned ------------------------------------
+// pair_e3gnn_parallel.cpp:803-866 (pack_forward_init / unpack_forward_init: index_select into the send buffer) and
+// :867-933 (pack_reverse / unpack_reverse: index_add of the returned gradient rows into their owners).
+// One thread per float4 (or float when the width is not a multiple of 4) of the packed buffer.
+template <class V>
+__global__ void halo_pack_kernel(long long total, int wv, const V* __restrict__ rows, const int* __restrict__ idx,
+                                 V* __restrict__ out) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const long long r = i / wv;
+  const int c = (int)(i - r * wv);
+  out[i] = rows[(size_t)__ldg(idx + r) * wv + c];
+}
+// the same owner row can be wanted by several peers: RED.ADD, like the reference's index_add_
+__global__ void halo_unpack_add_kernel(long long total, int width, float* __restrict__ rows, const int* __restrict__ idx,
+                                       const float* __restrict__ in) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const long long r = i / width;
+  const int c = (int)(i - r * width);
+  atomicAdd(rows + (size_t)__ldg(idx + r) * width + c, in[i]);
+}
+
+int halo_pack(long long m, int width, const float* rows, const int* idx, float* out, cudaStream_t st) {
+  if (m == 0 || width == 0) return B200_OK;
+  const bool v4 = width % 4 == 0 && ((uintptr_t)rows % 16 == 0) && ((uintptr_t)out % 16 == 0);
+  if (v4) {
+    const long long tot = m * (width / 4);
+    halo_pack_kernel<float4><<<blocks_for(tot, 256), 256, 0, st>>>(tot, width / 4, reinterpret_cast<const float4*>(rows), idx,
+                                                                   reinterpret_cast<float4*>(out));
+  } else {
+    const long long tot = m * width;
+    halo_pack_kernel<float><<<blocks_for(tot, 256), 256, 0, st>>>(tot, width, rows, idx, out);
+  }
+  return check_launch("halo_pack");
+}
+int halo_unpack_add(long long m, int width, float* rows, const int* idx, const float* in, cudaStream_t st) {
+  if (m == 0 || width == 0) return B200_OK;
+  const long long tot = m * width;
+  halo_unpack_add_kernel<<<blocks_for(tot, 256), 256, 0, st>>>(tot, width, rows, idx, in);
+  return check_launch("halo_unpack_add");
+}
+
 }  // namespace b200

@@ -101,6 +101,8 @@ int embed_fwd(int n_nodes, int n_species, int dim, const int* types, const float
 int rescale_fwd(int n_nodes, const int* types, const float* scaled, const float* scale, const float* shift,
                 int species_wise, float* out, cudaStream_t st);
 int colsum(int n_rows, int ncol, const float* in, float* out, cudaStream_t st);
+int halo_pack(long long m, int width, const float* rows, const int* idx, float* out, cudaStream_t st);
+int halo_unpack_add(long long m, int width, float* rows, const int* idx, const float* in, cudaStream_t st);
 
 size_t graph_workspace_bytes(int n);
 int graph_count(int n, const double* pos, const double* cell_host, const int* pbc_host, double cutoff, void* ws,

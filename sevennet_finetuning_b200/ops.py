@@ -304,6 +304,18 @@ def force_virial(rowptr, rrowptr, eid, vec, dvec):
     return force, vir
 
 
+def halo_pack(rows, idx, out):
+    """out[k] = rows[idx[k]] (rows the peers asked for); rows [n, width] fp32, idx int32, out [m, width]."""
+    check(lib().b200_halo_pack(idx.shape[0], rows.shape[1], _p(rows), _p(idx), _p(out), _stream()), 'halo_pack')
+    return out
+
+
+def halo_unpack_add(rows, idx, packed):
+    """rows[idx[k]] += packed[k] (gradient / force rows returned by the peers)."""
+    check(lib().b200_halo_unpack_add(idx.shape[0], rows.shape[1], _p(rows), _p(idx), _p(packed), _stream()), 'halo_unpack_add')
+    return rows
+
+
 def colsum(x):
     out = torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
     check(lib().b200_colsum(x.shape[0], x.shape[1], _p(x), _p(out), _stream()), 'colsum')

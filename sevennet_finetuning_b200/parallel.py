@@ -166,17 +166,39 @@ class HaloPlan:
         self.send_rows = g2l[want]
         if self.send_rows.numel() and int(self.send_rows.min()) < 0:
             raise RuntimeError('parallel: a peer asked for an atom this rank does not own')
+        self.send_rows32 = self.send_rows.to(torch.int32)
+        self._bufs = {}
         return self
 
     # ---- the three exchanges (rows: [n_local + n_ghost, width], ghosts after the locals) ----
+    def _buf(self, width, dtype, device):
+        # one packed send / receive buffer per row width, reused by every exchange of the step
+        key = (width, dtype)
+        if key not in self._bufs:
+            self._bufs[key] = torch.empty(self.send_rows.numel(), width, dtype=dtype, device=device)
+        return self._bufs[key]
+
     def fetch_ghost_rows(self, rows):
-        send = rows[:self.n_local].index_select(0, self.send_rows)
+        """pack_forward_init + forward_comm + unpack_forward_init (pair_e3gnn_parallel.cpp:803-866): the owners pack the rows
+        their peers asked for (CUDA kernel b200_halo_pack); the received rows ARE the ghost rows, no unpack copy."""
+        from . import ops
+        send = self._buf(rows.shape[1], rows.dtype, rows.device)
+        if rows.is_cuda:
+            ops.halo_pack(rows, self.send_rows32, send)
+        else:   # gloo tests of the bookkeeping (CPU tensors never reach the engine)
+            torch.index_select(rows[:self.n_local], 0, self.send_rows, out=send)
         self.comm.all_to_all(rows[self.n_local:], send, self.recv_counts, self.send_counts)
 
     def return_ghost_rows(self, rows):
-        back = torch.empty(self.send_rows.numel(), rows.shape[1], dtype=rows.dtype, device=rows.device)
-        self.comm.all_to_all(back, rows[self.n_local:].contiguous(), self.send_counts, self.recv_counts)
-        rows[:self.n_local].index_add_(0, self.send_rows, back)
+        """pack_reverse + reverse_comm + unpack_reverse (:867-933): ghost rows go back to their owners and are added
+        (b200_halo_unpack_add, RED.ADD like the reference's index_add_)."""
+        from . import ops
+        back = self._buf(rows.shape[1], rows.dtype, rows.device)
+        self.comm.all_to_all(back, rows[self.n_local:], self.send_counts, self.recv_counts)
+        if rows.is_cuda:
+            ops.halo_unpack_add(rows, self.send_rows32, back)
+        else:
+            rows[:self.n_local].index_add_(0, self.send_rows, back)
 
     def hook(self, phase, layer, rows):
         if phase == B200_HALO_FWD_X:

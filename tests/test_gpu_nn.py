@@ -456,3 +456,39 @@ def test_nequip_self_connection_model(gold, weights):
     assert fe <= 2e-5 * max(1.0, float(o64['inferred_force'].abs().max())), float(fe)
     se = (out['inferred_stress'].detach().cpu().double() - o64['inferred_stress'].detach()).abs().max()
     assert se <= 1e-4 * float(o64['inferred_stress'].abs().max()), float(se)
+
+
+def test_substitute_into_reference_sequential(gold, weights):
+    """nn.substitute: the reference-side container (oracle restatement of sevenn/nn/sequential.py with replace_module) keeps
+    its identity, every hot-path module is swapped key by key, parameters and their requires_grad flags are carried over,
+    and E/F/S match the golden vectors."""
+    if not torch.cuda.is_available():
+        pytest.skip('needs a CUDA device')
+    from sevennet_finetuning_b200 import nn as b200nn
+    cfg = dict(shift=weights['rescale_atomic_energy.shift'].tolist(), scale=weights['rescale_atomic_energy.scale'].tolist(),
+               conv_denominator=float(weights['0_convolution.denominator'][0]))
+    ref = _oracle(weights).float().cuda()
+    ref._modules['1_convolution'].denominator.requires_grad_(True)     # as train_denominator would leave it
+    keys = list(ref._modules)
+    out_model = b200nn.substitute(ref, cfg)
+    assert out_model is ref and list(ref._modules) == keys
+    for key, mod in ref._modules.items():
+        assert type(mod).__module__.endswith('sevennet_finetuning_b200.nn'), key
+    sd = ref.state_dict()
+    assert set(sd) == set(weights)
+    for k, v in weights.items():
+        assert np.array_equal(sd[k].cpu().numpy().reshape(-1), np.asarray(v, np.float32).reshape(-1)), k
+    grad = {k: p.requires_grad for k, p in ref.named_parameters()}
+    assert grad['1_convolution.denominator'] and not grad['0_convolution.denominator']
+    ref.eval()
+    ref.set_is_batch_data(False)
+    for name in ('si216.npz', 'hfo2_96.npz'):
+        g = gold(name)
+        data, _, _ = _data(g, torch.device('cuda:0'))
+        out = ref(data)
+        n = len(g['pos'])
+        assert abs(float(out['inferred_total_energy']) - float(g['o64_energy'])) / n <= 1e-6
+        assert np.abs(out['inferred_force'].detach().cpu().numpy() - g['o64_force']).max() <= 1e-5
+        assert np.abs(out['inferred_force'].detach().cpu().numpy() - g['ref_force']).max() <= 4e-5
+        s = out['inferred_stress'].detach().cpu().numpy()
+        assert np.abs(s - g['o64_stress']).max() <= 1e-4 * np.abs(g['o64_stress']).max()
