@@ -39,7 +39,7 @@ namespace pairk {
 #define B200_PAIR_FWD_MINB 3
 #endif
 #ifndef B200_PAIR_BWD_MINB
-#define B200_PAIR_BWD_MINB 2
+#define B200_PAIR_BWD_MINB 3
 #endif
 constexpr int kFwdUnroll = B200_PAIR_FWD_UNROLL, kBwdUnroll = B200_PAIR_BWD_UNROLL;   // the two edges of a pair: unrolled or looped
 constexpr int TE = B200_PAIR_TE;          // edges per chunk (even, <= 8)
@@ -380,10 +380,11 @@ struct Args {
 // which parts of a source row a warp needs: its share of the 0e block and its main block (1e for warp A, 2e for warp B)
 template <int WARP> struct Seg {
   int n0, g0, nM, gM, xw;
-  __device__ __host__ explicit Seg(const ConvDesc& d) {
-    n0 = WARP == 0 ? (d.m0 < 64 ? d.m0 : 64) : (d.m0 > 64 ? d.m0 - 64 : 0);
+  // main / r0: the warp works on its main block / on its share of the 0e block (a launch may do only one of them)
+  __device__ __host__ Seg(const ConvDesc& d, bool main, bool r0) {
+    n0 = !r0 ? 0 : (WARP == 0 ? (d.m0 < 64 ? d.m0 : 64) : (d.m0 > 64 ? d.m0 - 64 : 0));
     g0 = WARP * 64;
-    nM = WARP == 0 ? 3 * d.m1 : 5 * d.m2;
+    nM = !main ? 0 : (WARP == 0 ? 3 * d.m1 : 5 * d.m2);
     gM = WARP == 0 ? d.m0 : d.m0 + 3 * d.m1;
     xw = n0 + nM;
   }
@@ -449,7 +450,7 @@ __device__ __forceinline__ void stage_load(const float* __restrict__ Y, const fl
     in.r = __ldg(len + c0 + k);
   }
 }
-template <int WARP, int LOUT>
+template <int WARP, int LOUT, bool MAIN>
 __device__ __forceinline__ void stage_store(const WarpSmem<WARP>& sm, const Tab& tb, int lane, const StageIn& in) {
   constexpr int REC = WarpSmem<WARP>::REC;
   const int k = lane >> 2, j = lane & 3;
@@ -462,7 +463,7 @@ __device__ __forceinline__ void stage_store(const WarpSmem<WARP>& sm, const Tab&
     sm.ti[k] = ti;
     sm.tt[k] = fmaf(in.r, tb.inv_h, -(float)ti);
   }
-  if constexpr (LOUT == 2) {
+  if constexpr (LOUT == 2 && MAIN) {
     if constexpr (WARP == 0) {
       if (j == 0) cg_M<P111>(in.Y, r + PT<P111>::OFF);
       else if (j == 1) cg_M<P112>(in.Y, r + PT<P112>::OFF);
@@ -494,23 +495,24 @@ template <int WARP> struct LaneMap {
 };
 
 // ---- forward ---------------------------------------------------------------------------------------------------
-// MAIN: the row has 1e / 2e input channels (false: 0e only, the first layer)
-template <int WARP, int LOUT, bool MAIN>
+// MAIN: the warp works on its 1e / 2e block; R0: on its share of the 0e block.  Separate launches for the two keep the
+// register count (accumulators of one role only) and the loop body small: twice the resident warps.
+template <int WARP, int LOUT, bool MAIN, bool R0>
 __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsigned char* smem_base, int row, int lane) {
   constexpr int MR = WARP == 0 ? 1 : 2;   // main role of the warp
   constexpr int D1 = 2 * MR + 1;
   constexpr int REC = WarpSmem<WARP>::REC;
   using LM = typename RolePaths<MR, LOUT>::L;
   using L0 = typename RolePaths<0, LOUT>::L;
-  const Seg<WARP> sg(d);
+  const Seg<WARP> sg(d, MAIN, R0);
   const WarpSmem<WARP> sm(smem_base);
   const LaneMap<WARP> lm(d, lane);
   const int e0 = __ldg(a.rowptr + row), e1 = __ldg(a.rowptr + row + 1);
-  f2 accM[MAIN ? LM::NACC : 1], acc0[L0::NACC];
+  f2 accM[MAIN ? LM::NACC : 1], acc0[R0 ? L0::NACC : 1];
 #pragma unroll
   for (int c = 0; c < (MAIN ? LM::NACC : 1); ++c) accM[c] = B200_ZERO2;
 #pragma unroll
-  for (int c = 0; c < L0::NACC; ++c) acc0[c] = B200_ZERO2;
+  for (int c = 0; c < (R0 ? L0::NACC : 1); ++c) acc0[c] = B200_ZERO2;
 
   if (lane == 0) {
     tc::mbar_init(sm.bar, 1);
@@ -526,7 +528,7 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
     issue_x<WARP>(sg, a.x, d.xdim, s, ne, lane, sm.xbuf, sm.bar, sm.sidx);
     StageIn in;
     stage_load(a.Y, a.len, e0, ne, lane, in);
-    stage_store<WARP, LOUT>(sm, a.tab, lane, in);
+    stage_store<WARP, LOUT, MAIN>(sm, a.tab, lane, in);
     __syncwarp();
   }
   int s_next = (nchunk > 1 && lane < TE && e0 + TE + lane < e1) ? __ldg(a.src + e0 + TE + lane) : 0;
@@ -543,6 +545,8 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
     tc::mbar_wait(sm.bar + cur, (phase >> cur) & 1u);
     phase ^= 1u << cur;
     const float* xb = sm.xbuf + cur * TE * sg.xw;
+    // (Loading an edge's table entries one edge ahead into a second register set was tried: slower, 18.2 -> 20.4 ms forward
+    // and 38.3 -> 42.6 ms reverse per step - the kernels are bound by L2 throughput of the table reads, not by their latency.)
 #pragma unroll 1
     for (int kk = 0; kk < ne; kk += 2) {   // pairs of edges; a zero record / zero row stands behind an odd end
       if constexpr (MAIN) {
@@ -558,19 +562,21 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
           LM::fwd(sm.rec + k * REC, X, e, t, st, accM);
         }
       }
+      if constexpr (R0) {
 #pragma unroll kFwdUnroll
-      for (int s2 = 0; s2 < 2; ++s2) {
-        const int k = kk + s2;
-        const float t = sm.tt[k], st = t * (1.0f / kTabCDScale);
-        TabEntry e[L0::NP];
-        L0::template load_tab<false>(d, a.tab, sm.ti[k], lm.q0, e);
-        f2 X[1];
-        load_x_pair<1>(xb + k * sg.xw, lm.l0, X);
-        L0::fwd(sm.rec + k * REC, X, e, t, st, acc0);
+        for (int s2 = 0; s2 < 2; ++s2) {
+          const int k = kk + s2;
+          const float t = sm.tt[k], st = t * (1.0f / kTabCDScale);
+          TabEntry e[L0::NP];
+          L0::template load_tab<false>(d, a.tab, sm.ti[k], lm.q0, e);
+          f2 X[1];
+          load_x_pair<1>(xb + k * sg.xw, lm.l0, X);
+          L0::fwd(sm.rec + k * REC, X, e, t, st, acc0);
+        }
       }
     }
     __syncwarp();
-    if (ne_next > 0) stage_store<WARP, LOUT>(sm, a.tab, lane, in);
+    if (ne_next > 0) stage_store<WARP, LOUT, MAIN>(sm, a.tab, lane, in);
     __syncwarp();
   }
   float* orow = a.out + (size_t)row * d.odim;
@@ -583,20 +589,22 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
     }
     if (lm.actM && lm.half == 0) LM::store_o(d, orow, lm.qM, a.scale, accM);
   }
-  if (lm.act0) L0::store_o(d, orow, lm.q0, a.scale, acc0);
+  if constexpr (R0) {
+    if (lm.act0) L0::store_o(d, orow, lm.q0, a.scale, acc0);
+  }
 }
 
 // One kernel per warp type: all warps of a launch run the same loop, which then fits the instruction cache (with both
 // types in one kernel 30 % of the issue slots were lost to instruction fetch, ncu stall_no_inst).  Warp w of a CTA owns
 // destination row blockIdx.x * WPC + w and its own slice of the dynamic shared memory.
 constexpr int WPC = 4;
-template <int WT, int LOUT, bool MAIN>
-__global__ void __launch_bounds__(32 * WPC, B200_PAIR_FWD_MINB) conv_pair_fwd_kernel(ConvDesc d, Args a, int n_dst) {
+template <int WT, int LOUT, bool MAIN, bool R0>
+__global__ void __launch_bounds__(32 * WPC, (MAIN ? B200_PAIR_FWD_MINB : 6)) conv_pair_fwd_kernel(ConvDesc d, Args a, int n_dst) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * WPC + warp;
   if (row >= n_dst) return;
-  fwd_warp<WT, LOUT, MAIN>(d, a, smem + warp * WarpSmem<WT>::bytes(Seg<WT>(d).xw), row, lane);
+  fwd_warp<WT, LOUT, MAIN, R0>(d, a, smem + warp * WarpSmem<WT>::bytes(Seg<WT>(d, MAIN, R0).xw), row, lane);
 }
 
 // ---- reverse pass ------------------------------------------------------------------------------------------------
@@ -632,23 +640,23 @@ __device__ __forceinline__ void warp_reduce16(float* v, float& r0, float r1, int
   for (int o = 8; o > 0; o >>= 1) r0 += __shfl_xor_sync(0xffffffffu, r0, o);
 }
 
-template <int WARP, int LOUT, bool MAIN, bool DX>
+template <int WARP, int LOUT, bool MAIN, bool R0, bool DX>
 __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsigned char* smem_base, int row, int lane) {
   constexpr int MR = WARP == 0 ? 1 : 2;
   constexpr int D1 = 2 * MR + 1;
   constexpr int REC = WarpSmem<WARP>::REC;
   using LM = typename RolePaths<MR, LOUT>::L;
   using L0 = typename RolePaths<0, LOUT>::L;
-  const Seg<WARP> sg(d);
+  const Seg<WARP> sg(d, MAIN, R0);
   const WarpSmem<WARP> sm(smem_base);
   const LaneMap<WARP> lm(d, lane);
   const int e0 = __ldg(a.rowptr + row), e1 = __ldg(a.rowptr + row + 1);
   // output gradient of the row; idle lanes hold zeros, so everything they compute (linear in g) vanishes
-  f2 gM[MAIN ? LM::NACC : 1], g0[L0::NACC];
+  f2 gM[MAIN ? LM::NACC : 1], g0[R0 ? L0::NACC : 1];
   {
     const float* grow = a.gout + (size_t)row * d.odim;
     if constexpr (MAIN) LM::load_g(d, grow, lm.qM, lm.actM ? a.scale : 0.f, gM);
-    L0::load_g(d, grow, lm.q0, lm.act0 ? a.scale : 0.f, g0);
+    if constexpr (R0) L0::load_g(d, grow, lm.q0, lm.act0 ? a.scale : 0.f, g0);
   }
   if (lane == 0) {
     tc::mbar_init(sm.bar, 1);
@@ -664,7 +672,7 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
     issue_x<WARP>(sg, a.x, d.xdim, s, ne, lane, sm.xbuf, sm.bar, sm.sidx);
     StageIn in;
     stage_load(a.Y, a.len, e0, ne, lane, in);
-    stage_store<WARP, LOUT>(sm, a.tab, lane, in);
+    stage_store<WARP, LOUT, MAIN>(sm, a.tab, lane, in);
     __syncwarp();
   }
   int s_next = (nchunk > 1 && lane < TE && e0 + TE + lane < e1) ? __ldg(a.src + e0 + TE + lane) : 0;
@@ -726,6 +734,7 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
           }
         }
       }
+      if constexpr (R0) {
 #pragma unroll kBwdUnroll
       for (int s2 = 0; s2 < 2; ++s2) {
         const int k = kk + s2;
@@ -752,9 +761,10 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
         if (s2 == 0) r0 += hsum(drp);
         else r1 += hsum(drp);
       }
+      }
       warp_reduce16(v, r0, r1, lane);
       const float tot_r = r0 * a.tab.inv_h;   // d t / d r = 1 / h
-      if ((lane & 1) == 0) {
+      if ((MAIN || LOUT == 2) && (lane & 1) == 0) {
         const int idx = lane >> 1, ke = kk + (idx >> 3), m = idx & 7;
         if (ke < ne) atomicAdd(a.dY + (size_t)(c0 + ke) * 9 + 1 + m, v[0]);
       }
@@ -764,18 +774,18 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
       }
     }
     __syncwarp();
-    if (ne_next > 0) stage_store<WARP, LOUT>(sm, a.tab, lane, in);
+    if (ne_next > 0) stage_store<WARP, LOUT, MAIN>(sm, a.tab, lane, in);
     __syncwarp();
   }
 }
 
-template <int WT, int LOUT, bool MAIN, bool DX>
-__global__ void __launch_bounds__(32 * WPC, B200_PAIR_BWD_MINB) conv_pair_bwd_kernel(ConvDesc d, Args a, int n_dst) {
+template <int WT, int LOUT, bool MAIN, bool R0, bool DX>
+__global__ void __launch_bounds__(32 * WPC, (MAIN ? B200_PAIR_BWD_MINB : 4)) conv_pair_bwd_kernel(ConvDesc d, Args a, int n_dst) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * WPC + warp;
   if (row >= n_dst) return;
-  bwd_warp<WT, LOUT, MAIN, DX>(d, a, smem + warp * WarpSmem<WT>::bytes(Seg<WT>(d).xw), row, lane);
+  bwd_warp<WT, LOUT, MAIN, R0, DX>(d, a, smem + warp * WarpSmem<WT>::bytes(Seg<WT>(d, MAIN, R0).xw), row, lane);
 }
 
 }  // namespace pairk
@@ -796,8 +806,8 @@ int conv_pair_interleave(const ConvDesc& d, long long n_rows, float* x, int inve
   return check_launch("conv_pair_interleave");
 }
 
-template <int WT> static size_t pair_smem_bytes(const ConvDesc& d) {
-  return pairk::WPC * pairk::WarpSmem<WT>::bytes(pairk::Seg<WT>(d).xw);
+template <int WT> static size_t pair_smem_bytes(const ConvDesc& d, bool main, bool r0) {
+  return pairk::WPC * pairk::WarpSmem<WT>::bytes(pairk::Seg<WT>(d, main, r0).xw);
 }
 
 static pairk::Tab make_tab(const ConvDesc& d, const void* packed, float inv_h, int n_grid) {
@@ -811,8 +821,9 @@ static pairk::Tab make_tab(const ConvDesc& d, const void* packed, float inv_h, i
   return t;
 }
 
-template <int WT, class K> static int launch_pair(K kernel, const ConvDesc& d, const pairk::Args& a, int n_dst, cudaStream_t st) {
-  const size_t sm = pair_smem_bytes<WT>(d);
+template <int WT, class K>
+static int launch_pair(K kernel, const ConvDesc& d, const pairk::Args& a, int n_dst, bool main, bool r0, cudaStream_t st) {
+  const size_t sm = pair_smem_bytes<WT>(d, main, r0);
   if (sm > 48 * 1024 && cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess) {
     set_error("conv_pair: cannot reserve %zu bytes of shared memory", sm);
     return B200_ERR_CUDA;
@@ -820,11 +831,16 @@ template <int WT, class K> static int launch_pair(K kernel, const ConvDesc& d, c
   kernel<<<(n_dst + pairk::WPC - 1) / pairk::WPC, 32 * pairk::WPC, sm, st>>>(d, a, n_dst);
   return B200_OK;
 }
-// both warp types, one launch each
-#define B200_PAIR_BOTH(KERNEL, ...)                                                     \
-  do {                                                                                  \
-    rc = launch_pair<0>(pairk::KERNEL<0, __VA_ARGS__>, d, a, n_dst, st);                \
-    if (rc == B200_OK) rc = launch_pair<1>(pairk::KERNEL<1, __VA_ARGS__>, d, a, n_dst, st); \
+// one launch per warp type and role set: the 0e share of both warp types, then (if the row has 1e / 2e channels) the main
+// blocks.  KERNEL<WT, LOUT, MAIN, R0, ...>
+#define B200_PAIR_ROLES(KERNEL, LOUT, ...)                                                                              \
+  do {                                                                                                                  \
+    rc = launch_pair<0>(pairk::KERNEL<0, LOUT, false, true __VA_ARGS__>, d, a, n_dst, false, true, st);                 \
+    if (rc == B200_OK) rc = launch_pair<1>(pairk::KERNEL<1, LOUT, false, true __VA_ARGS__>, d, a, n_dst, false, true, st); \
+    if (rc == B200_OK && main)                                                                                          \
+      rc = launch_pair<0>(pairk::KERNEL<0, LOUT, true, false __VA_ARGS__>, d, a, n_dst, true, false, st);               \
+    if (rc == B200_OK && main)                                                                                          \
+      rc = launch_pair<1>(pairk::KERNEL<1, LOUT, true, false __VA_ARGS__>, d, a, n_dst, true, false, st);               \
   } while (0)
 
 int conv_pair_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
@@ -839,15 +855,10 @@ int conv_pair_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* sr
   a.out = out;
   const bool main = d.m1 > 0;
   int rc;
-  if (d.lout == 2) {
-    if (main) B200_PAIR_BOTH(conv_pair_fwd_kernel, 2, true);
-    else B200_PAIR_BOTH(conv_pair_fwd_kernel, 2, false);
-  } else {
-    if (main) B200_PAIR_BOTH(conv_pair_fwd_kernel, 0, true);
-    else B200_PAIR_BOTH(conv_pair_fwd_kernel, 0, false);
-  }
+  if (d.lout == 2) B200_PAIR_ROLES(conv_pair_fwd_kernel, 2);
+  else B200_PAIR_ROLES(conv_pair_fwd_kernel, 0);
   if (rc != B200_OK) return rc;
-  return check_launch("conv_pair_fwd", 2);
+  return check_launch("conv_pair_fwd", main ? 4 : 2);
 }
 
 int conv_pair_bwd(const ConvDesc& d, int n_dst, int n_src, const int* rowptr, const int* src, const float* x, const float* Y,
@@ -863,18 +874,17 @@ int conv_pair_bwd(const ConvDesc& d, int n_dst, int n_src, const int* rowptr, co
   a.gout = gout; a.dY = dY; a.dr = dr; a.dx = dx;
   const bool main = d.m1 > 0;
   int rc;
-#define B200_PAIR_BWD(LOUT)                                                        \
-  do {                                                                             \
-    if (main && dx) B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, true, true);        \
-    else if (main) B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, true, false);        \
-    else if (dx) B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, false, true);          \
-    else B200_PAIR_BOTH(conv_pair_bwd_kernel, LOUT, false, false);                 \
-  } while (0)
-  if (d.lout == 2) B200_PAIR_BWD(2);
-  else B200_PAIR_BWD(0);
-#undef B200_PAIR_BWD
+#define B200_COMMA ,
+  if (d.lout == 2) {
+    if (dx) B200_PAIR_ROLES(conv_pair_bwd_kernel, 2, B200_COMMA true);
+    else B200_PAIR_ROLES(conv_pair_bwd_kernel, 2, B200_COMMA false);
+  } else {
+    if (dx) B200_PAIR_ROLES(conv_pair_bwd_kernel, 0, B200_COMMA true);
+    else B200_PAIR_ROLES(conv_pair_bwd_kernel, 0, B200_COMMA false);
+  }
+#undef B200_COMMA
   if (rc != B200_OK) return rc;
-  return check_launch("conv_pair_bwd", 2);
+  return check_launch("conv_pair_bwd", main ? 4 : 2);
 }
 
 }  // namespace b200
