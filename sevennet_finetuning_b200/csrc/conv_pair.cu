@@ -327,45 +327,51 @@ template <> struct RolePaths<0, 0> { using L = PL<P000>; };
 template <> struct RolePaths<1, 0> { using L = PL<P110>; };
 template <> struct RolePaths<2, 0> { using L = PL<P220>; };
 
-// Source rows reach these kernels PAIR-INTERLEAVED: inside every l > 0 block the two channels of a pair are stored
-// [m][channel % 2] instead of [channel % 2][m] (a 2 x (2l+1) transpose inside each group of 2 (2l+1) floats, done in place
-// by pair_interleave_kernel once per layer), so X[m] = (channel 2q, channel 2q+1) is one aligned 8-byte shared-memory
-// load and one red.global.add.v2.f32 of the gradient, with no register shuffling.
-template <int D1> __device__ __forceinline__ void load_x_pair(const float* blk, int q, f2* X) {
-  const f2* r = reinterpret_cast<const f2*>(blk + 2 * q * D1);
+// Source rows reach these kernels COMPONENT-MAJOR: inside every l > 0 block the layout is [m][channel] instead of the
+// reference's [channel][m] (a transpose inside the block, done in place by block_transpose_kernel once per layer and
+// direction).  X[m] = (channel 2q, channel 2q+1) is then one aligned 8-byte shared-memory load, conflict-free across the
+// lanes, and the gradient of a component goes out as ONE red.global.add.v2.f32 per lane to 256 contiguous bytes per warp.
+// (With [channel][m] rows the 32 lanes of a RED touched 24-40 sectors for 8 useful ones, and an L2 slice retires RED
+// sectors at half the rate of reads: ncu, 40 % of the reverse pass's L2 time went into them.)
+template <int D1> __device__ __forceinline__ void load_x_pair(const float* blk, int mul, int q, f2* X) {
 #pragma unroll
-  for (int a = 0; a < D1; ++a) X[a] = r[a];
+  for (int a = 0; a < D1; ++a) X[a] = *reinterpret_cast<const f2*>(blk + a * mul + 2 * q);
 }
-template <int D1> __device__ __forceinline__ void red_x_pair(float* blk, int q, const f2* dx) {
-  float* r = blk + 2 * q * D1;
+template <int D1> __device__ __forceinline__ void red_x_pair(float* blk, int mul, int q, const f2* dx) {
 #pragma unroll
   for (int a = 0; a < D1; ++a)
-    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(r + 2 * a), "f"(lo(dx[a])), "f"(hi(dx[a])) : "memory");
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(blk + a * mul + 2 * q), "f"(lo(dx[a])), "f"(hi(dx[a]))
+                 : "memory");
 }
 
-// in-place [2][D] <-> [D][2] transpose of every channel-pair group of the 1e and 2e blocks of n rows
-__global__ void pair_interleave_kernel(float* __restrict__ x, long long n, int xdim, int m0, int m1, int m2, int inverse) {
-  const int g1 = m1 / 2, g2 = m2 / 2, gpr = g1 + g2;   // groups per row
-  const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (id >= n * gpr) return;
-  const long long row = id / gpr;
-  const int g = (int)(id % gpr);
-  const int D = g < g1 ? 3 : 5;
-  float* p = x + row * xdim + (g < g1 ? m0 + 6 * g : m0 + 3 * m1 + 10 * (g - g1));
-  float v[10];
-  for (int i = 0; i < 2 * D; ++i) v[i] = p[i];
-  for (int c = 0; c < 2; ++c)
-    for (int a = 0; a < D; ++a) {
-      if (inverse) p[c * D + a] = v[2 * a + c];
-      else p[2 * a + c] = v[c * D + a];
+// in-place [channel][m] <-> [m][channel] transpose of the 1e and 2e blocks of every row; one CTA per row
+__global__ void block_transpose_kernel(float* __restrict__ x, int xdim, int m0, int m1, int m2, int inverse) {
+  extern __shared__ float row_s[];
+  float* r = x + (size_t)blockIdx.x * xdim;
+  const int n = 3 * m1 + 5 * m2;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) row_s[i] = r[m0 + i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    // i indexes the OUTPUT; find the input element
+    const bool first = i < 3 * m1;
+    const int D = first ? 3 : 5, mul = first ? m1 : m2, off = first ? 0 : 3 * m1, j = i - off;
+    int src;
+    if (!inverse) {   // output [m][channel] <- input [channel][m]
+      const int a = j / mul, u = j - a * mul;
+      src = u * D + a;
+    } else {          // output [channel][m] <- input [m][channel]
+      const int u = j / D, a = j - u * D;
+      src = a * mul + u;
     }
+    r[m0 + i] = row_s[off + src];
+  }
 }
 
 // ---- per-warp machinery ------------------------------------------------------------------------------------
 struct Args {
   const int* rowptr;
   const int* src;
-  const float* x;     // [n_src, xdim], pair-interleaved (see above)
+  const float* x;     // [n_src, xdim], component-major blocks (see above)
   const float* Y;
   const float* len;
   Tab tab;
@@ -374,7 +380,7 @@ struct Args {
   const float* gout;  // reverse: d E / d out
   float* dY;          // reverse: [E, 9], added into
   float* dr;          // reverse: [E], added into
-  float* dx;          // reverse: [n_src, xdim] pair-interleaved, added into (zeroed by the launcher); nullptr: not needed
+  float* dx;          // reverse: [n_src, xdim] component-major blocks, added into (zeroed by the launcher); nullptr: not needed
 };
 
 // which parts of a source row a warp needs: its share of the 0e block and its main block (1e for warp A, 2e for warp B)
@@ -558,7 +564,7 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
           TabEntry e[LM::NP];
           LM::template load_tab<false>(d, a.tab, sm.ti[k], lm.qM, e);
           f2 X[D1];
-          load_x_pair<D1>(xb + k * sg.xw + sg.n0, lm.qM, X);
+          load_x_pair<D1>(xb + k * sg.xw + sg.n0, WARP == 0 ? d.m1 : d.m2, lm.qM, X);
           LM::fwd(sm.rec + k * REC, X, e, t, st, accM);
         }
       }
@@ -570,7 +576,7 @@ __device__ __forceinline__ void fwd_warp(const ConvDesc& d, const Args& a, unsig
           TabEntry e[L0::NP];
           L0::template load_tab<false>(d, a.tab, sm.ti[k], lm.q0, e);
           f2 X[1];
-          load_x_pair<1>(xb + k * sg.xw, lm.l0, X);
+          load_x_pair<1>(xb + k * sg.xw, 0, lm.l0, X);
           L0::fwd(sm.rec + k * REC, X, e, t, st, acc0);
         }
       }
@@ -703,14 +709,14 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
           TabEntry e[LM::NP];
           LM::template load_tab<true>(d, a.tab, sm.ti[k], lm.qM, e);
           f2 X[D1], dxv[D1], dY[9], drp = B200_ZERO2;
-          load_x_pair<D1>(xb + k * sg.xw + sg.n0, lm.qM, X);
+          load_x_pair<D1>(xb + k * sg.xw + sg.n0, WARP == 0 ? d.m1 : d.m2, lm.qM, X);
 #pragma unroll
           for (int b = 0; b < 9; ++b) dY[b] = B200_ZERO2;
 #pragma unroll
           for (int b = 0; b < D1; ++b) dxv[b] = B200_ZERO2;
           LM::template bwd<DX>(sm.rec + k * REC, X, gM, e, t, st, dY, dxv, drp);
           if constexpr (DX) {
-            if (k < ne && lm.actM) red_x_pair<D1>(a.dx + (size_t)sidx[k] * d.xdim + sg.gM, lm.qM, dxv);
+            if (k < ne && lm.actM) red_x_pair<D1>(a.dx + (size_t)sidx[k] * d.xdim + sg.gM, WARP == 0 ? d.m1 : d.m2, lm.qM, dxv);
           }
           if constexpr (WARP == 0) {
 #pragma unroll
@@ -742,13 +748,13 @@ __device__ __forceinline__ void bwd_warp(const ConvDesc& d, const Args& a, unsig
         TabEntry e[L0::NP];
         L0::template load_tab<true>(d, a.tab, sm.ti[k], lm.q0, e);
         f2 X[1], dxv[1], dY[9], drp = B200_ZERO2;
-        load_x_pair<1>(xb + k * sg.xw, lm.l0, X);
+        load_x_pair<1>(xb + k * sg.xw, 0, lm.l0, X);
 #pragma unroll
         for (int b = 0; b < 9; ++b) dY[b] = B200_ZERO2;
         dxv[0] = B200_ZERO2;
         L0::template bwd<DX>(sm.rec + k * REC, X, g0, e, t, st, dY, dxv, drp);
         if constexpr (DX) {
-          if (k < ne && lm.act0) red_x_pair<1>(a.dx + (size_t)sidx[k] * d.xdim + sg.g0, lm.l0, dxv);
+          if (k < ne && lm.act0) red_x_pair<1>(a.dx + (size_t)sidx[k] * d.xdim + sg.g0, 0, lm.l0, dxv);
         }
         if constexpr (LOUT == 2) {
 #pragma unroll
@@ -798,11 +804,11 @@ bool conv_pair_supported(const ConvDesc& d) {
          d.m1 % 4 == 0 && d.m2 >= 0 && d.m2 <= 32 && d.m2 % 4 == 0 && main_ok && d.wn % 2 == 0;
 }
 
-// in place: standard irreps-blocked rows <-> the pair-interleaved rows the kernels read (x) and write (d x)
+// in place: standard irreps-blocked rows <-> the component-major rows the kernels read (x) and write (d x)
 int conv_pair_interleave(const ConvDesc& d, long long n_rows, float* x, int inverse, cudaStream_t st) {
-  const long long groups = n_rows * (d.m1 / 2 + d.m2 / 2);
-  if (groups == 0) return B200_OK;
-  pairk::pair_interleave_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, st>>>(x, n_rows, d.xdim, d.m0, d.m1, d.m2, inverse);
+  const int n = 3 * d.m1 + 5 * d.m2;
+  if (n_rows == 0 || n == 0) return B200_OK;
+  pairk::block_transpose_kernel<<<(unsigned)n_rows, 128, n * sizeof(float), st>>>(x, d.xdim, d.m0, d.m1, d.m2, inverse);
   return check_launch("conv_pair_interleave");
 }
 

@@ -87,7 +87,7 @@ struct Layer {
   bool fused;   // radial layer + convolution run as the fused tcgen05 kernels (fused.cu)
   bool table;   // per-edge weights interpolated from the tabulated radial function (radial_table.cu)
   bool tabconv; // ... inside the convolution kernels: neither the weights nor their gradient are materialised
-  bool pair;    // ... by the channel-pair kernels (conv_pair.cu): packed table, pair-interleaved source rows
+  bool pair;    // ... by the channel-pair kernels (conv_pair.cu): packed table, component-major source rows
 };
 
 }  // namespace b200
@@ -409,7 +409,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     // layer 0: ghost rows are recomputed from their types (model_build.py:134-172 "ghost_" modules);
     // later layers: the owners' rows are fetched through the halo hook
     OP(CAT_NODE, irreps_linear(L.si1, t == 0 ? NA : N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
-    // the channel-pair kernels read pair-interleaved rows; ghost rows arrive from their owners already interleaved
+    // the channel-pair kernels read component-major rows; ghost rows arrive from their owners already transposed
     if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, t == 0 ? NA : N, b.xs[t], 0, st));
     if (t > 0) HALO(B200_HALO_FWD_X, t, b.xs[t], L.conv.xdim);
     const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
