@@ -60,7 +60,7 @@ int b200_edge_embed_dk(const EdgeParams* p, int64_t n_edges, const float* edge_v
 int b200_edge_embed_bwd2(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* bessel_coeffs,
                          const float* d_edge_attr, const float* d_edge_embedding, const float* a, float* d_edge_vec,
                          float* d_d_edge_attr, float* d_d_edge_embedding, float* d_coeffs, void* stream);
-/* same with dE/d|edge_vec| given directly (d_r[E], from b200_fused_conv_bwd) instead of d edge_embedding */
+/* same with dE/d|edge_vec| given directly (d_r[E], from the table-reading convolution kernels) instead of d edge_embedding */
 int b200_edge_embed_bwd_r(const EdgeParams* p, int64_t n_edges, const float* edge_vec, const float* d_edge_attr,
                           const float* d_r, float* d_edge_vec, void* stream);
 
@@ -115,25 +115,6 @@ int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* 
                     const int32_t* dst, const float* d_out, const float* edge_attr, const float* weight,
                     float denominator, float* d_x, void* stream);
 
-/* ---- fused convolution (same reference lines, convolution.py:97-121): the radial MLP's last layer runs on the
- *      tensor cores inside the convolution kernels and the per-edge weights [E, weight_numel] never reach HBM.
- *      Edges sorted by dst (= edge_index[0]); `radial` is the buffer b200_fused_radial fills once per layer and
- *      graph (hidden activations of weight_nn and their d/dr tangents, b200_fused_radial_bytes(E) bytes).
- *      Forward:  out[n_dst, out_dim] (zeroed inside) = scatter_sum(TP(x[src], Y, weight_nn(r))) / denominator.
- *      Backward: d_x[n_src, x_dim] (zeroed inside; NULL = not wanted), d_Y[E,9] (component 0 untouched) and d_r[E] = dE/d|edge_vec|
- *      through the radial MLP (accumulate=1 adds to d_Y, d_r).  Needs multiplicities that are multiples of 32
- *      (<= 128x0e, 64x1e, 32x2e) and a [nb<=16, 64, 64, wn] weight_nn: b200_fused_supported() tells. */
-int b200_fused_supported(int m0, int m1, int m2, int lout, const MlpDesc* mlp);
-size_t b200_fused_radial_bytes(int64_t n_edges);
-int b200_fused_radial(const EdgeParams* p, const MlpDesc* mlp, int64_t n_edges, const float* edge_vec,
-                      const float* bessel_coeffs, const float* W0, const float* W1, float* radial, void* stream);
-int b200_fused_conv_fwd(int m0, int m1, int m2, int lout, int n_dst, int64_t n_edges, const int32_t* dst,
-                        const int32_t* src, const float* x, const float* edge_attr, const float* radial, const float* W2,
-                        float denominator, float* out, void* stream);
-int b200_fused_conv_bwd(int m0, int m1, int m2, int lout, int n_src, int64_t n_edges, const int32_t* dst,
-                        const int32_t* src, const float* x, const float* edge_attr, const float* radial, const float* W2,
-                        const float* d_out, float denominator, float* d_x, float* d_edge_attr, float* d_r, int accumulate,
-                        void* stream);
 
 /* ---- per-node irreps linear: sevenn/nn/linear.py:46-49 (IrrepsLinear -> e3nn o3.Linear), also
  *      sevenn/nn/self_connection.py:60-62 (SelfConnectionLinearIntro) ------------------------------- */

@@ -58,11 +58,6 @@ SIGNATURES = {
     'b200_radial_table_build': (_i, [_P(EdgeParams), _P(MlpDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_radial_table_fwd': (_i, [_P(EdgeParams), _P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp]),
     'b200_radial_table_bwd': (_i, [_P(EdgeParams), _P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
-    'b200_fused_supported': (_i, [_i, _i, _i, _i, _P(MlpDesc)]),
-    'b200_fused_radial_bytes': (_sz, [_i64]),
-    'b200_fused_radial': (_i, [_P(EdgeParams), _P(MlpDesc), _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
-    'b200_fused_conv_fwd': (_i, [_i, _i, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp]),
-    'b200_fused_conv_bwd': (_i, [_i, _i, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _i, _vp]),
     'b200_conv_dims': (_i, [_i, _i, _i, _i, _P(_i), _P(_i)]),
     'b200_conv_fwd': (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp]),
     'b200_conv_bwd_edge': (_i, [_i, _i, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _i, _vp]),

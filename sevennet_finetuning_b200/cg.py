@@ -178,83 +178,9 @@ def generate_header():
     return '\n'.join(out)
 
 
-def generate_direct_header():
-    """Per-path straight-line code that contracts the sparse coupling table directly (no per-edge coupling
-    matrix in shared memory): used by the fused convolution kernels (csrc/fused.cu), where one thread owns one
-    (path, channel) pair.  Y[0] is the constant 1 of the component-normalised l=0 harmonic."""
-    out = ['// GENERATED by `python -m sevennet_finetuning_b200.cg` - do not edit.',
-           '// Direct sparse contractions with C[m1,m2,m3]*sqrt(2 l3+1); Y is the 9-vector of an edge.',
-           '//   fwd : acc[c] += sum_ab C[a,b,c] X[a] Y[b]        (X = weight * x)',
-           '//   tvec: T[b]    = sum_ac C[a,b,c] x[a] g[c]        (d weight = sum_b Y[b] T[b]; dY[b] += w T[b])',
-           '//   dxv : dx[a]   = sum_bc C[a,b,c] Y[b] g[c]        (caller scales by the weight)',
-           '#pragma once', '', 'template <int PID> struct CgD;', '']
-    yoff = (0, 1, 4)
-    for (l1, l2, l3) in ALL_PATHS:
-        C = coupling(l1, l2, l3)
-        d1, d2, d3 = C.shape
-        tag = f'{l1}{l2}{l3}'
-        yo = yoff[l2]
-
-        def yterm(b):
-            return None if l2 == 0 else f'Y[{yo + b}]'
-
-        out.append(f'template <> struct CgD<P{tag}> {{')
-        out.append(f'  static constexpr int L1 = {l1}, L2 = {l2}, L3 = {l3}, D1 = {d1}, D2 = {d2}, D3 = {d3}, YO = {yo};')
-        # ---- fwd
-        out.append('  __device__ __forceinline__ static void fwd(const float* X, const float* Y, float* acc) {')
-        prods = {}
-        for a in range(d1):
-            for b in range(d2):
-                if np.abs(C[a, b, :]).max() > 1e-9:
-                    name = f'q{a}{b}'
-                    prods[(a, b)] = name
-                    yt = yterm(b)
-                    out.append(f'    const float {name} = X[{a}]{" * " + yt if yt else ""};')
-        for c in range(d3):
-            for a in range(d1):
-                for b in range(d2):
-                    if abs(C[a, b, c]) > 1e-9:
-                        out.append(f'    acc[{c}] = fmaf({_fmt(C[a, b, c])}, {prods[(a, b)]}, acc[{c}]);')
-        out.append('  }')
-        # ---- tvec
-        out.append('  __device__ __forceinline__ static void tvec(const float* x, const float* g, float* T) {')
-        prods = {}
-        for a in range(d1):
-            for c in range(d3):
-                if np.abs(C[a, :, c]).max() > 1e-9:
-                    prods[(a, c)] = f'p{a}{c}'
-                    out.append(f'    const float p{a}{c} = x[{a}] * g[{c}];')
-        for b in range(d2):
-            terms = [(C[a, b, c], prods[(a, c)]) for a in range(d1) for c in range(d3) if abs(C[a, b, c]) > 1e-9]
-            expr = '0.0f'
-            for k, (cv, nm) in enumerate(terms):
-                expr = f'{_fmt(cv)} * {nm}' if k == 0 else f'fmaf({_fmt(cv)}, {nm}, {expr})'
-            out.append(f'    T[{b}] = {expr};')
-        out.append('  }')
-        # ---- dxv
-        out.append('  __device__ __forceinline__ static void dxv(const float* Y, const float* g, float* dx) {')
-        prods = {}
-        for b in range(d2):
-            for c in range(d3):
-                if np.abs(C[:, b, c]).max() > 1e-9:
-                    prods[(b, c)] = f'r{b}{c}'
-                    yt = yterm(b)
-                    out.append(f'    const float r{b}{c} = g[{c}]{" * " + yt if yt else ""};')
-        for a in range(d1):
-            terms = [(C[a, b, c], prods[(b, c)]) for b in range(d2) for c in range(d3) if abs(C[a, b, c]) > 1e-9]
-            expr = '0.0f'
-            for k, (cv, nm) in enumerate(terms):
-                expr = f'{_fmt(cv)} * {nm}' if k == 0 else f'fmaf({_fmt(cv)}, {nm}, {expr})'
-            out.append(f'    dx[{a}] = {expr};')
-        out.append('  }')
-        out.append('};')
-        out.append('')
-    return '\n'.join(out)
-
-
 if __name__ == '__main__':
     here = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'csrc')
-    for name, gen in (('cg_generated.cuh', generate_header), ('cg_direct.cuh', generate_direct_header)):
+    for name, gen in (('cg_generated.cuh', generate_header),):
         with open(os.path.join(here, name), 'w') as f:
             f.write(gen())
         print('wrote', os.path.join(here, name))

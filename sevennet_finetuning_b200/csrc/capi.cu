@@ -186,36 +186,6 @@ int b200_graph_fill(int n, const double* pos, const double* cell_host, const int
   return graph_fill(n, pos, cell_host, pbc_host, cutoff, ws, rowptr, src, dst, shift, edge_vec,
                     (unsigned long long*)tmp_keys, ST(stream));
 }
-int b200_fused_supported(int m0, int m1, int m2, int lout, const MlpDesc* mlp) {
-  if (!mlp || (lout != 0 && lout != 2)) return 0;
-  ConvDesc d;
-  fill_conv_desc(m0, m1, m2, lout, d);
-  return fused_supported(d, *mlp) ? 1 : 0;
-}
-size_t b200_fused_radial_bytes(int64_t E) { return fused_radial_bytes(E); }
-int b200_fused_radial(const EdgeParams* p, const MlpDesc* mlp, int64_t E, const float* vec, const float* coeffs,
-                      const float* W0, const float* W1, float* radial, void* stream) {
-  B200_REQUIRE(p && mlp && coeffs && W0 && W1 && (E == 0 || (vec && radial)), "fused_radial: null argument");
-  return fused_radial(*p, *mlp, E, vec, coeffs, W0, W1, radial, ST(stream));
-}
-int b200_fused_conv_fwd(int m0, int m1, int m2, int lout, int n_dst, int64_t E, const int32_t* dst, const int32_t* src,
-                        const float* x, const float* Y, const float* radial, const float* W2, float denom, float* out,
-                        void* stream) {
-  B200_REQUIRE(lout == 0 || lout == 2, "fused_conv_fwd: lout must be 0 or 2");
-  B200_REQUIRE(W2 && out && (E == 0 || (dst && src && x && Y && radial)), "fused_conv_fwd: null argument");
-  ConvDesc d;
-  fill_conv_desc(m0, m1, m2, lout, d);
-  return fused_conv_fwd(d, n_dst, E, dst, src, x, Y, radial, W2, denom, out, ST(stream));
-}
-int b200_fused_conv_bwd(int m0, int m1, int m2, int lout, int n_src, int64_t E, const int32_t* dst, const int32_t* src,
-                        const float* x, const float* Y, const float* radial, const float* W2, const float* d_out,
-                        float denom, float* d_x, float* d_Y, float* d_r, int accumulate, void* stream) {
-  B200_REQUIRE(lout == 0 || lout == 2, "fused_conv_bwd: lout must be 0 or 2");
-  B200_REQUIRE(W2 && (E == 0 || (dst && src && x && Y && radial && d_out && d_Y && d_r)), "fused_conv_bwd: null argument");
-  ConvDesc d;
-  fill_conv_desc(m0, m1, m2, lout, d);
-  return fused_conv_bwd(d, n_src, E, dst, src, x, Y, radial, W2, d_out, denom, d_x, d_Y, d_r, accumulate, ST(stream));
-}
 size_t b200_transpose_workspace_bytes(int n, int64_t E) { return transpose_workspace_bytes(n, E); }
 int b200_csr_transpose(int n, int64_t E, const int32_t* src, void* ws, int32_t* rrowptr, int32_t* eid, void* stream) {
   B200_REQUIRE(ws && rrowptr, "csr_transpose: null argument");

@@ -84,7 +84,6 @@ struct Layer {
   MlpDesc mlp;
   LinDesc sc, si1, si2;
   int lout;
-  bool fused;   // radial layer + convolution run as the fused tcgen05 kernels (fused.cu)
   bool table;   // per-edge weights interpolated from the tabulated radial function (radial_table.cu)
   bool tabconv; // ... inside the convolution kernels: neither the weights nor their gradient are materialised
   bool pair;    // ... by the channel-pair kernels (conv_pair.cu): packed table, component-major source rows
@@ -182,9 +181,7 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.sc = make_linear(L.in, L.gin);
     L.si1 = make_linear(L.in, L.in);
     L.si2 = make_linear(L.msg, L.gin);
-    const bool fused_env = getenv("B200_FUSED") && atoi(getenv("B200_FUSED")) != 0;   // opt-in
-    L.fused = fused_env && fused_supported(L.conv, L.mlp);
-    L.table = !fused_env && radial_table_supported(L.mlp) && !(getenv("B200_RADIAL_TABLE") && atoi(getenv("B200_RADIAL_TABLE")) == 0);
+    L.table = radial_table_supported(L.mlp) && !(getenv("B200_RADIAL_TABLE") && atoi(getenv("B200_RADIAL_TABLE")) == 0);
     L.tabconv = L.table && !(getenv("B200_TABLE_IN_CONV") && atoi(getenv("B200_TABLE_IN_CONV")) == 0);
     L.pair = L.tabconv && conv_pair_supported(L.conv) && !(getenv("B200_CONV_PAIR") && atoi(getenv("B200_CONV_PAIR")) == 0);
     m->layers.push_back(L);
@@ -259,7 +256,7 @@ struct Plan {
 };
 struct Buffers {
   float *Y, *emb, *len, *dY, *demb, *ddr, *dvec, *dw, *x[2], *conv_out, *g_x[2], *g_gin, *g_conv, *h, *s, *g_h, *g_s, *virial_atom;
-  std::vector<float*> w, xs, gin, rad;
+  std::vector<float*> w, xs, gin;
   int *rrowptr, *eid, *rorder;
   void *tws, *tws2;
 };
@@ -270,7 +267,7 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
     maxx = std::max(maxx, L.conv.xdim);
     maxg = std::max(maxg, L.sc.out_dim);
     maxmsg = std::max(maxmsg, L.conv.odim);
-    if (!L.fused && !L.tabconv) maxwn = std::max(maxwn, L.conv.wn);   // these layers materialise [E, wn] weights and their gradient
+    if (!L.tabconv) maxwn = std::max(maxwn, L.conv.wn);   // these layers materialise [E, wn] weights and their gradient
   }
   maxx = std::max(maxx, m->r1.in_dim);
   const int nb = m->cfg.edge.num_basis;
@@ -292,10 +289,9 @@ void plan_buffers(const B200Model* m, int NL, int NA, long long E, Plan& p, Buff
   b.s = p.take<float>((size_t)N);
   b.g_s = p.take<float>((size_t)N);
   b.virial_atom = p.take<float>((size_t)NA * 6);
-  b.w.clear(); b.xs.clear(); b.gin.clear(); b.rad.clear();
+  b.w.clear(); b.xs.clear(); b.gin.clear();
   for (const Layer& L : m->layers) {
-    b.w.push_back(p.take<float>((L.fused || L.tabconv) ? 0 : (size_t)E * L.conv.wn));
-    b.rad.push_back(reinterpret_cast<float*>(p.take<char>(L.fused ? fused_radial_bytes(E) : 0)));
+    b.w.push_back(p.take<float>(L.tabconv ? 0 : (size_t)E * L.conv.wn));
     b.xs.push_back(p.take<float>((size_t)NA * L.conv.xdim));
     b.gin.push_back(p.take<float>((size_t)N * L.sc.out_dim));
   }
@@ -415,10 +411,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
     const float* W1 = P(m, s + "_convolution.weight_nn.layer1.weight");
     const float* W2 = P(m, s + "_convolution.weight_nn.layer2.weight");
-    if (L.fused) {
-      OP(CAT_MLP_FWD, fused_radial(c.edge, L.mlp, E, edge_vec, coeffs, W0, W1, b.rad[t], st));
-      OP(CAT_CONV_FWD, fused_conv_fwd(L.conv, N, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, denom[t], b.conv_out, st));
-    } else {
+    {
       if (L.pair) {
         const RadialTableGrid tg = radial_table_grid(c.edge);
         OP(CAT_CONV_FWD, conv_pair_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h), tg.n, denom[t],
@@ -471,11 +464,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     const float* W2 = P(m, s + "_convolution.weight_nn.layer2.weight");
     // features entering layer t > 0 depend on the positions through the earlier layers: d x is needed there
     float* dxs = t > 0 ? b.conv_out : nullptr;
-    if (L.fused) {
-      OP(CAT_CONV_BWD_EDGE, fused_conv_bwd(L.conv, NA, E, dst, src, b.xs[t], b.Y, b.rad[t], W2, b.g_conv, denom[t], dxs, b.dY,
-                                           b.ddr, ddr_written ? 1 : 0, st));
-      dy_written = ddr_written = true;
-    } else if (L.pair) {
+    if (L.pair) {
       const RadialTableGrid tg = radial_table_grid(c.edge);
       OP(CAT_CONV_BWD_EDGE, conv_pair_bwd(L.conv, N, NA, rowptr, src, b.xs[t], b.Y, b.len, m->tables[t], (float)(1.0 / tg.h), tg.n,
                                           b.g_conv, denom[t], b.dY, b.ddr, dxs, st));
@@ -491,7 +480,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       OP(CAT_CONV_BWD_EDGE, conv_bwd_edge_x(L.conv, N, NA, (int)E, rowptr, src, b.xs[t], b.Y, b.w[t], b.g_conv, denom[t], b.dw,
                                             b.dY, dy_written ? 1 : 0, m->split_bwd_x ? nullptr : dxs, st));
       dy_written = true;
-      if (L.table) {   // d E / d r directly: joins the per-edge radial gradient of the fused layers (b.ddr)
+      if (L.table) {   // d E / d r directly: joins the per-edge radial gradient of the table-in-convolution layers (b.ddr)
         OP(CAT_MLP_BWD, radial_table_bwd(c.edge, L.mlp, E, b.len, b.rorder, m->tables[t], b.dw, b.ddr, ddr_written ? 1 : 0, st));
         ddr_written = true;
       } else {
@@ -502,7 +491,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     if (t > 0) {
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
       OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
-      if (!L.fused && !L.tabconv && m->split_bwd_x)
+      if (!L.tabconv && m->split_bwd_x)
         OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
       if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, N, b.conv_out, 1, st));   // back to the standard row layout

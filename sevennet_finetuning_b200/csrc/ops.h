@@ -74,16 +74,6 @@ int radial_table_fwd(const EdgeParams& p, const MlpDesc& d, long long E, const f
 int radial_table_bwd(const EdgeParams& p, const MlpDesc& d, long long E, const float* len, const int* order, const float* T,
                      const float* dw, float* dr, int accumulate, cudaStream_t st);
 
-// fused path (fused.cu): radial operand tiles, then convolution forward / backward with the weights kept in TMEM
-bool fused_supported(const ConvDesc& d, const MlpDesc& m);
-size_t fused_radial_bytes(long long E);
-int fused_radial(const EdgeParams& ep, const MlpDesc& m, long long E, const float* vec, const float* coeffs, const float* W0,
-                 const float* W1, float* tiles, cudaStream_t st);
-int fused_conv_fwd(const ConvDesc& d, int n_dst, long long E, const int* dst, const int* src, const float* x, const float* Y,
-                   const float* tiles, const float* W2, float denom, float* out, cudaStream_t st);
-int fused_conv_bwd(const ConvDesc& d, int n_src, long long E, const int* dst, const int* src, const float* x, const float* Y,
-                   const float* tiles, const float* W2, const float* gout, float denom, float* dx, float* dY, float* dr,
-                   int accumulate, cudaStream_t st);
 
 int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
                   cudaStream_t st);

@@ -41,24 +41,6 @@ def test_efs_matches_reference_graph(model, gold, name):
     assert np.abs(s - g['ref_stress']).max() <= 2e-4 * np.abs(g['ref_stress']).max()
 
 
-def test_efs_fused_engine_matches_reference_graph(weights, gold, monkeypatch):
-    """same parity gates with the fused tcgen05 convolution kernels switched on (B200_FUSED=1, csrc/fused.cu)"""
-    if not torch.cuda.is_available():
-        pytest.skip('needs a CUDA device')
-    from sevennet_finetuning_b200.model import B200SevenNet
-    monkeypatch.setenv('B200_FUSED', '1')
-    m = B200SevenNet(state_dict=weights)
-    for name in ('si216.npz', 'hfo2_96.npz'):
-        g = gold(name)
-        out = m.calculate(torch.tensor(g['pos'], dtype=torch.float64, device=m.device), g['cell'], [True] * 3,
-                          torch.tensor(g['types'], dtype=torch.int32, device=m.device))
-        n = len(g['pos'])
-        e, f, s = float(out['energy'].item()), out['forces'].cpu().numpy(), out['stress'].cpu().numpy()
-        assert abs(e - float(g['o64_energy'])) / n <= 1e-6
-        assert np.abs(f - g['o64_force']).max() <= 1e-5
-        assert np.abs(s - g['o64_stress']).max() <= 1e-4 * np.abs(g['o64_stress']).max()
-
-
 def test_full_size_properties(model):
     """C3-like cell at reduced size (20k atoms): size-independent properties - net force is zero,
     energy is invariant under a rigid translation and a permutation of the atoms."""

@@ -279,53 +279,6 @@ FUSED_CASES = [((128, 64, 32), 2, 'mid', 1500), ((128, 0, 0), 2, 'layer0', 700),
                ((64, 32, 32), 2, 'half', 333), ((128, 64, 32), 2, 'one_tile', 64), ((128, 64, 32), 2, 'tail', 129)]
 
 
-@pytest.mark.parametrize('muls,lout,name,E', FUSED_CASES)
-def test_fused_convolution_fwd_bwd(dev, muls, lout, name, E):
-    """fused path (tcgen05 radial layer inside the convolution kernels) against the float64 oracle chain
-    edge_vec -> Bessel x XPLOR -> FullyConnectedNet -> TensorProduct uvu -> scatter / denominator."""
-    from oracle import refnn
-    from sevennet_finetuning_b200 import ops
-    from sevennet_finetuning_b200._lib import EdgeParams
-    rng = np.random.default_rng(7)
-    torch.manual_seed(7)
-    n = 41
-    dst, src, rowptr, vec = _rand_edges(rng, n, E)
-    irx = '+'.join(f'{m}x{l}e' for l, m in enumerate(muls) if m)
-    tp = refnn.TensorProductUVU(irx, '1x0e+1x1e+1x2e', '+'.join(f'1x{l}e' for l in range(lout + 1))).double()
-    wn, od = ops.conv_dims(*muls, lout)
-    assert ops.fused_supported(muls, lout, 8, 64, 64, wn)
-    net = refnn.FullyConnectedNet([8, 64, 64, wn], 'silu').double()
-    coeffs = np.array([0.5079, 1.1099, 1.7265, 2.3767, 3.0392, 3.7201, 4.4142, 5.1186])
-    basis = refnn.BesselBasis(5.0, 8).double()
-    basis.coeffs.data = torch.tensor(coeffs)
-    env = refnn.XPLORCutoff(5.0, 4.5)
-    v64 = torch.tensor(vec, dtype=torch.float64)
-    r = torch.linalg.norm(v64, dim=-1).requires_grad_(True)
-    Y = refnn.SphericalEncoding(2, 1, True)(v64)
-    Yr = Y.clone().requires_grad_(True)
-    x = torch.randn(n, refnn.irreps_dim(tp.irreps_in1), dtype=torch.float64, requires_grad=True)
-    emb = basis(r) * env(r).unsqueeze(-1)
-    w = net(emb)
-    denom = 7.3
-    out = refnn.message_gather(x, torch.tensor(dst), tp(x[torch.tensor(src)], Yr, w)) / denom
-    g = torch.randn_like(out)
-    (out * g).sum().backward()
-    d = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a)).to(dt).to(dev).contiguous()
-    s32, d32 = d(src, torch.int32), d(dst, torch.int32)
-    x32, Y32, g32, v32 = d(x.detach()), d(Y), d(g), d(vec)
-    Ws = [getattr(net, f'layer{k}').weight.detach().float().to(dev).contiguous() for k in range(3)]
-    p = EdgeParams(8, 1, 1, 5.0, 4.5, 6.0)
-    rad = ops.fused_radial(p, v32, d(coeffs), Ws[0], Ws[1])
-    o = ops.fused_conv_fwd(muls, lout, n, d32, s32, x32, Y32, rad, Ws[2], denom)
-    assert _rel(o, out) < 2e-5, name
-    dx, dY, dr = ops.fused_conv_bwd(muls, lout, d32, s32, x32, Y32, rad, Ws[2], g32, denom)
-    assert _rel(dx, x.grad) < 2e-5, name
-    assert _rel(dY[:, 1:], Yr.grad[:, 1:]) < 2e-5, name
-    assert _rel(dr, r.grad) < 2e-5, name
-    dx2, dY2, dr2 = ops.fused_conv_bwd(muls, lout, d32, s32, x32, Y32, rad, Ws[2], g32, denom, dY=dY.clone(), dr=dr.clone())
-    assert _rel(dr2, 2 * r.grad) < 2e-5 and _rel(dY2[:, 1:], 2 * Yr.grad[:, 1:]) < 2e-5, name
-
-
 @pytest.mark.parametrize('cutoff,wn', [('xplor', 960), ('xplor', 224), ('poly', 384)])
 def test_radial_table_matches_float64_mlp(dev, cutoff, wn):
     """Tabulated radial weights (b200_radial_table_*): w(r) and sum_k dw_k dw_k/dr against the float64 oracle chain
