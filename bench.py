@@ -129,52 +129,174 @@ def load_weights():
     return dict(np.load(os.path.join(ROOT, 'tests', 'golden', 'sevennet0_weights.npz')))
 
 
-def reference_cpu_time(n_atoms, steps, warmup, seed=1):
-    """The reference's own PyTorch CPU path: its frozen TorchScript graph on the host cores."""
+def _reference_callable(pos, cell, pbc, types, device='cpu'):
+    """The reference's own implementation of the path: its frozen TorchScript graph (oracle/_ref/deployed_serial.pt,
+    kind 'reference'), else the oracle restatement (kind 'port').  Returns (call, kind); call() -> (E, F, S, n_edges, ei)."""
     from oracle.graph import radius_graph
     path = os.path.join(ROOT, 'oracle', '_ref', 'deployed_serial.pt')
+    if os.path.exists(path):
+        ts = torch.jit.load(path, map_location=device).eval()
+
+        def call():
+            ei, S, D = radius_graph(pos, cell, pbc, 5.0)
+            d = {'x': torch.tensor(types, dtype=torch.long, device=device),
+                 'pos': torch.tensor(pos, dtype=torch.float32, device=device).requires_grad_(True),
+                 'edge_index': torch.tensor(ei, device=device), 'pbc_shift': torch.tensor(S, dtype=torch.float32, device=device),
+                 'cell_lattice_vectors': torch.tensor(cell, dtype=torch.float32, device=device),
+                 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32, device=device),
+                 'num_atoms': torch.tensor(len(pos)), 'batch': torch.zeros(0, dtype=torch.long)}
+            o = ts(d)
+            return (float(o['inferred_total_energy'].detach()), o['inferred_force'].detach().cpu().numpy(),
+                    o['inferred_stress'].detach().cpu().numpy().reshape(-1), ei.shape[1], ei)
+        return call, 'reference'
+    # the restated oracle (port) when the frozen graph did not travel
+    from oracle.refmodel import build_model
+    w = load_weights()
+    m = build_model(dict(shift=w['rescale_atomic_energy.shift'].tolist(), scale=w['rescale_atomic_energy.scale'].tolist(),
+                         conv_denominator=float(w['0_convolution.denominator'][0])))
+    m.load_state_dict({k: torch.tensor(v) for k, v in w.items()})
+    m.eval()
+    m.set_is_batch_data(False)
+
+    def call():
+        ei, S, D = radius_graph(pos, cell, pbc, 5.0)
+        o = m({'x': torch.tensor(types, dtype=torch.long), 'edge_index': torch.tensor(ei),
+               'edge_vec': torch.tensor(D, dtype=torch.float32).requires_grad_(True),
+               'num_atoms': torch.tensor(len(pos)), 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
+               'batch': torch.zeros(0, dtype=torch.long)})
+        return (float(o['inferred_total_energy'].detach()), o['inferred_force'].detach().numpy(),
+                o['inferred_stress'].detach().numpy().reshape(-1), ei.shape[1], ei)
+    return call, 'port'
+
+
+def reference_cpu_time(n_atoms, steps, warmup, seed=1, full_atoms=None):
+    """The reference's own PyTorch CPU path on the host cores, on a bounded SAMPLE of the workload: an n_atoms cell of the
+    same generator; the per-atom rate is what is reported (`extrapolated`: the full-size cell is never run on the CPU)."""
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     pos, cell, pbc, types = make_cell(n_atoms, seed)
-    kind = 'reference'
-    if os.path.exists(path):
-        ts = torch.jit.load(path, map_location='cpu').eval()
-
-        def call():
-            ei, S, D = radius_graph(pos, cell, pbc, 5.0)
-            d = {'x': torch.tensor(types, dtype=torch.long), 'pos': torch.tensor(pos, dtype=torch.float32).requires_grad_(True),
-                 'edge_index': torch.tensor(ei), 'pbc_shift': torch.tensor(S, dtype=torch.float32),
-                 'cell_lattice_vectors': torch.tensor(cell, dtype=torch.float32),
-                 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
-                 'num_atoms': torch.tensor(len(pos)), 'batch': torch.zeros(0, dtype=torch.long)}
-            o = ts(d)
-            return float(o['inferred_total_energy']), ei.shape[1]
-    else:  # the restated oracle (port) when the frozen graph did not travel
-        kind = 'port'
-        from oracle.refmodel import build_model
-        w = load_weights()
-        m = build_model(dict(shift=w['rescale_atomic_energy.shift'].tolist(), scale=w['rescale_atomic_energy.scale'].tolist(),
-                             conv_denominator=float(w['0_convolution.denominator'][0])))
-        m.load_state_dict({k: torch.tensor(v) for k, v in w.items()})
-        m.eval()
-        m.set_is_batch_data(False)
-
-        def call():
-            ei, S, D = radius_graph(pos, cell, pbc, 5.0)
-            o = m({'x': torch.tensor(types, dtype=torch.long), 'edge_index': torch.tensor(ei),
-                   'edge_vec': torch.tensor(D, dtype=torch.float32).requires_grad_(True),
-                   'num_atoms': torch.tensor(len(pos)), 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
-                   'batch': torch.zeros(0, dtype=torch.long)})
-            return float(o['inferred_total_energy']), ei.shape[1]
+    call, kind = _reference_callable(pos, cell, pbc, types)
     for _ in range(warmup):
         call()
     t0 = time.perf_counter()
     for _ in range(steps):
-        _, ne = call()
+        ne = call()[3]
     dt = (time.perf_counter() - t0) / steps
-    return dict(value=n_atoms / dt, unit=UNIT, cores=cores, kind=kind,
-                sample=f'{n_atoms}-atom amorphous cell of the same generator, {ne} edges, {steps} timed calls '
-                       f'({dt:.2f} s/call), graph via the numpy restatement'), dt
+    return dict(value=n_atoms / dt, unit=UNIT, cores=cores, kind=kind, extrapolated=True, sample_atoms=n_atoms, sample_edges=int(ne),
+                full_atoms=full_atoms,
+                sample=f'{n_atoms}-atom amorphous cell of the same generator (NOT the full-size cell: per-atom rate, extrapolated), '
+                       f'{ne} edges, {steps} timed calls ({dt:.2f} s/call), graph via the numpy restatement'), dt
+
+
+def si216_cpu_time(steps=3, warmup=1):
+    """BASELINE config 1 at its full size: Si-216 on the host cores through the same reference graph (not extrapolated)."""
+    from sevennet_finetuning_b200.synthetic import SPECIES_INDEX, si_diamond
+    pos, cell, pbc, sym = si_diamond()
+    types = np.array([SPECIES_INDEX[x] for x in sym], np.int32)
+    torch.set_num_threads(os.cpu_count() or 1)
+    call, kind = _reference_callable(pos, cell, pbc, types)
+    for _ in range(warmup):
+        call()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e, _, _, ne, _ = call()
+    dt = (time.perf_counter() - t0) / steps
+    return dict(config='config 1: Si-216 diamond supercell, full size', value=len(pos) / dt, unit=UNIT, s_per_call=dt, n_edges=int(ne),
+                energy=e, cores=os.cpu_count() or 1, kind=kind, extrapolated=False)
+
+
+def parity_vs_reference(model, n_atoms, seed=1):
+    """The benchmarked workload's generator at the size the reference arm evaluates: CUDA engine against the reference's frozen
+    fp32 graph on the CPU (tolerances of tests/test_gpu_model.py: 1e-6 eV/atom; 4e-5 eV/A relative to max(1, |F|max) against
+    the fp32 graph, which itself sits 1-2e-5 from float64; stress 2e-4 of max|sigma|)."""
+    pos, cell, pbc, types = make_cell(n_atoms, seed)
+    call, kind = _reference_callable(pos, cell, pbc, types)
+    e, f, sg, ne, ei = call()
+    dev = model.device
+    out = model.calculate(torch.tensor(pos, dtype=torch.float64, device=dev), cell, pbc, torch.tensor(types, dtype=torch.int32, device=dev),
+                          sort_atoms=False)
+    same = bool(out['graph']['src'].shape[0] == ne and (out['graph']['src'].cpu().numpy() == ei[1]).all()
+                and (out['graph']['dst'].cpu().numpy() == ei[0]).all())
+    de = abs(float(out['energy'].item()) - e) / n_atoms
+    df = float(np.abs(out['forces'].cpu().numpy() - f).max())
+    fmax = float(np.abs(f).max())
+    ds = float(np.abs(out['stress'].cpu().numpy().reshape(-1) - sg).max() / max(np.abs(sg).max(), 1e-30))
+    ok = bool(same and de <= 1e-6 and df <= 4e-5 * max(1.0, fmax) and ds <= 2e-4)
+    return dict(against=f'{kind}: frozen TorchScript graph, fp32, CPU', n_atoms=n_atoms, n_edges=int(ne), edge_set_equal=same,
+                dE_per_atom=de, max_dF=df, max_F=fmax, rel_dS=ds, within_tolerance=ok)
+
+
+def parity_parallel(model, par, dev, n_atoms=20000):
+    """N > 1: the decomposed call over NCCL against the single-GPU engine on the same cell (every rank evaluates the whole
+    cell alone and compares its own atoms); max over ranks."""
+    import torch.distributed as dist
+    pos, cell, pbc, types = make_cell(n_atoms, seed=2)
+    pos_d = torch.tensor(pos, dtype=torch.float64, device=dev)
+    types_d = torch.tensor(types, dtype=torch.int32, device=dev)
+    ref = model.calculate(pos_d, cell, pbc, types_d)
+    out = par.calculate(pos_d, cell, pbc, types_d)
+    ids = out['local_ids'].long()
+    df = (out['forces'] - ref['forces'][ids]).abs().max().double()
+    de = (out['energy'].double() - ref['energy'].double()).abs().max() / n_atoms
+    ds = ((out['stress'] - ref['stress']).abs().max() / ref['stress'].abs().max()).double()
+    ne = torch.tensor([float(out['n_edges'])], device=dev, dtype=torch.float64)
+    t = torch.stack([de.reshape(()), df.reshape(()), ds.reshape(())])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.all_reduce(ne)
+    de, df, ds = (float(v) for v in t.cpu())
+    return dict(against='single-GPU engine on the whole cell (same kernels, one rank)', transport='NCCL', n_atoms=n_atoms,
+                edge_count_equal=bool(int(ne.item()) == int(ref['graph']['src'].shape[0])), dE_per_atom=de, max_dF=df, rel_dS=ds,
+                within_tolerance=bool(de <= 1e-6 and df <= 6e-5 and ds <= 1e-4))
+
+
+def reference_gpu_time(dev, n_atoms, steps=3, warmup=2):
+    """the reference's frozen TorchScript graph with map_location='cuda' on this B200 ("the one to beat"), at the
+    largest size of the same generator that fits (it materialises [E, 3136] messages and keeps them for autograd)."""
+    from sevennet_finetuning_b200 import ops
+    path = os.path.join(ROOT, 'oracle', '_ref', 'deployed_serial.pt')
+    if not os.path.exists(path):
+        return dict(unavailable='oracle/_ref/deployed_serial.pt did not travel')
+    for fn in ('_jit_override_can_fuse_on_gpu', '_jit_set_texpr_fuser_enabled', '_jit_set_nvfuser_enabled'):
+        try:   # as pair_e3gnn.cpp:324-329 does: no JIT fusers
+            getattr(torch._C, fn)(False)
+        except Exception:
+            pass
+    ts = torch.jit.load(path, map_location=dev).eval()
+    while n_atoms >= 500:
+        try:
+            pos, cell, pbc, types = make_cell(n_atoms, seed=1)
+            pos_d = torch.tensor(pos, dtype=torch.float64, device=dev)
+            x = torch.tensor(types, dtype=torch.long, device=dev)
+            cell_t = torch.tensor(cell, dtype=torch.float32, device=dev)
+            vol = torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32, device=dev)
+
+            def call():
+                g = ops.radius_graph(pos_d, cell, pbc, 5.0)   # graph by the CUDA cell list (the reference would use ASE on the CPU)
+                d = {'x': x, 'pos': pos_d.float().requires_grad_(True),
+                     'edge_index': torch.stack([g['dst'].long(), g['src'].long()]), 'pbc_shift': g['shift'].float(),
+                     'cell_lattice_vectors': cell_t, 'cell_volume': vol, 'num_atoms': torch.tensor(n_atoms),
+                     'batch': torch.zeros(0, dtype=torch.long)}
+                o = ts(d)
+                return o['inferred_total_energy'], o['inferred_force'], int(g['src'].shape[0])
+            for _ in range(warmup):
+                call()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                e, f, ne = call()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            return dict(value=n_atoms / (ms * 1e-3), unit=UNIT, n_atoms=n_atoms, n_edges=ne, ms_per_call=ms, steps=steps,
+                        kind='reference: frozen TorchScript graph (deployed_serial.pt), map_location=cuda, fp32, JIT fusers off',
+                        peak_mem_gb=torch.cuda.max_memory_allocated(dev) / 1e9, energy=float(e.detach()))
+        except torch.cuda.OutOfMemoryError:
+            torch.cuda.empty_cache()
+            n_atoms //= 2
+        except Exception as ex:
+            return dict(unavailable=repr(ex)[:300])
+    return dict(unavailable='out of memory at every size tried')
 
 
 FT_METRIC = 'SevenNet-0 fine-tune structures/s'
@@ -372,6 +494,9 @@ def main():
                     help="md: configs 3/4 (atom-steps/s, the default line); finetune: configs 2/5 (structures/s)")
     ap.add_argument('--batch', type=int, default=32, help='finetune: structures per train batch (and per replay batch)')
     ap.add_argument('--no-finetune', action='store_true', help='md line without the appended fine-tune measurement')
+    ap.add_argument('--strong-atoms', type=int, default=1_048_576, help='N>1: size of the one cell of the strong-scaling view')
+    ap.add_argument('--no-alt', action='store_true', help='skip the second scaling view (scaling_base / strong_scaling)')
+    ap.add_argument('--ref-gpu-atoms', type=int, default=8000, help='N=1: size tried first for the reference graph on the GPU')
     a = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
@@ -402,11 +527,17 @@ def main():
                                   gpu_launches=0)))
             return
         steps = max(1, min(a.steps, 3))
-        cb, dt = reference_cpu_time(a.cpu_atoms, steps, min(a.warmup, 1))
+        cb, dt = reference_cpu_time(max(a.cpu_atoms, 3000), steps, min(a.warmup, 1), full_atoms=n_total)
+        cfg = dict(cfg, reference_sample=cb['sample'])
         line = dict(metric=METRIC, value=cb['value'], unit=UNIT, n_gpus=a.gpus, steps=steps, warmup=min(a.warmup, 1),
                     ms_per_step=dt * 1e3, higher_is_better=True, scaling='weak', vs_baseline=None, dtype='f32',
                     data='synthetic', config=cfg, impl='reference', cpu_baseline=cb,
-                    e2e=dict(value=cb['value'], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
+                    e2e=dict(value=cb['value'], unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0,
+                    extrapolated=True)
+        try:
+            line['si216'] = si216_cpu_time()
+        except Exception as ex:
+            line['si216'] = {'error': repr(ex)[:200]}
         print(json.dumps(line))
         return
 
@@ -482,6 +613,11 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), out
 
+    # parity of the benchmarked workload before anything is timed
+    try:
+        parity = parity_vs_reference(model, a.cpu_atoms) if par is None else parity_parallel(model, par, dev)
+    except Exception as ex:
+        parity = {'error': repr(ex)[:300]}
     for _ in range(warmup):
         out = step_resident()
     if par is None:
@@ -556,12 +692,33 @@ def main():
                 step_roofline=dict(bound='hbm', algorithmic_bytes=step_bytes, achieved=step_bytes / (step_ms * 1e-3) / 1e9,
                                    peak=pk['hbm'] * world, unit='GB/s',
                                    frac=step_bytes / (step_ms * 1e-3) / 1e9 / (pk['hbm'] * world)),
-                kernel_ms_per_step=cat_ms, ms_each_step=per_step_res, clocks=clocks)
+                kernel_ms_per_step=cat_ms, ms_each_step=per_step_res, clocks=clocks, parity=parity)
+    # second scaling views (3 steps each after 1 warm-up): N = 1 at the per-GPU size of the multi-GPU runs; N > 1 strong
+    # scaling of ONE 1,048,576-atom cell next to the weak-scaling `value`
+    try:
+        n_alt = a.atoms_per_gpu if world == 1 else a.strong_atoms
+        if n_alt and n_alt != n_total and not a.no_alt:
+            model._ws = None
+            out = None
+            torch.cuda.empty_cache()
+            pos2, cell2, pbc2, types2 = make_cell(n_alt, seed=0)
+            pos2_d = torch.tensor(pos2, dtype=torch.float64, device=dev)
+            types2_d = torch.tensor(types2, dtype=torch.int32, device=dev)
+            fn2 = lambda: calc(pos2_d, cell2, pbc2, types2_d)   # noqa: E731
+            fn2()
+            t_alt, out = timed(fn2, 3)
+            key = 'scaling_base' if world == 1 else 'strong_scaling'
+            line[key] = dict(n_atoms=n_alt, value=n_alt * 3 / t_alt, unit=UNIT, ms_per_step=t_alt / 3 * 1e3, steps=3,
+                             note=('N = 1 at the per-GPU cell size of the N > 1 runs' if world == 1 else
+                                   f'strong scaling: one {n_alt}-atom cell on {world} GPUs'))
+            pos2_d = types2_d = None
+    except Exception as ex:
+        line['scaling_base' if world == 1 else 'strong_scaling'] = {'error': repr(ex)[:300]}
     if world == 1 and not a.no_finetune:
         # second half of BASELINE.json's metric ("...; fine-tune structures/s"): config 2 in the same run, after the MD
         # workspace is released (full line: python bench.py --workload finetune)
         model._ws = None
-        del out, pos_d, types_d
+        out = pos_d = types_d = None
         torch.cuda.empty_cache()
         try:
             fa = argparse.Namespace(**vars(a))
@@ -573,7 +730,10 @@ def main():
             line['finetune'] = {'error': repr(ex)}
     if rank == 0:
         if not a.no_cpu_baseline and world == 1:
-            line['cpu_baseline'], _ = reference_cpu_time(a.cpu_atoms, 2, 1)
+            line['cpu_baseline'], _ = reference_cpu_time(a.cpu_atoms, 2, 1, full_atoms=n_total)
+            model._ws = None
+            torch.cuda.empty_cache()
+            line['reference_gpu'] = reference_gpu_time(dev, a.ref_gpu_atoms)
         print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()

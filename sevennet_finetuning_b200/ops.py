@@ -322,6 +322,45 @@ def colsum(x):
     return out
 
 
+def edge_embed_bwd_r(params, vec, dY, dr):
+    E = vec.shape[0]
+    dvec = torch.empty(E, 3, dtype=torch.float32, device=vec.device)
+    check(lib().b200_edge_embed_bwd_r(C.byref(params), E, _p(vec), _p(dY), _p(dr), _p(dvec), _stream()), 'edge_embed_bwd_r')
+    return dvec
+
+
+@_timed
+def gate_bwd2(ns, m1, m2, x, gout, a):
+    """Second-order pass of the gate: a = dL/d(gate_bwd output) -> (dL/dx, dL/d gout)."""
+    dx = torch.empty_like(x)
+    dg = torch.empty_like(gout)
+    check(lib().b200_gate_bwd2(ns, m1, m2, x.shape[0], _p(x), _p(gout), _p(a), _p(dx), _p(dg), _stream()), 'gate_bwd2')
+    return dx, dg
+
+
+@_timed
+def edge_embed_dk(params, vec, coeffs, demb):
+    """d bessel_coeffs of the first reverse pass (deterministic two-stage sum over the edges)."""
+    dk = torch.empty(params.num_basis, dtype=torch.float32, device=vec.device)
+    check(lib().b200_edge_embed_dk(C.byref(params), vec.shape[0], _p(vec), _p(coeffs), _p(demb), _p(dk), _stream()),
+          'edge_embed_dk')
+    return dk
+
+
+@_timed
+def edge_embed_bwd2(params, vec, coeffs, gY, gemb, a, want_dk=True):
+    """Second-order pass of the edge embedding: a = dL/d(dvec) -> (dL/dvec, dL/d gY, dL/d gemb, dL/d coeffs)."""
+    E = vec.shape[0]
+    dev = vec.device
+    dvec2 = torch.empty(E, 3, dtype=torch.float32, device=dev)
+    dgY = torch.empty(E, 9, dtype=torch.float32, device=dev)
+    dgemb = torch.empty(E, params.num_basis, dtype=torch.float32, device=dev)
+    dk = torch.empty(params.num_basis, dtype=torch.float32, device=dev) if want_dk else None
+    check(lib().b200_edge_embed_bwd2(C.byref(params), E, _p(vec), _p(coeffs), _p(gY), _p(gemb), _p(a), _p(dvec2), _p(dgY),
+                                     _p(dgemb), _p(dk), _stream()), 'edge_embed_bwd2')
+    return dvec2, dgY, dgemb, dk
+
+
 # ---- tabulated radial weights (MD path) -----------------------------------------------------------------------------------
 def radial_table_build(params, coeffs, W0, W1, W2):
     d = MlpDesc(W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1])
