@@ -173,8 +173,12 @@ class AtomGraphSequential(nn.Sequential):
         self._modules.update({key: module})
 
     def prepand_module(self, key, module):
-        self._modules.update({key: module})
-        self._modules.move_to_end(key, last=False)
+        # (torch >= 2.x keeps _modules in a plain dict: rebuild it with the new key first instead of move_to_end)
+        rest = [(k, v) for k, v in self._modules.items() if k != key]
+        self._modules.clear()
+        self._modules[key] = module
+        for k, v in rest:
+            self._modules[k] = v
 
     def delete_module_by_key(self, key):
         if key in self._modules:

@@ -535,6 +535,138 @@ class AtomReduce(nn.Module):
         return data
 
 
+class _EdgeVecFn(torch.autograd.Function):
+    """edge_vec = pos[idx1] - pos[idx0] + shift @ cell at zero strain (sevenn/nn/edge_embedding.py:62-75) with the reverse pass
+    on the CUDA force / virial kernel: d E / d pos is minus the force sum of b200_force_virial and d E / d strain the
+    symmetrised sum of r (x) dE/dr (what autograd makes of the strain trick, :33-60).  First order (eval) only."""
+
+    @staticmethod
+    def forward(ctx, pos, strain, cell, shift, batch, g, batched):
+        ei_dst, ei_src = g['dst'].long(), g['src'].long()          # destination-sorted edge list of the graph cache
+        sh = shift if g['perm'] is None else shift.index_select(0, g['perm'])
+        if batched:
+            vec = pos[ei_src] - pos[ei_dst] + torch.einsum('ni,nij->nj', sh, cell[batch[ei_dst]])
+        else:
+            vec = pos[ei_src] - pos[ei_dst] + sh @ cell
+        vec = vec.float().contiguous()
+        ctx.g, ctx.batched, ctx.nb = g, batched, (strain.shape[0] if batched else 0)
+        ctx.save_for_backward(vec, batch)
+        if g['perm'] is not None:                                   # hand the vectors back in the caller's edge order
+            out = torch.empty_like(vec)
+            out[g['perm']] = vec
+            return out
+        return vec
+
+    @staticmethod
+    def backward(ctx, gvec):
+        vec, batch = ctx.saved_tensors
+        g = ctx.g
+        gv = ops._f32(gvec)
+        if g['perm'] is not None:
+            gv = gv.index_select(0, g['perm']).contiguous()
+        force, vir = ops.force_virial(g['rowptr'], g['rrowptr'], g['eid'], vec, gv)    # F = -dE/dpos; vir per source atom
+        if ctx.batched:
+            v6 = torch.zeros(ctx.nb, 6, dtype=vir.dtype, device=vir.device).index_add_(0, batch, vir[:batch.shape[0]])
+        else:
+            v6 = ops.colsum(vir).view(1, 6)
+        # [xx, yy, zz, xy, yz, zx] -> symmetric 3x3 (sum_e r (x) g is symmetric for a rotation-invariant energy)
+        idx = torch.tensor([0, 3, 5, 3, 1, 4, 5, 4, 2], device=v6.device)
+        dstrain = v6[:, idx].view(-1, 3, 3)
+        if not ctx.batched:
+            dstrain = dstrain[0]
+        return -force[:batch.shape[0]] if ctx.batched else -force, dstrain, None, None, None, None, None
+
+
+class EdgePreprocess(nn.Module):
+    """sevenn/nn/edge_embedding.py:13-77: edge vectors from positions, image shifts and the cell, with a zero strain tensor
+    as a differentiable leaf (`_strain`) so that stress = -(dE/d strain)/V.  Prepended by scripts/deploy.py:22."""
+
+    def __init__(self, is_stress=True):
+        super().__init__()
+        self.is_stress = is_stress
+        self._is_batch_data = True
+
+    def forward(self, data):
+        pos, shift, batch = data['pos'], data['pbc_shift'], data['batch']
+        cell = data['cell_lattice_vectors'].view(-1, 3, 3) if self._is_batch_data else data['cell_lattice_vectors'].view(3, 3)
+        if self.training or not pos.is_cuda:
+            # second-order (training) flavour: plain differentiable tensor algebra, exactly the reference's lines
+            if self.is_stress:
+                if self._is_batch_data:
+                    strain = torch.zeros((_num_structures(data), 3, 3), dtype=pos.dtype, device=pos.device, requires_grad=True)
+                    sym = 0.5 * (strain + strain.transpose(-1, -2))
+                    pos = pos + torch.bmm(pos.unsqueeze(-2), sym[batch]).squeeze(-2)
+                    cell = cell + torch.bmm(cell, sym)
+                else:
+                    strain = torch.zeros((3, 3), dtype=pos.dtype, device=pos.device, requires_grad=True)
+                    sym = 0.5 * (strain + strain.transpose(-1, -2))
+                    pos = pos + torch.mm(pos, sym)
+                    cell = cell + torch.mm(cell, sym)
+                data['_strain'] = strain
+            i0, i1 = data['edge_index'][0], data['edge_index'][1]
+            vec = pos[i1] - pos[i0]
+            vec = vec + (torch.einsum('ni,nij->nj', shift, cell[batch[i0]]) if self._is_batch_data
+                         else torch.einsum('ni,ij->nj', shift, cell))
+        else:
+            nb = _num_structures(data) if self._is_batch_data else 0
+            strain = torch.zeros((nb, 3, 3) if self._is_batch_data else (3, 3), dtype=pos.dtype, device=pos.device,
+                                 requires_grad=self.is_stress)
+            if self.is_stress:
+                data['_strain'] = strain
+            vec = _EdgeVecFn.apply(pos, strain, cell, shift, batch, _graph_of(data), self._is_batch_data)
+        data['edge_vec'] = vec
+        data['edge_length'] = torch.linalg.norm(vec, dim=-1)
+        return data
+
+
+class ForceOutput(nn.Module):
+    """sevenn/nn/force_output.py:12-48: F = -dE/dpos."""
+
+    def __init__(self, data_key_pos='pos', data_key_energy='inferred_total_energy', data_key_force='inferred_force'):
+        super().__init__()
+        self.key_pos, self.key_energy, self.key_force = data_key_pos, data_key_energy, data_key_force
+
+    def forward(self, data):
+        (grad,) = torch.autograd.grad([data[self.key_energy].sum()], [data[self.key_pos]], create_graph=self.training,
+                                      allow_unused=True)
+        if grad is not None:
+            data[self.key_force] = torch.neg(grad)
+        return data
+
+
+class ForceStressOutput(nn.Module):
+    """sevenn/nn/force_output.py:52-130: F = -dE/dpos, stress = -(dE/d strain)/V in the order [xx, yy, zz, xy, yz, zx], volume
+    clamped at 1e-3 (:98-102).  Swapped in by scripts/deploy.py:23; needs EdgePreprocess in front (`_strain`)."""
+
+    def __init__(self, data_key_pos='pos', data_key_energy='inferred_total_energy', data_key_force='inferred_force',
+                 data_key_stress='inferred_stress', data_key_cell_volume='cell_volume'):
+        super().__init__()
+        self.key_pos, self.key_energy, self.key_force = data_key_pos, data_key_energy, data_key_force
+        self.key_stress, self.key_cell_volume = data_key_stress, data_key_cell_volume
+        self._is_batch_data = True
+
+    def forward(self, data):
+        grad = torch.autograd.grad([data[self.key_energy].sum()], [data[self.key_pos], data['_strain']],
+                                   create_graph=self.training, allow_unused=True)
+        if grad[0] is not None:
+            data[self.key_force] = torch.neg(grad[0])
+        volume = data[self.key_cell_volume]
+        vlim = 1e-3
+        if self._is_batch_data:
+            volume = torch.clamp(volume, min=vlim)
+        elif float(volume) < vlim:
+            volume = torch.tensor(vlim, device=volume.device)
+        sgrad = grad[1]
+        if sgrad is not None:
+            if self._is_batch_data:
+                s = torch.neg(sgrad) / volume.view(-1, 1, 1)
+                data[self.key_stress] = torch.stack((s[:, 0, 0], s[:, 1, 1], s[:, 2, 2], s[:, 0, 1], s[:, 1, 2], s[:, 0, 2]), dim=1)
+            else:
+                s = torch.neg(sgrad) / volume
+                data[self.key_stress] = torch.stack((s[0, 0], s[1, 1], s[2, 2], s[0, 1], s[1, 2], s[0, 2]))
+        return data
+
+
 class ForceStressOutputFromEdge(nn.Module):
     """sevenn/nn/force_output.py:133-215: forces and stress from dE/d edge_vec."""
 
@@ -557,6 +689,19 @@ class ForceStressOutputFromEdge(nn.Module):
         n = g['n_src']
         if fij is None:
             fij = torch.zeros_like(rij)
+        if not _second_order(self) and rij.is_cuda:
+            # first-order flavour (calculator, MD): the CUDA force / virial kernel on the destination-sorted edge list
+            r_s, f_s = ops._f32(rij.detach()), ops._f32(fij)
+            if g['perm'] is not None:
+                r_s, f_s = r_s.index_select(0, g['perm']).contiguous(), f_s.index_select(0, g['perm']).contiguous()
+            force, vir = ops.force_virial(g['rowptr'], g['rrowptr'], g['eid'], r_s, f_s)
+            data[self.key_force] = force
+            if self._is_batch_data:
+                per = torch.zeros(_num_structures(data), 6, dtype=vir.dtype, device=vir.device).index_add_(0, data['batch'], vir[:data['batch'].shape[0]])
+                data[self.key_stress] = -per / data[self.key_cell_volume].view(-1, 1)
+            else:
+                data[self.key_stress] = -ops.colsum(vir) / data[self.key_cell_volume]
+            return data
         ei = data[self.key_edge_idx]
         force = torch.zeros(n, 3, dtype=fij.dtype, device=fij.device)
         force.index_add_(0, ei[0], fij)
@@ -595,8 +740,12 @@ class AtomGraphSequential(nn.Sequential):
         self._is_batch_data = flag
 
     def prepand_module(self, key, module):
-        self._modules.update({key: module})
-        self._modules.move_to_end(key, last=False)
+        # (torch >= 2.x keeps _modules in a plain dict: rebuild it with the new key first instead of move_to_end)
+        rest = [(k, v) for k, v in self._modules.items() if k != key]
+        self._modules.clear()
+        self._modules[key] = module
+        for k, v in rest:
+            self._modules[k] = v
 
     def replace_module(self, key, module):
         self._modules.update({key: module})
@@ -675,7 +824,7 @@ def build_E3_equivariant_model(config=None):
     return AtomGraphSequential(L, cutoff)
 
 
-_TWINS = ('EdgeEmbedding', 'OnehotEmbedding', 'IrrepsLinear', 'SelfConnectionLinearIntro', 'SelfConnectionIntro', 'SelfConnectionOutro',
+_TWINS = ('EdgePreprocess', 'ForceOutput', 'ForceStressOutput', 'EdgeEmbedding', 'OnehotEmbedding', 'IrrepsLinear', 'SelfConnectionLinearIntro', 'SelfConnectionIntro', 'SelfConnectionOutro',
           'IrrepsConvolution', 'EquivariantGate', 'Rescale', 'SpeciesWiseRescale', 'AtomReduce', 'ForceStressOutputFromEdge')
 
 

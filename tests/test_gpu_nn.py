@@ -492,3 +492,55 @@ def test_substitute_into_reference_sequential(gold, weights):
         assert np.abs(out['inferred_force'].detach().cpu().numpy() - g['ref_force']).max() <= 4e-5
         s = out['inferred_stress'].detach().cpu().numpy()
         assert np.abs(s - g['o64_stress']).max() <= 1e-4 * np.abs(g['o64_stress']).max()
+
+
+@pytest.mark.parametrize('name', ['si216.npz', 'hfo2_96.npz'])
+def test_deployed_serial_form_matches_golden(twin, gold, name):
+    """The deployed serial form of the model, assembled exactly as sevenn/scripts/deploy.py:22-23 does: EdgePreprocess
+    prepended, force_output replaced by ForceStressOutput, inputs = the deployed dict (pos, pbc_shift, cell_lattice_vectors,
+    cell_volume) - the same fp32 arithmetic from the same inputs as the reference's frozen graph that produced ref_*."""
+    import copy
+    from sevennet_finetuning_b200 import nn as b200nn
+    g = gold(name)
+    dev = torch.device('cuda:0')
+    m = copy.deepcopy(twin)
+    m.prepand_module('edge_preprocess', b200nn.EdgePreprocess(True))
+    m.replace_module('force_output', b200nn.ForceStressOutput())
+    assert list(m._modules)[0] == 'edge_preprocess' and type(m._modules['force_output']).__name__ == 'ForceStressOutput'
+    m = m.to(dev).eval()
+    n = len(g['pos'])
+
+    def inputs(batched, shuffle):
+        ei, sh = g['edge_index'], g['shift']
+        if shuffle:
+            p = np.random.default_rng(1).permutation(ei.shape[1])
+            ei, sh = ei[:, p], sh[p]
+        vol = torch.tensor(abs(np.linalg.det(g['cell'])), dtype=torch.float32, device=dev)
+        return {'x': torch.tensor(g['types'], dtype=torch.long, device=dev),
+                'pos': torch.tensor(g['pos'], dtype=torch.float32, device=dev).requires_grad_(True),
+                'edge_index': torch.tensor(ei, dtype=torch.long, device=dev),
+                'pbc_shift': torch.tensor(sh, dtype=torch.float32, device=dev),
+                'cell_lattice_vectors': torch.tensor(g['cell'], dtype=torch.float32, device=dev).view((1, 3, 3) if batched else (3, 3)),
+                'cell_volume': vol.view(1) if batched else vol,
+                'num_atoms': torch.tensor([n], device=dev) if batched else torch.tensor(n, device=dev),
+                'batch': torch.zeros(n if batched else 0, dtype=torch.long, device=dev)}
+
+    for batched, shuffle in ((False, False), (False, True), (True, False)):
+        m.set_is_batch_data(batched)
+        out = m(inputs(batched, shuffle))
+        e = float(out['inferred_total_energy'].reshape(-1)[0])
+        f = out['inferred_force'].detach().cpu().numpy()
+        s = out['inferred_stress'].detach().cpu().numpy().reshape(-1)
+        # 1e-6 eV/atom, but never tighter than two fp32 ulps of the total energy (96 atoms at -972 eV: one ulp = 6.4e-7 eV/atom)
+        etol = max(1e-6, 2.0 * float(np.spacing(np.float32(abs(e)))) / n)
+        assert abs(e - float(g['ref_energy'])) / n <= etol and abs(e - float(g['o64_energy'])) / n <= etol
+        # fp32 positions: an edge vector carries ~2e-6 A of rounding before anything is computed (the reference's frozen graph,
+        # fed the same dict, sits 1-2e-5 eV/A from float64 for the same reason), hence 4e-5 against both
+        assert np.abs(f - g['ref_force']).max() <= 4e-5 and np.abs(f - g['o64_force']).max() <= 4e-5
+        assert np.abs(s - g['ref_stress']).max() <= 2e-4 * np.abs(g['ref_stress']).max()
+        assert np.abs(s - g['o64_stress']).max() <= 1e-4 * np.abs(g['o64_stress']).max()
+    # ForceOutput alone (no stress): same forces
+    m.replace_module('force_output', b200nn.ForceOutput())
+    m.set_is_batch_data(False)
+    out = m(inputs(False, False))
+    assert np.abs(out['inferred_force'].detach().cpu().numpy() - g['o64_force']).max() <= 4e-5 and 'inferred_stress' not in out
