@@ -254,9 +254,11 @@ neighbor_kernel(GridHost G, int n, const double* __restrict__ pos, const GridDev
             keep = dd < G.cut2 && !(i == j && s0 == 0 && s1 == 0 && s2 == 0);
           }
           const unsigned m = __ballot_sync(0xffffffffu, keep);
+          // image shifts beyond the 10-bit fields of the packed sort key: flagged in the counting pass, whose result the
+          // host reads back anyway (graph_count fails with B200_ERR_INVALID)
+          if (!FILL && keep && err && (abs(s0) > 511 || abs(s1) > 511 || abs(s2) > 511)) atomicExch(err, 1);
           if (FILL && keep) {
             const int p = base + count + __popc(m & ((1u << lane) - 1u));
-            if (abs(s0) > 511 || abs(s1) > 511 || abs(s2) > 511) atomicExch(err, 1);
             tmp_key[p] = pack_key(j, s0, s1, s2);
           }
           count += __popc(m);
@@ -340,13 +342,18 @@ int graph_count(int n, const double* pos, const double* cell_host, const int* pb
   exclusive_scan_kernel<<<1, 1024, 0, st>>>(w.bin_count, w.bin_start, &w.grid->nbins, 0);
   fill_bins_kernel<<<nb, 256, 0, st>>>(n, w.bin_of, w.bin_start, w.bin_cursor, w.bin_atoms);
   const unsigned nwb = (unsigned)(((long long)n * 32 + 255) / 256);
+  int* err = w.bin_cursor;   // free again after fill_bins_kernel: the overflow flag of the packed sort key
+  cudaMemsetAsync(err, 0, sizeof(int), st);
   neighbor_kernel<false><<<nwb, 256, 0, st>>>(G, n, pos, w.grid, w.bin_of, w.off, w.bin_start, w.bin_atoms, w.deg, nullptr,
-                                              nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+                                              nullptr, nullptr, nullptr, nullptr, nullptr, err);
   exclusive_scan_kernel<<<1, 1024, 0, st>>>(w.deg, rowptr, nullptr, n);
-  int total = 0;
+  int total = 0, overflow = 0;
   cudaMemcpyAsync(&total, rowptr + n, sizeof(int), cudaMemcpyDeviceToHost, st);
+  cudaMemcpyAsync(&overflow, err, sizeof(int), cudaMemcpyDeviceToHost, st);
   cudaStreamSynchronize(st);
   *n_edges_host = total;
+  B200_REQUIRE(overflow == 0, "radius_graph: an edge needs a periodic image shift beyond +-511 cells (cell much thinner than the "
+                              "cutoff, or atoms far outside the cell): not representable in the packed sort key");
   return check_launch("graph_count", 6);
 }
 
@@ -357,11 +364,9 @@ int graph_fill(int n, const double* pos, const double* cell_host, const int* pbc
   GridHost G;
   if (int rc = make_grid_host(cell_host, pbc_host, cutoff, n, G)) return rc;
   GraphWs w = carve(ws, n);
-  int* err = w.bin_cursor;  // reuse as the overflow flag
-  cudaMemsetAsync(err, 0, sizeof(int), st);
   const unsigned nwb = (unsigned)(((long long)n * 32 + 255) / 256);
   neighbor_kernel<true><<<nwb, 256, 0, st>>>(G, n, pos, w.grid, w.bin_of, w.off, w.bin_start, w.bin_atoms, nullptr, rowptr,
-                                             tmp_key, src, dst, shift, edge_vec, err);
+                                             tmp_key, src, dst, shift, edge_vec, nullptr);
   return check_launch("graph_fill");
 }
 

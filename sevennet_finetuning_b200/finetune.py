@@ -272,7 +272,11 @@ class RehearsalTrainer:
 
     def compute_fisher_matrix(self, batches, loss_thr=-1.0):
         """Fisher[name] = mean over the kept batches of grad^2; theta* = current parameters (trainer.py:126-152)."""
-        fisher = {n: torch.zeros_like(p) for n, p in self.model.named_parameters()}
+        # names without DDP's 'module.' prefix: EWCLoss strips it before looking a name up, so a Fisher dict computed under
+        # DDP must not carry it (with the prefix no name matches and the penalty is silently zero)
+        def bare(n):
+            return n[7:] if n.startswith('module.') else n
+        fisher = {bare(n): torch.zeros_like(p) for n, p in self.model.named_parameters()}
         self.model.train()
         cnt = 0
         for batch in batches:
@@ -282,11 +286,11 @@ class RehearsalTrainer:
                 loss.backward()
                 for n, p in self.model.named_parameters():
                     if p.grad is not None:
-                        fisher[n] += p.grad.detach().clone() ** 2
+                        fisher[bare(n)] += p.grad.detach().clone() ** 2
                 cnt += 1
         for n in fisher:
             fisher[n] /= max(cnt, 1)
-        opt = {k: v.data.detach().clone() for k, v in self.model.named_parameters()}
+        opt = {bare(k): v.data.detach().clone() for k, v in self.model.named_parameters()}
         return fisher, opt, cnt
 
 

@@ -155,11 +155,11 @@ class _ConvFn(torch.autograd.Function):
     """weight_nn + uvu tensor product + scatter / denominator (convolution.py:105-121); edges sorted by dst."""
 
     @staticmethod
-    def forward(ctx, x, Y, emb, W0, W1, W2, denom, graph, muls, lout):
+    def forward(ctx, x, Y, emb, W0, W1, W2, denom, graph, muls, lout, denom_host):
         x32, Y32, e32 = ops._f32(x), ops._f32(Y), ops._f32(emb)
         Ws = [ops._f32(W) for W in (W0, W1, W2)]
         w = ops.radial_mlp_fwd(e32, *Ws)
-        d = float(denom)
+        d = denom_host
         out = ops.conv_fwd(muls, lout, graph['rowptr'][:graph['n_dst'] + 1].contiguous(), graph['src'], x32, Y32, w, d)
         ctx.save_for_backward(x32, Y32, e32, *Ws, out)
         ctx.graph, ctx.muls, ctx.lout, ctx.denom = graph, muls, lout, d
@@ -180,22 +180,21 @@ class _ConvFn(torch.autograd.Function):
         demb = ops.radial_mlp_bwd(emb, W0, W1, W2, dw) if ctx.needs_input_grad[2] else None
         dW0 = dW1 = dW2 = None
         if any(ctx.needs_input_grad[3:6]):
-            # parameter gradients of the radial MLP: small dense GEMMs over the edge axis (library GEMMs)
-            nb, h = W0.shape[0], W1.shape[0]
-            z1 = emb @ W0 / math.sqrt(nb)
-            s1 = torch.sigmoid(z1)
-            h1 = C_SILU * z1 * s1
-            z2 = h1 @ W1 / math.sqrt(h)
-            s2 = torch.sigmoid(z2)
-            h2 = C_SILU * z2 * s2
-            k2 = 1.0 / math.sqrt(W2.shape[0])
-            dW2 = h2.t() @ dw * k2
-            dz2 = (dw @ W2.t() * k2) * (C_SILU * s2 * (1 + z2 * (1 - s2)))
-            dW1 = h1.t() @ dz2 / math.sqrt(h)
-            dz1 = (dz2 @ W1.t() / math.sqrt(h)) * (C_SILU * s1 * (1 + z1 * (1 - s1)))
-            dW0 = emb.t() @ dz1 / math.sqrt(nb)
+            # parameter gradients of the radial MLP over the edge axis with the library's own kernels: a dense layer is the l = 0
+            # block of an irreps linear (b200_irreps_linear / its transpose / b200_irreps_linear_wgrad), c * silu a gate of scalars
+            nb, h1n, h2n, wn = W0.shape[0], W0.shape[1], W1.shape[1], W2.shape[1]
+            (d0, n0), (d1, n1), (d2, n2) = (ops.make_lin_desc(f'{a}x0e', f'{b}x0e') for a, b in ((nb, h1n), (h1n, h2n), (h2n, wn)))
+            z1 = ops.irreps_linear(d0, emb, W0.reshape(-1))
+            a1 = ops.gate_fwd(h1n, 0, 0, z1)
+            z2 = ops.irreps_linear(d1, a1, W1.reshape(-1))
+            a2 = ops.gate_fwd(h2n, 0, 0, z2)
+            dW2 = ops.irreps_linear_wgrad(d2, a2, dw, n2).view_as(W2)
+            dz2 = ops.gate_bwd(h2n, 0, 0, z2, ops.irreps_linear(d2, dw, W2.reshape(-1), transpose=True))
+            dW1 = ops.irreps_linear_wgrad(d1, a1, dz2, n1).view_as(W1)
+            dz1 = ops.gate_bwd(h1n, 0, 0, z1, ops.irreps_linear(d1, dz2, W1.reshape(-1), transpose=True))
+            dW0 = ops.irreps_linear_wgrad(d0, emb, dz1, n0).view_as(W0)
         dden = -(out * gout).sum().reshape(1) / d if ctx.needs_input_grad[6] else None
-        return dx, dY, demb, dW0, dW1, dW2, dden, None, None, None
+        return dx, dY, demb, dW0, dW1, dW2, dden, None, None, None, None
 
 
 # ---- modules ----------------------------------------------------------------------------------------------------------
@@ -438,6 +437,14 @@ class IrrepsConvolution(nn.Module):
         self._comm_size = self.muls[0] + 3 * self.muls[1] + 5 * self.muls[2]   # convolution.py:102
         self._mlp_descs = None
 
+    def _denominator_host(self):
+        # host copy of the denominator, refreshed only when the parameter changed (optimizer step, load_state_dict): reading
+        # it every forward is a device->host synchronisation per layer
+        ver = (self.denominator._version, self.denominator.data_ptr())
+        if getattr(self, '_den_cache', None) is None or self._den_cache[0] != ver:
+            self._den_cache = (ver, float(self.denominator.detach()))
+        return self._den_cache[1]
+
     def forward(self, data):
         g = _graph_of(data)
         x = data[self.key_x]
@@ -455,11 +462,11 @@ class IrrepsConvolution(nn.Module):
             if self.denominator.requires_grad:   # train_denominator: keep 1/denominator in the graph
                 out = ho.ConvF.apply(x, Y, w, g, self.muls, self.lout, 1.0) / self.denominator
             else:
-                out = ho.ConvF.apply(x, Y, w, g, self.muls, self.lout, float(self.denominator))
+                out = ho.ConvF.apply(x, Y, w, g, self.muls, self.lout, self._denominator_host())
             data[self.key_x] = out
             return data
         out = _ConvFn.apply(x, Y, emb, nn_.layer0.weight, nn_.layer1.weight, nn_.layer2.weight, self.denominator, g,
-                            self.muls, self.lout)
+                            self.muls, self.lout, self._denominator_host())
         data[self.key_x] = out   # rows of the local atoms only (convolution.py:119-121)
         return data
 

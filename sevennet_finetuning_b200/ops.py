@@ -54,6 +54,10 @@ def _p(t):
         return None
     if not t.is_cuda:
         raise RuntimeError('sevennet_b200: CPU tensor passed to a CUDA-only op (there is no CPU fallback)')
+    if t.device.index != torch.cuda.current_device():
+        # kernels launch on the current device's current stream (_stream): a tensor of another GPU would be an invalid pointer
+        raise RuntimeError(f'sevennet_b200: tensor on {t.device} but the current CUDA device is {torch.cuda.current_device()}; '
+                           'wrap the call in torch.cuda.device(tensor.device)')
     if not t.is_contiguous():
         raise RuntimeError('sevennet_b200: tensor must be contiguous')
     return C.c_void_p(t.data_ptr())
