@@ -544,3 +544,64 @@ def test_deployed_serial_form_matches_golden(twin, gold, name):
     m.set_is_batch_data(False)
     out = m(inputs(False, False))
     assert np.abs(out['inferred_force'].detach().cpu().numpy() - g['o64_force']).max() <= 4e-5 and 'inferred_stress' not in out
+
+
+def test_batched_rehearsal_gradient_matches_float64_oracle(weights):
+    """Config 2's iteration on a BATCH (4 structures of ~32 atoms): every parameter gradient of the trainer's own loss
+    (RehearsalTrainer._fwd_loss: Huber E/F/S + EWC) against float64 double-backward through the oracle model in batch mode, and
+    the gradient the second optimizer.step of the iteration sees - the reference does not zero the gradients between the train
+    batch and the replay batch (sevenn/train/trainer.py:185-210), so it is grad_train(theta0) + grad_replay(theta1)."""
+    from sevennet_finetuning_b200 import finetune as ft, nn as b200nn
+    from sevennet_finetuning_b200.model import B200SevenNet
+    from sevennet_finetuning_b200.synthetic import bulk_batch
+    dev = torch.device('cuda:0')
+    cfg = dict(shift=weights['rescale_atomic_energy.shift'].tolist(), scale=weights['rescale_atomic_energy.scale'].tolist(),
+               conv_denominator=float(weights['0_convolution.denominator'][0]))
+    sd = {k: torch.tensor(v) for k, v in weights.items()}
+    engine = B200SevenNet(state_dict=weights, device=dev)
+    graphs = ft.synthetic_graphs(bulk_batch(4, seed=11, target_atoms=32), 5.0, dev, label_model=engine, noise=0.02, seed=11)
+    mem = ft.synthetic_graphs(bulk_batch(4, seed=12, target_atoms=32), 5.0, dev, label_model=engine, noise=0.02, seed=12)
+
+    def run(model, device, dtype):
+        """the iteration of RehearsalTrainer.run_one_step with the gradients recorded before each optimizer.step"""
+        fisher = {k: torch.full_like(v, 1e-3).to(dtype) for k, v in sd.items()}
+        star = {k: (v + 0.01 * torch.sin(torch.arange(v.numel(), dtype=torch.float64).reshape(v.shape) + 1.0)).to(dtype) for k, v in sd.items()}
+        lf = ft.get_loss_functions('huber', {'delta': 0.01}, 1.0, True, 0.01, fisher, star, ewc_lambda=1e3, device=device)
+        for p in model.parameters():
+            p.requires_grad_(True)
+        tr = ft.RehearsalTrainer(model, lf, 'sgd', {'lr': 1e-6}, device=device)
+        seen = []
+        step = tr.optimizer.step
+        tr.optimizer.step = lambda *a, **k: (seen.append({n: p.grad.detach().double().cpu().clone() for n, p in tr.model.named_parameters()}), step(*a, **k))[1]
+
+        def batch_of(gs):
+            b = ft.collate(gs, device)
+            if dtype == torch.float64:
+                b = {k: (v.double() if torch.is_tensor(v) and v.is_floating_point() else v) for k, v in b.items()}
+                b['edge_vec'] = b['edge_vec'].detach().requires_grad_(True)
+            return b
+        l, lm = tr.run_one_step(batch_of(graphs), batch_of(mem))
+        return seen, float(l), float(lm)
+
+    twin = b200nn.build_E3_equivariant_model(cfg)
+    twin.load_state_dict(sd)
+    got, l32, lm32 = run(twin, dev, torch.float32)
+    torch.set_default_dtype(torch.float64)
+    try:
+        ref = _oracle(weights)
+        want, l64, lm64 = run(ref, torch.device('cpu'), torch.float64)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    assert len(got) == 2 and len(want) == 2
+    assert abs(l32 - l64) <= 1e-4 * abs(l64) and abs(lm32 - lm64) <= 1e-4 * abs(lm64)
+    worst = [0.0, 0.0]
+    for s in range(2):
+        for k in want[s]:
+            a, b = got[s][k].reshape(-1), want[s][k].reshape(-1)
+            rel = float((a - b).abs().max() / max(float(b.abs().max()), 1e-12))
+            worst[s] = max(worst[s], rel)
+            assert rel < 1e-3, (s, k, rel)
+    # the second step really saw the sum (not the replay gradient alone)
+    k = '1_convolution.weight_nn.layer2.weight'
+    assert float((got[1][k] - got[0][k]).abs().max()) > 0 and float((got[1][k]).abs().max()) > 0
+    print('worst relative error: train-batch gradient', worst[0], 'accumulated gradient at the second step', worst[1])
