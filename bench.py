@@ -714,9 +714,10 @@ def main():
             pos2_d = types2_d = None
     except Exception as ex:
         line['scaling_base' if world == 1 else 'strong_scaling'] = {'error': repr(ex)[:300]}
-    if world == 1 and not a.no_finetune:
-        # second half of BASELINE.json's metric ("...; fine-tune structures/s"): config 2 in the same run, after the MD
-        # workspace is released (full line: python bench.py --workload finetune)
+    if not a.no_finetune:
+        # second half of BASELINE.json's metric ("...; fine-tune structures/s"): config 2 (N = 1) / config 5 (N > 1: data
+        # parallel, DDP over NCCL, 32 + 32 structures per GPU) in the same run, after the MD workspace is released (full
+        # line: python bench.py --workload finetune)
         model._ws = None
         out = pos_d = types_d = None
         torch.cuda.empty_cache()

@@ -154,6 +154,12 @@ int b200_rescale_fwd(int n_nodes, const int32_t* types, const float* scaled, con
                      int species_wise, float* atomic_energy, void* stream);
 /* out[c] = sum_n in[n, c], c < ncol <= 8 (fp64 accumulation, deterministic) */
 int b200_colsum(int n_rows, int ncol, const float* in, float* out, void* stream);
+/* Brick decomposition of a fully periodic cell for the spatially decomposed call (pair_e3gnn_parallel.cpp:277-314 takes
+ * LAMMPS' decomposition as given): key[i] = class * n_bins + cell_list_bin, class 0 = owned by this brick, 1 + owner = ghost
+ * (within margin = cutoff / cell height of the brick, periodic images included) owned by brick `owner`, n_bricks + 1 = not
+ * needed.  A stable sort of the keys orders the rank's atoms (cell-list order) and its ghosts (grouped by owner). */
+int b200_partition_keys(int64_t n_atoms, const double* pos, const double* inv_cell_host, const int* grid, const int* my_brick,
+                        const double* margin, const int* cell_bins, int64_t* key, void* stream);
 /* Halo exchange of the spatially decomposed call: pack_forward_init / unpack_forward_init (index_select of the rows a
  * peer asked for, pair_e3gnn_parallel.cpp:803-866) and pack_reverse / unpack_reverse (index_add of the returned gradient
  * rows into their owners, :867-933).  rows: [n, width] fp32; idx: int32 row numbers; out / in: packed [m, width]. */

@@ -71,6 +71,7 @@ SIGNATURES = {
     'b200_embed_fwd': (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     'b200_rescale_fwd': (_i, [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     'b200_colsum': (_i, [_i, _i, _vp, _vp, _vp]),
+    'b200_partition_keys': (_i, [_i64, _vp, _P(C.c_double), _P(C.c_int), _P(C.c_int), _P(C.c_double), _P(C.c_int), _vp, _vp]),
     'b200_halo_pack': (_i, [_i64, _i, _vp, _vp, _vp, _vp]),
     'b200_halo_unpack_add': (_i, [_i64, _i, _vp, _vp, _vp, _vp]),
     'b200_force_virial': (_i, [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -428,6 +428,55 @@ int csr_transpose(int n, long long E, const int* src, void* ws, int* rrowptr, in
   return check_launch("csr_transpose", E > 0 ? 4 : 1);
 }
 
+// ---- spatial decomposition: ownership / ghost classification of every atom of the cell (parallel.py) -------------------
+// pair_e3gnn_parallel.cpp:277-314 takes LAMMPS' brick decomposition as given; a stand-alone caller has to make it.  One
+// thread per atom: fractional coordinates, owner brick, distance to this rank's brick (periodic images included), and the
+// cell-list bin of the atom.  key = class * n_bins + bin with class 0 = owned by `rank`, 1 + owner = ghost of `rank` owned
+// by `owner`, n_ranks + 1 = not needed: ONE stable sort of the keys gives the rank's atoms in cell-list order followed by
+// its ghosts grouped by owner, and a histogram of the classes gives every count.  Fully periodic cells only.
+struct PartitionArgs {
+  double inv[9];      // inverse cell (frac = pos @ inv)
+  int grid[3];        // bricks per axis
+  int mine[3];        // this rank's brick
+  double margin[3];   // cutoff in units of the cell height per axis
+  int nb[3];          // cell-list bins per axis
+};
+__global__ void partition_keys_kernel(long long n, const double* __restrict__ pos, PartitionArgs a, long long* __restrict__ key) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double p0 = pos[3 * i], p1 = pos[3 * i + 1], p2 = pos[3 * i + 2];
+  int b[3], c[3];
+  bool near = true, local = true;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    double f = p0 * a.inv[k] + p1 * a.inv[3 + k] + p2 * a.inv[6 + k];
+    f -= floor(f);
+    b[k] = min(max((int)floor(f * a.grid[k]), 0), a.grid[k] - 1);
+    c[k] = min(max((int)(f * a.nb[k]), 0), a.nb[k] - 1);
+    local = local && b[k] == a.mine[k];
+    const double lo = (double)a.mine[k] / a.grid[k], hi = (double)(a.mine[k] + 1) / a.grid[k];
+    double d = fmax(fmax(lo - f, f - hi), 0.0);
+    d = fmin(d, fmax(fmax(lo - (f - 1.0), (f - 1.0) - hi), 0.0));
+    d = fmin(d, fmax(fmax(lo - (f + 1.0), (f + 1.0) - hi), 0.0));
+    near = near && d <= a.margin[k];
+  }
+  const int owner = (b[0] * a.grid[1] + b[1]) * a.grid[2] + b[2];
+  const int world = a.grid[0] * a.grid[1] * a.grid[2];
+  const long long cls = local ? 0 : (near ? 1 + owner : world + 1);
+  const long long bins = (long long)a.nb[0] * a.nb[1] * a.nb[2];
+  key[i] = cls * bins + ((long long)c[0] * a.nb[1] + c[1]) * a.nb[2] + c[2];
+}
+
+int partition_keys(long long n, const double* pos, const double* inv_cell_host, const int* grid, const int* mine,
+                   const double* margin, const int* nbins, long long* key, cudaStream_t st) {
+  if (n == 0) return B200_OK;
+  PartitionArgs a;
+  for (int k = 0; k < 9; ++k) a.inv[k] = inv_cell_host[k];
+  for (int k = 0; k < 3; ++k) { a.grid[k] = grid[k]; a.mine[k] = mine[k]; a.margin[k] = margin[k]; a.nb[k] = nbins[k]; }
+  partition_keys_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, pos, a, key);
+  return check_launch("partition_keys");
+}
+
 // ---- allocation-free variant of csr_transpose -----------------------------------------------------------
 // The two per-node counter arrays live in a file-scope device array instead of a caller workspace, so the call makes
 // no cudaMalloc / cudaFree (CUDA-graph capture, serving loops, harnesses that forbid allocation).  Every GPU that
@@ -477,4 +526,14 @@ extern "C" int b200_csr_transpose_static(int n, int64_t E, const int32_t* src, i
   const int rc = transpose_scratch_ptr(&ws);
   if (rc != B200_OK) return rc;
   return csr_transpose(n, E, src, ws, rrowptr, eid, (cudaStream_t)stream);
+}
+
+extern "C" int b200_partition_keys(int64_t n_atoms, const double* pos, const double* inv_cell_host, const int* grid,
+                                   const int* my_brick, const double* margin, const int* cell_bins, int64_t* key, void* stream) {
+  B200_REQUIRE(n_atoms >= 0 && inv_cell_host && grid && my_brick && margin && cell_bins && (n_atoms == 0 || (pos && key)),
+               "partition_keys: null argument");
+  for (int k = 0; k < 3; ++k)
+    B200_REQUIRE(grid[k] >= 1 && my_brick[k] >= 0 && my_brick[k] < grid[k] && cell_bins[k] >= 1, "partition_keys: bad brick grid");
+  return b200::partition_keys(n_atoms, pos, inv_cell_host, grid, my_brick, margin, cell_bins, (long long*)key,
+                              (cudaStream_t)stream);
 }

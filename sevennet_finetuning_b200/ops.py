@@ -308,6 +308,17 @@ def force_virial(rowptr, rrowptr, eid, vec, dvec):
     return force, vir
 
 
+def partition_keys(pos, inv_cell, grid, mine, margin, nbins):
+    """Sort keys of the brick decomposition (see include/sevennet_b200.h); pos float64 [N,3] on the device."""
+    n = pos.shape[0]
+    key = torch.empty(n, dtype=torch.int64, device=pos.device)
+    inv = (C.c_double * 9)(*[float(v) for v in np.asarray(inv_cell, np.float64).reshape(-1)])
+    g3, m3 = (C.c_int * 3)(*[int(v) for v in grid]), (C.c_int * 3)(*[int(v) for v in mine])
+    mg, nb = (C.c_double * 3)(*[float(v) for v in margin]), (C.c_int * 3)(*[int(v) for v in nbins])
+    check(lib().b200_partition_keys(n, _p(pos), inv, g3, m3, mg, nb, _p(key), _stream()), 'partition_keys')
+    return key
+
+
 def halo_pack(rows, idx, out):
     """out[k] = rows[idx[k]] (rows the peers asked for); rows [n, width] fp32, idx int32, out [m, width]."""
     check(lib().b200_halo_pack(idx.shape[0], rows.shape[1], _p(rows), _p(idx), _p(out), _stream()), 'halo_pack')

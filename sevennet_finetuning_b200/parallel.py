@@ -33,6 +33,11 @@ class DistComm:
     def all_reduce_sum(self, t):
         dist.all_reduce(t, group=self.group)
 
+    def all_gather(self, t):
+        out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t, group=self.group)
+        return out
+
 
 class ThreadComm:
     """In-process transport: the ranks are threads of one process sharing one device and one stream.
@@ -72,6 +77,13 @@ class ThreadComm:
         self.sh.barrier.wait()
         t.copy_(tot)
 
+    def all_gather(self, t):
+        self.sh.slots[self.rank] = t.clone()
+        self.sh.barrier.wait()
+        out = torch.stack([self.sh.slots[r] for r in range(self.world)])
+        self.sh.barrier.wait()
+        return out
+
 
 def brick_grid(world):
     """2 -> (2,1,1), 4 -> (2,2,1), 8 -> (2,2,2), otherwise the most cubic factorisation."""
@@ -110,6 +122,24 @@ class HaloPlan:
         for a in range(3):
             if pbc[a] and h[a] <= cutoff:
                 raise ValueError('parallel: periodic cell thinner than the cutoff is not supported')
+        self._n_global = pos.shape[0]
+        self.send_rows = None
+        self.send_counts = None
+        if pos.is_cuda and all(pbc):
+            # device path (fully periodic cell): ONE kernel classifies every atom (owned / ghost of which owner / not needed)
+            # and bins it into the cell list, one stable sort of the keys orders the rank's atoms (cell-list order) and its
+            # ghosts (grouped by owner), one histogram gives all counts: no per-atom eager tensor algebra, one host read
+            from . import ops
+            mine = np.array(np.unravel_index(rank, self.grid))
+            nb = [max(1, int(h[a] / cutoff)) for a in range(3)]
+            key = ops.partition_keys(pos, np.linalg.inv(cell), self.grid, mine, cutoff / h, nb)
+            skey, order = torch.sort(key, stable=True)
+            nbins = nb[0] * nb[1] * nb[2]
+            self._class_counts = torch.bincount(torch.div(skey, nbins, rounding_mode='floor'), minlength=world + 2)
+            self._order = order
+            self.presorted = True        # local_ids / ghost_ids already follow the cell list
+            return
+        self.presorted = False
         inv = torch.tensor(np.linalg.inv(cell), dtype=torch.float64, device=dev)
         frac = pos @ inv
         pb = torch.tensor(pbc, device=dev)
@@ -148,12 +178,30 @@ class HaloPlan:
         self.n_local, self.n_ghost = int(self.local_ids.numel()), int(self.ghost_ids.numel())
         self.recv_counts = torch.bincount(gown, minlength=world).cpu().tolist()
         self.subset = torch.cat([self.local_ids, self.ghost_ids])
-        self._n_global = pos.shape[0]
-        self.send_rows = None
-        self.send_counts = None
+        self._class_counts = None
 
     def connect(self):
         """Tell every owner which of its atoms this rank needs (two small all-to-alls per graph build)."""
+        if self._class_counts is not None:
+            # device path: every rank learns every (needer, owner) count from one all-gather of the class histograms; one host
+            # read per graph build (the split sizes of the exchanges are host arguments of the collective)
+            dev = self._order.device
+            allc = self.comm.all_gather(self._class_counts[:self.world + 1].contiguous()).cpu()   # [needer, class]
+            me = self.rank
+            self.n_local = int(allc[me, 0])
+            self.recv_counts = allc[me, 1:].tolist()           # ghosts of mine owned by r
+            self.send_counts = allc[:, 1 + me].tolist()        # atoms of mine that rank r needs
+            self.n_ghost = int(sum(self.recv_counts))
+            self.subset = self._order[:self.n_local + self.n_ghost]
+            self.local_ids, self.ghost_ids = self.subset[:self.n_local], self.subset[self.n_local:]
+            want = torch.empty(sum(self.send_counts), dtype=torch.int64, device=dev)
+            self.comm.all_to_all(want, self.ghost_ids.contiguous(), self.send_counts, self.recv_counts)
+            g2l = torch.full((self._n_global,), -1, dtype=torch.int32, device=dev)
+            g2l[self.local_ids] = torch.arange(self.n_local, device=dev, dtype=torch.int32)
+            self.send_rows32 = g2l[want]
+            self.send_rows = self.send_rows32.long()
+            self._bufs = {}
+            return self
         dev = self.subset.device
         rc = torch.tensor(self.recv_counts, dtype=torch.int64, device=dev)
         sc = torch.empty_like(rc)
@@ -228,7 +276,8 @@ class ParallelSevenNet:
         # cell-list atom order (as in B200SevenNet.calculate): local and ghost rows of a brick follow it, so the
         # gathers and the RED scatter of the convolution kernels stay L2-local; local_ids are mapped back below
         perm = None
-        if pos.shape[0] >= self.model.SORT_MIN_ATOMS:
+        device_path = pos.is_cuda and all(bool(b) for b in np.asarray(pbc).reshape(3))
+        if not device_path and pos.shape[0] >= self.model.SORT_MIN_ATOMS:
             perm = self.model.cell_order(pos, cell, cutoff)
             pos, types = pos[perm].contiguous(), types[perm].contiguous()
         plan = HaloPlan(pos, cell, pbc, cutoff, self.grid, self.rank, self.comm).connect()
