@@ -712,6 +712,9 @@ def main():
                              note=('N = 1 at the per-GPU cell size of the N > 1 runs' if world == 1 else
                                    f'strong scaling: one {n_alt}-atom cell on {world} GPUs'))
             pos2_d = types2_d = None
+        elif world > 1 and n_alt == n_total:
+            line['strong_scaling'] = dict(n_atoms=n_total, value=value, unit=UNIT, ms_per_step=step_ms, steps=a.steps,
+                                          note='the weak-scaling run at this N is the strong-scaling cell')
     except Exception as ex:
         line['scaling_base' if world == 1 else 'strong_scaling'] = {'error': repr(ex)[:300]}
     if not a.no_finetune:
