@@ -149,3 +149,145 @@ def to_graphs(structures, cutoff, chemical_species, device):
                        'force_of_atoms': torch.tensor(st['forces'], dtype=torch.float32),
                        'stress': torch.tensor(st['stress'], dtype=torch.float32), 'info': st['info']})
     return graphs
+
+
+# ---- extended XYZ (the reference's default data format, dataload.py:192-196 via ase.io.read) ---------------------------------
+_KV = re.compile(r'(\w+)\s*=\s*("[^"]*"|\S+)')
+
+
+def _parse_index(index, n):
+    """ASE index strings: ':', 'a:b', 'a:b:c', '-1', or an int / slice."""
+    if isinstance(index, slice):
+        return range(n)[index]
+    if isinstance(index, int):
+        return [range(n)[index]]
+    parts = str(index).split(':')
+    if len(parts) == 1:
+        return [range(n)[int(parts[0])]]
+    vals = [int(p) if p.strip() else None for p in parts]
+    return range(n)[slice(*vals)]
+
+
+def read_extxyz(path, index=':'):
+    """Frames of an extended-XYZ file as the dicts ``read_outcar`` returns.  Comment-line keys (case-insensitive): ``Lattice``
+    (9 numbers, rows = lattice vectors), ``Properties`` (species:S:1:pos:R:3[:forces:R:3] ...), ``energy`` / ``free_energy``
+    (the reference prefers the force-consistent free energy, dataload.py:94-97), ``stress`` (9 numbers, ASE's sign = minus
+    VASP's; the label keeps VASP's sign and the order xx yy zz xy yz zx as dataload.py:99-106 ends up with), ``pbc``."""
+    with open(path, 'r') as f:
+        lines = f.readlines()
+    frames, i = [], 0
+    while i < len(lines):
+        if not lines[i].strip():
+            i += 1
+            continue
+        n = int(lines[i].split()[0])
+        info = {k.lower(): v.strip('"') for k, v in _KV.findall(lines[i + 1])}
+        props = info.get('properties', 'species:S:1:pos:R:3').split(':')
+        cols, c = {}, 0
+        for name, kind, cnt in zip(props[0::3], props[1::3], props[2::3]):
+            cols[name.lower()] = (c, int(cnt), kind)
+            c += int(cnt)
+        rows = [ln.split() for ln in lines[i + 2:i + 2 + n]]
+        sp = cols.get('species', cols.get('z'))
+        if sp is None or 'pos' not in cols:
+            raise ValueError(f'{path}: Properties without species / pos')
+        if sp[2] == 'S':
+            numbers = np.array([ATOMIC_NUMBER[r[sp[0]]] for r in rows])
+        else:
+            numbers = np.array([int(r[sp[0]]) for r in rows])
+        take = lambda key: np.array([[float(v) for v in r[cols[key][0]:cols[key][0] + cols[key][1]]] for r in rows])  # noqa: E731
+        fkey = 'forces' if 'forces' in cols else ('force' if 'force' in cols else None)
+        cell = np.array([float(v) for v in info['lattice'].split()]).reshape(3, 3) if 'lattice' in info else np.zeros((3, 3))
+        pbc = ([v.upper().startswith('T') for v in info['pbc'].split()] if 'pbc' in info else [bool(np.any(cell))] * 3)
+        energy = float(info['free_energy']) if 'free_energy' in info else (float(info['energy']) if 'energy' in info else float('nan'))
+        if 'stress' in info:
+            s = -np.array([float(v) for v in info['stress'].split()]).reshape(3, 3)
+            stress = np.array([s[0, 0], s[1, 1], s[2, 2], s[0, 1], s[1, 2], s[2, 0]])
+        else:
+            stress = np.full(6, np.nan)
+        frames.append(dict(numbers=numbers, pos=take('pos'), cell=cell, energy=energy,
+                           forces=take(fkey) if fkey else np.full((n, 3), np.nan), stress=stress, pbc=pbc,
+                           info={'data_from': 'extxyz', 'file': os.path.abspath(path)}))
+        i += 2 + n
+    return [frames[k] for k in _parse_index(index, len(frames))]
+
+
+def write_extxyz(path, structures):
+    """The inverse of ``read_extxyz`` (ASE conventions: stress = minus VASP's, full 3x3)."""
+    with open(path, 'w') as f:
+        for st in structures:
+            n = len(st['numbers'])
+            lat = ' '.join(repr(float(v)) for v in np.asarray(st['cell']).reshape(-1))
+            head = f'Lattice="{lat}" Properties=species:S:1:pos:R:3:forces:R:3 energy={float(st["energy"])!r} '
+            if not np.isnan(np.asarray(st['stress'], float)).any():
+                xx, yy, zz, xy, yz, zx = (-float(v) for v in st['stress'])
+                head += 'stress="' + ' '.join(repr(v) for v in (xx, xy, zx, xy, yy, yz, zx, yz, zz)) + '" '
+            head += 'pbc="' + ' '.join('T' if b else 'F' for b in st['pbc']) + '"'
+            f.write(f'{n}\n{head}\n')
+            for z, p, fr in zip(st['numbers'], st['pos'], st['forces']):
+                f.write(f'{CHEMICAL_SYMBOLS[int(z)]} ' + ' '.join(repr(float(v)) for v in list(p) + list(fr)) + '\n')
+
+
+# ---- checkpoints (trainer.py:98-107 get_checkpoint_dict, scripts/processing_epoch.py:34-40, util.py:186-231) -----------------
+def config_from_reference(config):
+    """The reference's checkpoint ``config`` (keys of sevenn/_keys.py) -> the keyword dict ``nn.build_E3_equivariant_model``
+    reads.  Raises for model options the CUDA path does not implement instead of building something else silently."""
+    c = dict(config)
+    rb, cf = dict(c.get('radial_basis', {})), dict(c.get('cutoff_function', {}))
+    if rb.get('radial_basis_name', 'bessel') != 'bessel':
+        raise ValueError('B200 path: only the Bessel radial basis')
+    if c.get('is_parity', False):
+        raise ValueError('B200 path: is_parity=True (odd irreps) is not implemented')
+    if c.get('interaction_type', 'nequip') != 'nequip':
+        raise ValueError("B200 path: interaction_type 'nequip' only")
+    name = cf.get('cutoff_function_name', 'poly_cut')
+    out = dict(cutoff=float(c['cutoff']), num_species=int(c.get('_number_of_species', len(c.get('chemical_species', [])))),
+               lmax=int(c['lmax']), num_convolution_layer=int(c['num_convolution_layer']),
+               bessel_basis_num=int(rb.get('bessel_basis_num', 8)),
+               cutoff_function=({'name': 'XPLOR', 'cutoff_on': float(cf['cutoff_on'])} if name.upper() == 'XPLOR'
+                                else {'name': 'poly_cut', 'poly_cut_p_value': cf.get('poly_cut_p_value', 6)}),
+               weight_nn_hidden_neurons=list(c.get('weight_nn_hidden_neurons', [64, 64])),
+               self_connection_type=c.get('self_connection_type', 'nequip'),
+               use_species_wise_shift_scale=bool(c.get('use_species_wise_shift_scale', False)),
+               train_shift_scale=bool(c.get('train_shift_scale', False)), train_denominator=bool(c.get('train_denominator', False)),
+               use_bias_in_linear=bool(c.get('use_bias_in_linear', False)), normalize_sph=bool(c.get('_normalize_sph', True)))
+    tolist = lambda v: v.tolist() if hasattr(v, 'tolist') else v   # noqa: E731
+    for k in ('conv_denominator', 'shift', 'scale'):
+        if k in c:
+            out[k] = tolist(c[k])
+    if c.get('irreps_manual'):
+        out['irreps_manual'] = list(c['irreps_manual'])
+    else:   # model_build.py:300-334 with is_parity False: channel x (0e .. lmax e), scalars only after the last layer
+        ch, lm, nl = int(c['channel']), int(c['lmax']), int(c['num_convolution_layer'])
+        mid = '+'.join(f'{ch}x{l}e' for l in range(lm + 1))
+        out['irreps_manual'] = [f'{ch}x0e'] + [mid] * (nl - 1) + [f'{ch}x0e']
+    return out
+
+
+def checkpoint_dict(model, optimizer=None, scheduler=None, config=None, epoch=None):
+    """What the reference writes to checkpoint_{epoch}.pth: model / optimizer / scheduler state dicts + config + epoch."""
+    m = model.module if hasattr(model, 'module') else model
+    out = {'model_state_dict': m.state_dict()}
+    if optimizer is not None:
+        out['optimizer_state_dict'] = optimizer.state_dict()
+    if scheduler is not None:
+        out['scheduler_state_dict'] = scheduler.state_dict()
+    if config is not None:
+        out['config'] = config
+    if epoch is not None:
+        out['epoch'] = epoch
+    return out
+
+
+def model_from_checkpoint(checkpoint, device='cuda'):
+    """``sevenn.util.model_from_checkpoint``: a checkpoint file or dict -> (model built from the B200 twins, config).  Every
+    key of ``model_state_dict`` must have a twin parameter (strict)."""
+    from . import nn as b200nn
+    if isinstance(checkpoint, str):
+        checkpoint = torch.load(checkpoint, map_location='cpu', weights_only=False)
+    if not isinstance(checkpoint, dict) or 'model_state_dict' not in checkpoint or 'config' not in checkpoint:
+        raise ValueError('checkpoint must be a path or a dict with model_state_dict and config')
+    model = b200nn.build_E3_equivariant_model(config_from_reference(checkpoint['config']))
+    missing = model.load_state_dict(checkpoint['model_state_dict'], strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    return model.to(device), checkpoint['config']

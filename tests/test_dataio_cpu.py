@@ -87,3 +87,54 @@ def test_shipped_example_data_parses():
             assert s['pos'].shape == (n, 3) and s['forces'].shape == (n, 3) and set(s['numbers'].tolist()) <= {72, 8}
             assert np.abs(s['forces'].sum(0)).max() < 1e-3 and np.isfinite(s['energy']) and np.isfinite(s['stress']).all()
             assert abs(np.linalg.det(s['cell'])) / n > 5.0             # A^3 per atom
+
+
+def test_extxyz_round_trip_and_conventions(tmp_path):
+    """ASE-free extended-XYZ reader (the reference's default data format, dataload.py:192-196 through ase.io.read): frames,
+    index strings, and the label conventions of dataload.py:94-106 (free energy preferred; stress = minus ASE's, xx yy zz xy yz zx)."""
+    import numpy as np
+    from sevennet_finetuning_b200 import dataio
+    rng = np.random.default_rng(0)
+    frames = [dict(numbers=np.array([72, 8, 8, 72]), pos=rng.uniform(0, 5, (4, 3)), cell=np.eye(3) * 5 + rng.normal(0, 0.1, (3, 3)),
+                   energy=-30.0 - k, forces=rng.normal(0, 1, (4, 3)), stress=rng.normal(0, 0.01, 6), pbc=[True, True, True], info={})
+              for k in range(3)]
+    p = str(tmp_path / 'a.extxyz')
+    dataio.write_extxyz(p, frames)
+    back = dataio.read_extxyz(p)
+    assert len(back) == 3
+    for a, b in zip(frames, back):
+        assert (a['numbers'] == b['numbers']).all() and b['pbc'] == [True] * 3
+        for k in ('pos', 'cell', 'forces', 'stress'):
+            assert np.array_equal(np.asarray(a[k], float), b[k]), k
+        assert a['energy'] == b['energy']
+    assert dataio.read_extxyz(p, '-1')[0]['energy'] == -32.0 and [f['energy'] for f in dataio.read_extxyz(p, '1:')] == [-31.0, -32.0]
+    # a hand-written frame as ASE writes it: free_energy wins over energy, 3x3 stress with ASE's sign, Z column, no forces
+    q = str(tmp_path / 'b.xyz')
+    with open(q, 'w') as f:
+        f.write('2\nLattice="4.0 0.0 0.0 0.0 4.0 0.0 0.0 0.0 4.0" Properties=species:S:1:pos:R:3:Z:I:1 energy=-1.0 free_energy=-1.25 '
+                'stress="0.1 0.4 0.6 0.4 0.2 0.5 0.6 0.5 0.3" pbc="T T F"\nSi 0.0 0.0 0.0 14\nO 1.0 1.0 1.0 8\n')
+    (fr,) = dataio.read_extxyz(q)
+    assert fr['energy'] == -1.25 and fr['pbc'] == [True, True, False] and list(fr['numbers']) == [14, 8]
+    assert np.allclose(fr['stress'], [-0.1, -0.2, -0.3, -0.4, -0.5, -0.6]) and np.isnan(fr['forces']).all()
+
+
+def test_checkpoint_config_mapping():
+    """The reference's checkpoint config (keys of sevenn/_keys.py, values of pretrained_potentials/.../pre_train.yaml) maps to the
+    twin builder's keywords; options the CUDA path does not implement raise."""
+    import pytest
+    from sevennet_finetuning_b200 import dataio
+    ref_cfg = {'chemical_species': ['Hf', 'O'], '_number_of_species': 2, 'cutoff': 5.0, 'channel': 128, 'is_parity': False, 'lmax': 2,
+               'num_convolution_layer': 5,
+               'irreps_manual': ['128x0e'] + ['128x0e+64x1e+32x2e'] * 4 + ['128x0e'], 'weight_nn_hidden_neurons': [64, 64],
+               'radial_basis': {'radial_basis_name': 'bessel', 'bessel_basis_num': 8},
+               'cutoff_function': {'cutoff_function_name': 'XPLOR', 'cutoff_on': 4.5}, 'conv_denominator': 35.989574,
+               'train_shift_scale': True, 'train_denominator': False, 'self_connection_type': 'linear', 'shift': [0.1, 0.2],
+               'scale': [1.5, 1.6], 'use_species_wise_shift_scale': True}
+    c = dataio.config_from_reference(ref_cfg)
+    assert c['num_species'] == 2 and c['cutoff_function'] == {'name': 'XPLOR', 'cutoff_on': 4.5} and c['train_shift_scale'] is True
+    assert c['irreps_manual'][1] == '128x0e+64x1e+32x2e' and c['bessel_basis_num'] == 8 and c['shift'] == [0.1, 0.2]
+    d = dict(ref_cfg)
+    d.pop('irreps_manual')
+    assert dataio.config_from_reference(d)['irreps_manual'] == ['128x0e'] + ['128x0e+128x1e+128x2e'] * 4 + ['128x0e']
+    with pytest.raises(ValueError):
+        dataio.config_from_reference(dict(ref_cfg, is_parity=True))

@@ -57,3 +57,43 @@ def test_outcar_to_batch_to_model(gold, weights, tmp_path):
     e = out['inferred_total_energy'].detach().cpu().numpy()
     # same structure twice; energy of the golden structure up to the 5-decimal rounding of the printed positions
     assert abs(e[0] - e[1]) < 1e-3 and abs(e[0] - float(g['o64_energy'])) / 96 < 5e-4
+
+
+def test_checkpoint_dict_round_trip(weights, gold, tmp_path):
+    """checkpoint_{epoch}.pth as the reference writes it (trainer.py:98-107 + processing_epoch.py:34-40) -> model built from the
+    twins by `model_from_checkpoint` (util.py:186-231): same E/F/S as the golden vectors; optimizer state restored."""
+    import torch
+    from sevennet_finetuning_b200 import dataio, nn as b200nn
+    ref_cfg = {'chemical_species': 'auto', '_number_of_species': 89, 'cutoff': 5.0, 'channel': 128, 'is_parity': False, 'lmax': 2,
+               'num_convolution_layer': 5, 'irreps_manual': ['128x0e'] + ['128x0e+64x1e+32x2e'] * 4 + ['128x0e'],
+               'weight_nn_hidden_neurons': [64, 64], 'radial_basis': {'radial_basis_name': 'bessel', 'bessel_basis_num': 8},
+               'cutoff_function': {'cutoff_function_name': 'XPLOR', 'cutoff_on': 4.5},
+               'conv_denominator': float(weights['0_convolution.denominator'][0]), 'train_shift_scale': False,
+               'train_denominator': False, 'self_connection_type': 'linear', 'shift': weights['rescale_atomic_energy.shift'].tolist(),
+               'scale': weights['rescale_atomic_energy.scale'].tolist(), 'use_species_wise_shift_scale': True}
+    m = b200nn.build_E3_equivariant_model(dataio.config_from_reference(ref_cfg))
+    m.load_state_dict({k: torch.tensor(v) for k, v in weights.items()})
+    opt = torch.optim.Adam([p for p in m.parameters() if p.requires_grad], lr=1e-4)
+    path = str(tmp_path / 'checkpoint_3.pth')
+    torch.save(dataio.checkpoint_dict(m, opt, None, ref_cfg, epoch=3), path)
+    ck = torch.load(path, map_location='cpu', weights_only=False)
+    assert set(ck) == {'model_state_dict', 'optimizer_state_dict', 'config', 'epoch'} and ck['epoch'] == 3
+    m2, cfg = dataio.model_from_checkpoint(path, device='cuda:0')
+    assert cfg['cutoff'] == 5.0
+    opt2 = torch.optim.Adam([p for p in m2.parameters() if p.requires_grad], lr=1.0)
+    opt2.load_state_dict(ck['optimizer_state_dict'])
+    assert opt2.param_groups[0]['lr'] == 1e-4
+    import numpy as np
+    from oracle.graph import radius_graph
+    g = gold('si216.npz')
+    ei, S, D = radius_graph(g['pos'], g['cell'], [True] * 3, 5.0)
+    dev = torch.device('cuda:0')
+    m2.eval()
+    m2.set_is_batch_data(False)
+    out = m2({'x': torch.tensor(g['types'], dtype=torch.long, device=dev), 'edge_index': torch.tensor(ei, device=dev),
+              'edge_vec': torch.tensor(D, dtype=torch.float32, device=dev).requires_grad_(True),
+              'num_atoms': torch.tensor(len(g['pos']), device=dev),
+              'cell_volume': torch.tensor(abs(np.linalg.det(g['cell'])), dtype=torch.float32, device=dev),
+              'batch': torch.zeros(len(g['pos']), dtype=torch.long, device=dev)})
+    assert abs(float(out['inferred_total_energy'].detach()) - float(g['o64_energy'])) / len(g['pos']) <= 1e-6
+    assert np.abs(out['inferred_force'].detach().cpu().numpy() - g['o64_force']).max() <= 1e-5
