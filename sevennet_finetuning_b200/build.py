@@ -23,6 +23,7 @@ def _stale():
 
 def build(force=False, verbose=False):
     if not force and not _stale():
+        build_torch_ops()
         return LIB
     nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
     objs = []
@@ -47,7 +48,28 @@ def build(force=False, verbose=False):
     # the native caller: plain C++ against include/sevennet_b200.h, no torch, no Python
     subprocess.check_call([nvcc, '-O2', '-std=c++17', os.path.join(CSRC, 'pair_driver.cpp'), '-o', DRIVER, '-L' + HERE,
                            '-lsevennet_b200', '-lcudart', '-Xlinker', '-rpath', '-Xlinker', '$ORIGIN'])
+    build_torch_ops()
     return LIB
+
+
+TORCH_OPS = os.path.join(HERE, 'libb200_torch_ops.so')   # torch.ops.b200.* for TorchScript deployment (csrc/torch_ops.cpp)
+
+
+def build_torch_ops(force=False):
+    """g++ against the torch headers; links libsevennet_b200.so (rpath $ORIGIN) and the torch libraries."""
+    src = os.path.join(CSRC, 'torch_ops.cpp')
+    if not force and os.path.exists(TORCH_OPS) and os.path.getmtime(TORCH_OPS) > max(os.path.getmtime(src), os.path.getmtime(LIB)):
+        return TORCH_OPS
+    import torch
+    from torch.utils import cpp_extension as ce
+    inc = [f'-I{p}' for p in ce.include_paths()] + ['-I/usr/local/cuda/include']
+    libdir = os.path.join(os.path.dirname(torch.__file__), 'lib')
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    cmd = ['g++', '-O2', '-std=c++17', '-fPIC', '-shared', f'-D_GLIBCXX_USE_CXX11_ABI={abi}', src, '-o', TORCH_OPS] + inc + [
+        f'-L{HERE}', '-lsevennet_b200', f'-L{libdir}', '-lc10', '-lc10_cuda', '-ltorch_cpu', '-ltorch_cuda', '-ltorch',
+        '-L/usr/local/cuda/lib64', '-lcudart', '-Wl,-rpath,$ORIGIN', f'-Wl,-rpath,{libdir}']
+    subprocess.check_call(cmd)
+    return TORCH_OPS
 
 
 if __name__ == '__main__':

@@ -69,3 +69,26 @@ def test_cpu_tensor_is_an_error_not_a_fallback():
     from sevennet_finetuning_b200 import ops
     with pytest.raises(RuntimeError):
         ops.gate_fwd(4, 0, 0, torch.zeros(3, 4))
+
+
+def test_torch_operator_library_registers_the_deployment_op():
+    """csrc/torch_ops.cpp: the C++-registered dispatcher operator a deployed TorchScript file calls; scripting the deployment
+    module needs no GPU (the operator is resolved, not run) and the saved file carries the reference's extra files."""
+    import tempfile
+    import numpy as np
+    import torch
+    from sevennet_finetuning_b200 import build, deploy
+    build.build_torch_ops()
+    deploy.ops_library()
+    schema = str(torch.ops.b200.sevennet_efs.default._schema)
+    assert 'Tensor x, Tensor pos, Tensor edge_index, Tensor pbc_shift, Tensor cell, Tensor cell_volume, Tensor flat' in schema
+    assert 'CUDA' in torch._C._dispatch_dump('b200::sevennet_efs')
+    w = dict(np.load(os.path.join(ROOT, 'tests', 'golden', 'sevennet0_weights.npz')))
+    with tempfile.TemporaryDirectory() as d:
+        pt = deploy.deploy(w, None, os.path.join(d, 'm'))
+        extra = {'chemical_symbols_to_index': '', 'cutoff': '', 'num_species': '', 'dtype': '', 'model_type': ''}
+        m = torch.jit.load(pt, _extra_files=extra)
+        assert 'b200.sevennet_efs' in m.code or 'b200::sevennet_efs' in str(m.graph)
+        assert extra['cutoff'] in (b'5.0', '5.0') and len((extra['chemical_symbols_to_index'].decode()
+                                                            if isinstance(extra['chemical_symbols_to_index'], bytes)
+                                                            else extra['chemical_symbols_to_index']).split()) == 89
