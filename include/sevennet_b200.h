@@ -146,6 +146,22 @@ int b200_gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const fl
 int b200_gate_bwd2(int ns, int m1, int m2, int n_nodes, const float* in, const float* d_out, const float* a, float* dx,
                    float* dg, void* stream);
 
+/* ---- train-mode radial weights from a table: sevenn/nn/convolution.py:97-106 (weight = weight_nn(edge_embedding)) under
+ *      sevenn/train/trainer.py:173-186.  weight_nn is a function of the edge length alone; the caller evaluates it on the
+ *      n_grid + 1 grid points r = i h (differentiably, in its own framework) and passes per-interval cubic coefficients
+ *      P[n_grid, 4, wn] = (a, b, c, d): w(t) = a + b t + c t^2 + d t^3, t = r * inv_h - i (inv_h = 1 / h as the fp32 number the grid points were generated with: r_i = i / inv_h).  m = order of the derivative in r
+ *      (0..3; 4 gives zeros).  `order`: edge ids sorted by interval (NULL = natural order; locality only).
+ *      The three maps are closed under differentiation (csrc/table_train.cu). --------------------------------------- */
+/* out[e, k] = coef[e] * d^m w_k / d r^m (r[e])      (coef NULL = 1) */
+int b200_table_interp(int m, int wn, int64_t n_edges, float inv_h, int n_grid, const float* P, const float* r,
+                      const int32_t* order, const float* coef, float* out, void* stream);
+/* out[e] = sum_k g[e, k] * d^m w_k / d r^m (r[e]) */
+int b200_table_dot(int m, int wn, int64_t n_edges, float inv_h, int n_grid, const float* P, const float* r, const int32_t* order,
+                   const float* g, float* out, void* stream);
+/* G[n_grid, 4, wn] = d (sum_e coef[e] sum_k g[e, k] d^m w_k / d r^m (r[e])) / d P     (overwritten; coef NULL = 1) */
+int b200_table_scatter(int m, int wn, int64_t n_edges, float inv_h, int n_grid, const float* g, const float* coef, const float* r,
+                       const int32_t* order, float* G, void* stream);
+
 /* ---- node embedding: sevenn/nn/node_embedding.py:39-48 + nn/linear.py:37-44 (one-hot . W / sqrt(n_species)) */
 int b200_embed_fwd(int n_nodes, int n_species, int dim, const int32_t* types, const float* W, float* x, void* stream);
 

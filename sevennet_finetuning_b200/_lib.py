@@ -68,6 +68,9 @@ SIGNATURES = {
     'b200_gate_fwd': (_i, [_i, _i, _i, _i, _vp, _vp, _vp]),
     'b200_gate_bwd': (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     'b200_gate_bwd2': (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_table_interp': (_i, [_i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_table_dot': (_i, [_i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_table_scatter': (_i, [_i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_embed_fwd': (_i, [_i, _i, _i, _vp, _vp, _vp, _vp]),
     'b200_rescale_fwd': (_i, [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     'b200_colsum': (_i, [_i, _i, _vp, _vp, _vp]),

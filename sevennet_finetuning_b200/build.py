@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libsevennet_b200.so')
 DRIVER = os.path.join(HERE, 'b200_pair_driver')   # stand-alone C++ caller of the C-ABI (csrc/pair_driver.cpp)
-SOURCES = ['capi.cu', 'conv.cu', 'conv_pair.cu', 'edge.cu', 'radial.cu', 'radial_tc.cu', 'radial_table.cu', 'linear.cu', 'linear_tc.cu', 'node.cu', 'graph.cu', 'engine.cu']
+SOURCES = ['capi.cu', 'conv.cu', 'conv_pair.cu', 'edge.cu', 'radial.cu', 'radial_tc.cu', 'radial_table.cu', 'table_train.cu', 'linear.cu', 'linear_tc.cu', 'node.cu', 'graph.cu', 'engine.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '--use_fast_math=false', '-Xcompiler', '-fPIC', '-Xcompiler', '-O2']
 

@@ -143,6 +143,21 @@ int b200_gate_fwd(int ns, int m1, int m2, int n, const float* in, float* out, vo
 int b200_gate_bwd(int ns, int m1, int m2, int n, const float* in, const float* dout, float* din, void* stream) {
   return gate_bwd(ns, m1, m2, n, in, dout, din, ST(stream));
 }
+int b200_table_interp(int m, int wn, int64_t E, float inv_h, int n_grid, const float* P, const float* r, const int32_t* order,
+                      const float* coef, float* out, void* stream) {
+  B200_REQUIRE(E == 0 || (P && r && out), "table_interp: null argument");
+  return table_interp(m, wn, E, inv_h, n_grid, P, r, order, coef, out, ST(stream));
+}
+int b200_table_dot(int m, int wn, int64_t E, float inv_h, int n_grid, const float* P, const float* r, const int32_t* order,
+                   const float* g, float* out, void* stream) {
+  B200_REQUIRE(E == 0 || (P && r && g && out), "table_dot: null argument");
+  return table_dot(m, wn, E, inv_h, n_grid, P, r, order, g, out, ST(stream));
+}
+int b200_table_scatter(int m, int wn, int64_t E, float inv_h, int n_grid, const float* g, const float* coef, const float* r,
+                       const int32_t* order, float* G, void* stream) {
+  B200_REQUIRE(G && (E == 0 || (g && r)), "table_scatter: null argument");
+  return table_scatter(m, wn, E, inv_h, n_grid, g, coef, r, order, G, ST(stream));
+}
 int b200_gate_bwd2(int ns, int m1, int m2, int n, const float* in, const float* dout, const float* a, float* dx, float* dg,
                    void* stream) {
   B200_REQUIRE(n == 0 || (in && dout && a && dx && dg), "gate_bwd2: null argument");

@@ -83,6 +83,14 @@ int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float*
 int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const float* dy, float* dW, int accumulate,
                         cudaStream_t st);
 
+// train-mode radial weights from per-interval cubic coefficients P[n_grid, 4, wn] (table_train.cu)
+int table_interp(int m, int wn, long long E, float inv_h, int n_grid, const float* P, const float* r, const int* order,
+                 const float* coef, float* out, cudaStream_t st);
+int table_dot(int m, int wn, long long E, float inv_h, int n_grid, const float* P, const float* r, const int* order,
+              const float* g, float* out, cudaStream_t st);
+int table_scatter(int m, int wn, long long E, float inv_h, int n_grid, const float* g, const float* coef, const float* r,
+                  const int* order, float* G, cudaStream_t st);
+
 int gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, cudaStream_t st);
 int gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, float* din, cudaStream_t st);
 int gate_bwd2(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, const float* a, float* dx,

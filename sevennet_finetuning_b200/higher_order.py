@@ -275,6 +275,76 @@ class EmbedF(Function):
         return None, dW.reshape(-1), None, None
 
 
+# ---- train-mode radial weights from a table (csrc/table_train.cu; sevenn/nn/convolution.py:97-106) ------------------------
+# P[n_grid, 4, wn]: per-interval cubic coefficients of weight_nn as a function of the edge length, built by the caller with
+# differentiable tensor operations on the grid points.  tab = (inv_h, order): 1 / grid step (fp32-exact), edge ids sorted by interval (int32).
+class TabInterp(Function):
+    """[E, wn] = coef[e] * d^m w / d r^m (r[e])   (coef None = 1)."""
+
+    @staticmethod
+    def forward(ctx, P, r, coef, m, tab):
+        ctx.save_for_backward(P, r, coef)
+        ctx.m, ctx.tab = m, tab
+        return ops.table_interp(m, _c(P.detach()), tab[0], _c(r.detach()), tab[1], None if coef is None else _c(coef.detach()))
+
+    @staticmethod
+    def backward(ctx, g):
+        P, r, coef = ctx.saved_tensors
+        dP = dr = dc = None
+        if ctx.needs_input_grad[0] and not force_pass.active:
+            dP = TabScatter.apply(g, coef, r, ctx.m, P.shape[0], ctx.tab)
+        if ctx.needs_input_grad[1]:
+            dr = TabDot.apply(P, r, g, ctx.m + 1, ctx.tab)
+            if coef is not None:
+                dr = dr * coef
+        if coef is not None and ctx.needs_input_grad[2]:
+            dc = TabDot.apply(P, r, g, ctx.m, ctx.tab)
+        return dP, dr, dc, None, None
+
+
+class TabDot(Function):
+    """[E] = sum_k g[e, k] d^m w_k / d r^m (r[e])."""
+
+    @staticmethod
+    def forward(ctx, P, r, g, m, tab):
+        ctx.save_for_backward(P, r, g)
+        ctx.m, ctx.tab = m, tab
+        return ops.table_dot(m, _c(P.detach()), tab[0], _c(r.detach()), _c(g.detach()), tab[1])
+
+    @staticmethod
+    def backward(ctx, a):
+        P, r, g = ctx.saved_tensors
+        dP = TabScatter.apply(g, a, r, ctx.m, P.shape[0], ctx.tab) if ctx.needs_input_grad[0] and not force_pass.active else None
+        dr = a * TabDot.apply(P, r, g, ctx.m + 1, ctx.tab) if ctx.needs_input_grad[1] else None
+        dg = TabInterp.apply(P, r, a, ctx.m, ctx.tab) if ctx.needs_input_grad[2] else None
+        return dP, dr, dg, None, None
+
+
+class TabScatter(Function):
+    """[n_grid, 4, wn] = d (sum_e coef[e] sum_k g[e, k] d^m w_k / d r^m (r[e])) / d P  (coef None = 1)."""
+
+    @staticmethod
+    def forward(ctx, g, coef, r, m, n_grid, tab):
+        ctx.save_for_backward(g, coef, r)
+        ctx.m, ctx.tab = m, tab
+        return ops.table_scatter(m, n_grid, tab[0], _c(g.detach()), _c(r.detach()), tab[1],
+                                 None if coef is None else _c(coef.detach()))
+
+    @staticmethod
+    def backward(ctx, A):
+        g, coef, r = ctx.saved_tensors
+        dg = dc = dr = None
+        if ctx.needs_input_grad[0]:
+            dg = TabInterp.apply(A, r, coef, ctx.m, ctx.tab)
+        if coef is not None and ctx.needs_input_grad[1]:
+            dc = TabDot.apply(A, r, g, ctx.m, ctx.tab)
+        if ctx.needs_input_grad[2]:
+            dr = TabDot.apply(A, r, g, ctx.m + 1, ctx.tab)
+            if coef is not None:
+                dr = dr * coef
+        return dg, dc, dr, None, None, None
+
+
 def radial_mlp(emb, W0, W1, W2, descs):
     """weight_nn (e3nn FullyConnectedNet [nb, h1, h2, wn], c*silu; sevenn/nn/convolution.py:97-106) as a chain of the
     closed families above: a dense layer is the l = 0 block of an irreps linear, the activation a gate with scalars only."""

@@ -97,6 +97,12 @@ def _num_structures(data):
     return int(data['batch'].max()) + 1
 
 
+# train() mode: weight_nn through a table over the edge length rebuilt from the current parameters every forward
+# (csrc/table_train.cu) instead of one network evaluation per edge.  B200_TRAIN_TABLE=0 restores the per-edge network.
+import os as _os
+_TRAIN_TABLE = _os.environ.get('B200_TRAIN_TABLE', '1') != '0'
+
+
 def _second_order(module):
     """train() mode with grad enabled: the forces must stay differentiable (force_output.py:168 create_graph=self.training)."""
     return module.training and torch.is_grad_enabled()
@@ -251,6 +257,38 @@ class EdgeEmbedding(nn.Module):
                               float(c.cutoff_on), 6.0)
         return EdgeParams(b.num_basis, B200_CUTOFF_POLY, int(self.spherical.normalize), float(c.cutoff_length), 0.0, float(c.p))
 
+    def radial_grid(self, device):
+        """Grid of the train-mode radial table (csrc/table_train.cu): (inv_h, n_grid, B, dB) with B[i, n] = bessel_n(r_i) *
+        cutoff(r_i) and dB = dB / dr on the n_grid + 1 points r_i = i / inv_h, float64, differentiable with respect to the
+        Bessel frequencies.  edge_embedding.py:80-116 (2/r_c sin(k_n r)/r), :119-145 (polynomial), :148-173 (XPLOR).  The
+        spacing is about r_c / 4000, adjusted so that the XPLOR switching radius is a grid point (the functions are smooth
+        inside every interval); inv_h is an fp32 number: the kernels locate an edge with t = r * inv_h - i."""
+        c, b = self.cutoff_function, self.basis_function
+        rc = float(c.cutoff_length)
+        h = rc / 4000.0
+        r_on = float(c.cutoff_on) if isinstance(c, XPLORCutoff) else 0.0
+        if 0.0 < r_on < rc and math.floor(r_on / h + 0.5) >= 1:
+            h = r_on / math.floor(r_on / h + 0.5)
+        inv_h = float(torch.tensor(1.0 / h, dtype=torch.float32))
+        n_grid = int(math.ceil(rc * inv_h)) + 1
+        r = torch.arange(n_grid + 1, dtype=torch.float64, device=device) / inv_h
+        r[0] = 1e-6                               # sin(k r) / r at r = 0; no edge is that short
+        k = b.coeffs.to(torch.float64)
+        ur, kr = r.unsqueeze(1), r.unsqueeze(1) * k.unsqueeze(0)
+        bes = (2.0 / rc) * torch.sin(kr) / ur
+        dbes = (2.0 / rc) * (k.unsqueeze(0) * torch.cos(kr) / ur - torch.sin(kr) / (ur * ur))
+        if isinstance(c, XPLORCutoff):
+            u, v, den = rc * rc - r * r, rc * rc + 2.0 * r * r - 3.0 * r_on * r_on, (rc * rc - r_on * r_on) ** 3
+            inner = r < r_on
+            env = torch.where(inner, torch.ones_like(r), u * u * v / den)
+            denv = torch.where(inner, torch.zeros_like(r), (-4.0 * r * u * v + 4.0 * r * u * u) / den)
+        else:
+            pw, x = float(c.p), r / rc
+            c0, c1, c2 = (pw + 1.0) * (pw + 2.0) / 2.0, pw * (pw + 2.0), pw * (pw + 1.0) / 2.0
+            env = 1.0 - c0 * x ** pw + c1 * x ** (pw + 1.0) - c2 * x ** (pw + 2.0)
+            denv = (-c0 * pw * x ** (pw - 1.0) + c1 * (pw + 1.0) * x ** pw - c2 * (pw + 2.0) * x ** (pw + 1.0)) / rc
+        return inv_h, n_grid, bes * env.unsqueeze(1), dbes * env.unsqueeze(1) + bes * denv.unsqueeze(1)
+
     def forward(self, data):
         if _second_order(self):
             vec = data['edge_vec']
@@ -259,6 +297,11 @@ class EdgeEmbedding(nn.Module):
             if vec.dtype != torch.float32:
                 vec = vec.to(torch.float32)
             ln, Y, emb = ho.EdgeF.apply(vec, self.basis_function.coeffs, self._params())
+            if _TRAIN_TABLE:
+                # the convolutions read weight_nn from a table over the edge length (IrrepsConvolution._table_weights)
+                inv_h, n_grid, B, dB = self.radial_grid(vec.device)
+                data['_b200_radial_table'] = {'inv_h': inv_h, 'n_grid': n_grid, 'B': B, 'dB': dB,
+                                              'r': torch.linalg.vector_norm(vec, dim=1)}
         else:
             ln, Y, emb = _EdgeEmbedFn.apply(data['edge_vec'], self.basis_function.coeffs, self._params())
         data['edge_length'], data['edge_attr'], data['edge_embedding'] = ln, Y, emb
@@ -445,6 +488,31 @@ class IrrepsConvolution(nn.Module):
             self._den_cache = (ver, float(self.denominator.detach()))
         return self._den_cache[1]
 
+    def _table_weights(self, tab, g):
+        """weight_nn (convolution.py:97-106; e3nn FullyConnectedNet: W / sqrt(fan_in), normalize2mom silu) as a function of
+        the edge length: value and r-derivative of the network on the grid points (forward mode, float64, plain tensor
+        operations: differentiable to any order with respect to the weights and the Bessel frequencies), turned into
+        per-interval cubic Hermite coefficients, then read per edge by the kernels of csrc/table_train.cu."""
+        nn_ = self.weight_nn
+        c = 1.6791767923989418   # normalize2mom(silu)
+        z, dz = tab['B'], tab['dB']
+        for W, last in ((nn_.layer0.weight, False), (nn_.layer1.weight, False), (nn_.layer2.weight, True)):
+            W64 = W.to(torch.float64) / math.sqrt(W.shape[0])
+            z, dz = z @ W64, dz @ W64
+            if not last:
+                sg = torch.sigmoid(z)
+                z, dz = c * z * sg, c * sg * (1.0 + z * (1.0 - sg)) * dz
+        h = 1.0 / tab['inv_h']
+        v0, v1, s0, s1 = z[:-1], z[1:], h * dz[:-1], h * dz[1:]
+        dv = v1 - v0
+        P = torch.stack([v0, s0, 3.0 * dv - 2.0 * s0 - s1, s0 + s1 - 2.0 * dv], dim=1).to(torch.float32)
+        key = None if g['perm'] is None else g['perm'].data_ptr()
+        if tab.get('key', 0) != key:   # edge order of this graph: the same for every layer
+            r = tab['r'] if g['perm'] is None else tab['r'].index_select(0, g['perm'])
+            bins = (r.detach() * tab['inv_h']).to(torch.int32).clamp_(0, tab['n_grid'] - 1)
+            tab['key'], tab['r_g'], tab['order'] = key, r, torch.argsort(bins).to(torch.int32)
+        return ho.TabInterp.apply(P, tab['r_g'], None, 0, (tab['inv_h'], tab['order']))
+
     def forward(self, data):
         g = _graph_of(data)
         x = data[self.key_x]
@@ -455,10 +523,14 @@ class IrrepsConvolution(nn.Module):
             Y, emb = Y.index_select(0, g['perm']), emb.index_select(0, g['perm'])
         nn_ = self.weight_nn
         if _second_order(self):
-            hs = [nn_.layer0.weight.shape[0], nn_.layer0.weight.shape[1], nn_.layer1.weight.shape[1], self.weight_numel]
-            if self._mlp_descs is None:
-                self._mlp_descs = [ops.make_lin_desc(f'{a}x0e', f'{b}x0e') for a, b in zip(hs[:-1], hs[1:])]
-            w = ho.radial_mlp(emb, nn_.layer0.weight, nn_.layer1.weight, nn_.layer2.weight, self._mlp_descs)
+            tab = data.get('_b200_radial_table')
+            if tab is not None:
+                w = self._table_weights(tab, g)
+            else:
+                hs = [nn_.layer0.weight.shape[0], nn_.layer0.weight.shape[1], nn_.layer1.weight.shape[1], self.weight_numel]
+                if self._mlp_descs is None:
+                    self._mlp_descs = [ops.make_lin_desc(f'{a}x0e', f'{b}x0e') for a, b in zip(hs[:-1], hs[1:])]
+                w = ho.radial_mlp(emb, nn_.layer0.weight, nn_.layer1.weight, nn_.layer2.weight, self._mlp_descs)
             if self.denominator.requires_grad:   # train_denominator: keep 1/denominator in the graph
                 out = ho.ConvF.apply(x, Y, w, g, self.muls, self.lout, 1.0) / self.denominator
             else:

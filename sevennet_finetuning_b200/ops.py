@@ -354,6 +354,36 @@ def gate_bwd2(ns, m1, m2, x, gout, a):
 
 
 @_timed
+def table_interp(m, P, inv_h, r, order=None, coef=None):
+    """out[e, :] = coef[e] * d^m w / d r^m (r[e]) from per-interval cubic coefficients P[n_grid, 4, wn] on the grid r_i = i / inv_h
+    (csrc/table_train.cu)."""
+    n_grid, _, wn = P.shape
+    out = torch.empty(r.shape[0], wn, dtype=torch.float32, device=r.device)
+    check(lib().b200_table_interp(m, wn, r.shape[0], inv_h, n_grid, _p(P), _p(r), _p(order), _p(coef), _p(out), _stream()),
+          'table_interp')
+    return out
+
+
+@_timed
+def table_dot(m, P, inv_h, r, g, order=None):
+    """out[e] = sum_k g[e, k] * d^m w_k / d r^m (r[e])."""
+    n_grid, _, wn = P.shape
+    out = torch.empty(r.shape[0], dtype=torch.float32, device=r.device)
+    check(lib().b200_table_dot(m, wn, r.shape[0], inv_h, n_grid, _p(P), _p(r), _p(order), _p(g), _p(out), _stream()), 'table_dot')
+    return out
+
+
+@_timed
+def table_scatter(m, n_grid, inv_h, g, r, order=None, coef=None):
+    """G[n_grid, 4, wn]: gradient with respect to P of sum_e coef[e] sum_k g[e, k] d^m w_k / d r^m (r[e])."""
+    wn = g.shape[1]
+    G = torch.empty(n_grid, 4, wn, dtype=torch.float32, device=r.device)
+    check(lib().b200_table_scatter(m, wn, r.shape[0], inv_h, n_grid, _p(g), _p(coef), _p(r), _p(order), _p(G), _stream()),
+          'table_scatter')
+    return G
+
+
+@_timed
 def edge_embed_dk(params, vec, coeffs, demb):
     """d bessel_coeffs of the first reverse pass (deterministic two-stage sum over the edges)."""
     dk = torch.empty(params.num_basis, dtype=torch.float32, device=vec.device)
