@@ -110,6 +110,19 @@ int b200_conv_bwd_edge(int m0, int m1, int m2, int lout, int n_dst, int64_t n_ed
 int b200_conv_bwd(int m0, int m1, int m2, int lout, int n_dst, int n_src, int64_t n_edges, const int32_t* rowptr,
                   const int32_t* src, const float* x, const float* edge_attr, const float* weight, const float* d_out,
                   float denominator, float* d_weight, float* d_edge_attr, int accumulate, float* d_x, void* stream);
+/* Variants for the second-order pass of force-matching training (force_output.py:165-170 create_graph=self.training, then
+ * trainer.py:173-186 loss.backward()): path_scale[15] (HOST array, canonical path order 000 011 022 101 110 111 112 121 122 202
+ * 211 212 220 221 222; NULL = all 1) multiplies the weights of a path on the way in and its weight gradient on the way out -
+ * the variation of edge_attr acts on the l2 > 0 paths only (scale 0 on 000, 101, 202), which would otherwise be a masked copy
+ * of weight[E,wn] and of its gradient.  dw_mode 0: d_weight overwritten, 1: added into, 2: not computed (d_weight may be NULL).
+ * d_x NULL: not computed. */
+int b200_conv_fwd_scaled(int m0, int m1, int m2, int lout, int n_dst, const int32_t* rowptr, const int32_t* src,
+                         const float* x, const float* edge_attr, const float* weight, float denominator, float* out,
+                         const float* path_scale, void* stream);
+int b200_conv_bwd_scaled(int m0, int m1, int m2, int lout, int n_dst, int n_src, int64_t n_edges, const int32_t* rowptr,
+                         const int32_t* src, const float* x, const float* edge_attr, const float* weight, const float* d_out,
+                         float denominator, float* d_weight, float* d_edge_attr, int accumulate, float* d_x,
+                         const float* path_scale, int dw_mode, void* stream);
 /* d x[n_src,x_dim]; rrowptr[n_src+1] / eid_by_src[E]: CSR of the same edges sorted by source, dst[E] = edge_index[0] */
 int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* rrowptr, const int32_t* eid_by_src,
                     const int32_t* dst, const float* d_out, const float* edge_attr, const float* weight,

@@ -62,6 +62,8 @@ SIGNATURES = {
     'b200_conv_fwd': (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp]),
     'b200_conv_bwd_edge': (_i, [_i, _i, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _i, _vp]),
     'b200_conv_bwd': (_i, [_i, _i, _i, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _i, _vp, _vp]),
+    'b200_conv_bwd_scaled': (_i, [_i, _i, _i, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _i, _vp, _vp, _i, _vp]),
+    'b200_conv_fwd_scaled': (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp]),
     'b200_conv_bwd_x': (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp]),
     'b200_irreps_linear': (_i, [_P(LinDesc), _i, _vp, _vp, _vp, _i, _i, _vp]),
     'b200_irreps_linear_wgrad': (_i, [_P(LinDesc), _i, _vp, _vp, _vp, _i, _vp]),

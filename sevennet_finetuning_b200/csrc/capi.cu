@@ -119,6 +119,24 @@ int b200_conv_bwd(int m0, int m1, int m2, int lout, int n_dst, int n_src, int64_
   fill_conv_desc(m0, m1, m2, lout, d);
   return conv_bwd_edge_x(d, n_dst, n_src, (int)E, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, dx, ST(stream));
 }
+int b200_conv_fwd_scaled(int m0, int m1, int m2, int lout, int n_dst, const int32_t* rowptr, const int32_t* src, const float* x,
+                         const float* Y, const float* w, float denom, float* out, const float* path_scale, void* stream) {
+  B200_REQUIRE(lout == 0 || lout == 2, "conv_fwd_scaled: lout must be 0 or 2");
+  B200_REQUIRE(rowptr && out, "conv_fwd_scaled: null argument");
+  ConvDesc d;
+  fill_conv_desc(m0, m1, m2, lout, d);
+  return conv_fwd_scaled(d, n_dst, rowptr, src, x, Y, w, denom, out, path_scale, ST(stream));
+}
+int b200_conv_bwd_scaled(int m0, int m1, int m2, int lout, int n_dst, int n_src, int64_t E, const int32_t* rowptr,
+                         const int32_t* src, const float* x, const float* Y, const float* w, const float* gout, float denom,
+                         float* dw, float* dY, int accumulate, float* dx, const float* path_scale, int dw_mode, void* stream) {
+  B200_REQUIRE(lout == 0 || lout == 2, "conv_bwd_scaled: lout must be 0 or 2");
+  B200_REQUIRE(dY != nullptr, "conv_bwd_scaled: d_edge_attr is NULL");   // d_x NULL: not computed
+  ConvDesc d;
+  fill_conv_desc(m0, m1, m2, lout, d);
+  return conv_bwd_scaled(d, n_dst, n_src, (int)E, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, dx, path_scale, dw_mode,
+                         ST(stream));
+}
 int b200_conv_bwd_x(int m0, int m1, int m2, int lout, int n_src, const int32_t* rrowptr, const int32_t* eid,
                     const int32_t* dst, const float* gout, const float* Y, const float* w, float denom, float* dx,
                     void* stream) {

@@ -219,6 +219,21 @@ __device__ __forceinline__ void p_bwde(const float* rec, const float* x, const f
 }
 
 // ---- path lists (one per thread group) ----------------------------------------------------------
+// Variants of the passes over per-edge weights for the second-order pass of the training path (higher_order.py,
+// ConvB.backward): the weights of a path are scaled on the way in and its weight gradient on the way out (the variation of
+// the filter acts on the l2 > 0 paths only: scale 0 on the others), and the weight gradient can be added into its array or
+// left out.
+struct ConvMode {
+  float wscale[kNumPaths];
+  int dw_mode;   // 0: d weight overwritten, 1: added into, 2: not computed
+};
+static ConvMode plain_mode() {
+  ConvMode m;
+  for (int p = 0; p < kNumPaths; ++p) m.wscale[p] = 1.f;
+  m.dw_mode = 0;
+  return m;
+}
+
 template <int... PIDS> struct PL;
 template <> struct PL<> {
   static constexpr int NACC = 0;
@@ -232,6 +247,8 @@ template <> struct PL<> {
   __device__ __forceinline__ static void load_o(const ConvDesc&, const float*, int, float, float*) {}
   __device__ __forceinline__ static void store_o(const ConvDesc&, float*, int, float, const float*) {}
   __device__ __forceinline__ static void store_w(const ConvDesc&, float*, int, const float*) {}
+  __device__ __forceinline__ static void load_ws(const ConvDesc&, const ConvMode&, const float*, int, float*) {}
+  __device__ __forceinline__ static void store_ws(const ConvDesc&, const ConvMode&, float*, int, const float*) {}
 };
 template <int PID, int... REST> struct PL<PID, REST...> {
   using P = PathT<PID>;
@@ -263,6 +280,19 @@ template <int PID, int... REST> struct PL<PID, REST...> {
   __device__ __forceinline__ static void store_w(const ConvDesc& d, float* __restrict__ wrow, int u, const float* wv) {
     wrow[d.woff[PID] + u] = wv[0];
     R::store_w(d, wrow, u, wv + 1);
+  }
+  // per-edge weights from memory, scaled per path; their gradient scaled the same way, stored or added
+  __device__ __forceinline__ static void load_ws(const ConvDesc& d, const ConvMode& md, const float* __restrict__ wrow, int u,
+                                                 float* wv) {
+    wv[0] = md.wscale[PID] * __ldg(wrow + d.woff[PID] + u);
+    R::load_ws(d, md, wrow, u, wv + 1);
+  }
+  __device__ __forceinline__ static void store_ws(const ConvDesc& d, const ConvMode& md, float* __restrict__ wrow, int u,
+                                                  const float* wv) {
+    float* p = wrow + d.woff[PID] + u;
+    const float v = md.wscale[PID] * wv[0];
+    *p = md.dw_mode == 1 ? *p + v : v;
+    R::store_ws(d, md, wrow, u, wv + 1);
   }
   __device__ __forceinline__ static void fwd(const float* rec, const float* x, const float* wv, float* acc) {
     p_fwd<PID>(rec, x, wv[0], acc);
@@ -365,7 +395,7 @@ template <int ROLE> __device__ __forceinline__ int role_xoff(const ConvDesc& d) 
 template <int ROLE, int LOUT, int G, bool TAB>
 __device__ __forceinline__ void fwd_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
                                           const float* __restrict__ x, const float* __restrict__ w, int u, float* acc,
-                                          const int* s_ti, const float* s_tt) {
+                                          const int* s_ti, const float* s_tt, const ConvMode& md) {
   using L = typename GroupT<ROLE, LOUT, G>::L;
   constexpr int D1 = RoleT<ROLE, LOUT>::D1;
   const int xo = role_xoff<ROLE>(d) + u * D1;
@@ -376,7 +406,7 @@ __device__ __forceinline__ void fwd_group(const ConvDesc& d, const float* rec, c
 #pragma unroll
     for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
     if constexpr (TAB) L::template load_w<true>(d, w + (size_t)s_ti[k] * 4 * d.wn, u, s_tt[k], wv);
-    else L::template load_w<false>(d, w + (size_t)s_e[k] * d.wn, u, 0.f, wv);
+    else L::load_ws(d, md, w + (size_t)s_e[k] * d.wn, u, wv);
     L::fwd(rec + k * RoleT<ROLE, LOUT>::REC, xv, wv, acc);
   }
 }
@@ -385,7 +415,7 @@ template <int ROLE, int LOUT, bool TAB>
 __global__ void __launch_bounds__(256)
 conv_fwd_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
                 const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w, float denom,
-                float* __restrict__ out, TabArg tab) {
+                float* __restrict__ out, TabArg tab, ConvMode md) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int TE = te_of<ROLE>();
   __shared__ __align__(16) float rec[TE * RT::REC];
@@ -405,10 +435,10 @@ conv_fwd_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const in
     stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne, TAB ? &tab : nullptr, s_ti, s_tt);
     __syncthreads();
     if (active) {
-      if (grp == 0) fwd_group<ROLE, LOUT, 0, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
-      else if (grp == 1) fwd_group<ROLE, LOUT, 1, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
-      else if (grp == 2) fwd_group<ROLE, LOUT, 2, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
-      else fwd_group<ROLE, LOUT, 3, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt);
+      if (grp == 0) fwd_group<ROLE, LOUT, 0, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt, md);
+      else if (grp == 1) fwd_group<ROLE, LOUT, 1, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt, md);
+      else if (grp == 2) fwd_group<ROLE, LOUT, 2, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt, md);
+      else fwd_group<ROLE, LOUT, 3, TAB>(d, rec, s_e, s_g, ne, x, w, u, acc, s_ti, s_tt, md);
     }
   }
   if (active) {
@@ -514,7 +544,8 @@ template <int ROLE, int LOUT, int G, bool DX, bool TAB>
 __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, const int* s_e, const int* s_g, int ne,
                                            const float* __restrict__ x, const float* __restrict__ w,
                                            float* __restrict__ dw, const float* gv, int u, bool active, float* s_dY,
-                                           float* __restrict__ dxo, const int* s_ti, const float* s_tt, float* s_dr) {
+                                           float* __restrict__ dxo, const int* s_ti, const float* s_tt, float* s_dr,
+                                           const ConvMode& md) {
   using L = typename GroupT<ROLE, LOUT, G>::L;
   constexpr int D1 = RoleT<ROLE, LOUT>::D1;
   const int xo = role_xoff<ROLE>(d) + u * D1;
@@ -531,7 +562,7 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
 #pragma unroll
       for (int a = 0; a < D1; ++a) xv[a] = __ldg(xr + a);
       if constexpr (TAB) L::load_wd(d, w + (size_t)s_ti[k] * 4 * d.wn, u, s_tt[k], wv, wdv);
-      else L::template load_w<false>(d, w + (size_t)s_e[k] * d.wn, u, 0.f, wv);
+      else L::load_ws(d, md, w + (size_t)s_e[k] * d.wn, u, wv);
       float dxv[D1];
 #pragma unroll
       for (int a = 0; a < D1; ++a) dxv[a] = 0.f;
@@ -540,7 +571,7 @@ __device__ __forceinline__ void bwde_group(const ConvDesc& d, const float* rec, 
 #pragma unroll
         for (int q = 0; q < L::NP; ++q) drp = fmaf(dwv[q], wdv[q], drp);
       } else {
-        L::store_w(d, dw + (size_t)s_e[k] * d.wn, u, dwv);
+        if (md.dw_mode != 2) L::store_ws(d, md, dw + (size_t)s_e[k] * d.wn, u, dwv);
       }
       if constexpr (DX) {   // scatter to the source atom's row (RED.ADD; the row was zeroed by the launcher)
         float* xr = dxo + (size_t)s_g[k] * d.xdim + xo;
@@ -567,7 +598,7 @@ __global__ void __launch_bounds__(256)
 conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const int* __restrict__ src,
                  const float* __restrict__ x, const float* __restrict__ Y, const float* __restrict__ w,
                  const float* __restrict__ gout, float inv_denom, float* __restrict__ dw, float* __restrict__ dYo,
-                 int accumulate, float* __restrict__ dxo, TabArg tab) {
+                 int accumulate, float* __restrict__ dxo, TabArg tab, ConvMode md) {
   using RT = RoleT<ROLE, LOUT>;
   constexpr int NG = num_groups<ROLE, LOUT>();
   constexpr int TE = te_of<ROLE>();
@@ -597,10 +628,10 @@ conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const i
     stage_chunk<ROLE, LOUT>(rec, s_e, s_g, Y, nullptr, src, c0, ne, TAB ? &tab : nullptr, s_ti, s_tt);
     __syncthreads();
     float* s_dr = s_dY + nwarps * TE * 8;
-    if (grp == 0) bwde_group<ROLE, LOUT, 0, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
-    else if (grp == 1) bwde_group<ROLE, LOUT, 1, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
-    else if (grp == 2) bwde_group<ROLE, LOUT, 2, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
-    else bwde_group<ROLE, LOUT, 3, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr);
+    if (grp == 0) bwde_group<ROLE, LOUT, 0, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr, md);
+    else if (grp == 1) bwde_group<ROLE, LOUT, 1, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr, md);
+    else if (grp == 2) bwde_group<ROLE, LOUT, 2, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr, md);
+    else bwde_group<ROLE, LOUT, 3, DX, TAB>(d, rec, s_e, s_g, ne, x, w, dw, gv, u, active, s_dY, dxo, s_ti, s_tt, s_dr, md);
     if constexpr (TAB || !(LOUT == 0 && ROLE == 0)) __syncthreads();
     if constexpr (TAB) {   // d E / d r of the chunk's edges: sum over the warps (channels), times d t / d r = 1 / h
       for (int k = threadIdx.x; k < ne; k += blockDim.x) {
@@ -625,13 +656,15 @@ conv_bwde_kernel(ConvDesc d, int mulpad, const int* __restrict__ rowptr, const i
 // ---- launchers ------------------------------------------------------------------------------------
 template <int ROLE, int LOUT>
 static void launch_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
-                       const float* w, float denom, float* out, cudaStream_t st, const TabArg* tab = nullptr) {
+                       const float* w, float denom, float* out, cudaStream_t st, const TabArg* tab = nullptr,
+                       const ConvMode* mode = nullptr) {
   const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
   if (mul == 0 || n_dst == 0) return;
   const int mulpad = round_up(mul, 32);
   const int threads = mulpad * num_groups<ROLE, LOUT>();
-  if (tab) conv_fwd_kernel<ROLE, LOUT, true><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out, *tab);
-  else conv_fwd_kernel<ROLE, LOUT, false><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out, TabArg{});
+  const ConvMode md = mode ? *mode : plain_mode();
+  if (tab) conv_fwd_kernel<ROLE, LOUT, true><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out, *tab, md);
+  else conv_fwd_kernel<ROLE, LOUT, false><<<n_dst, threads, 0, st>>>(d, mulpad, rowptr, src, x, Y, w, denom, out, TabArg{}, md);
 }
 template <int ROLE, int LOUT>
 static void launch_bwdx(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst,
@@ -647,25 +680,26 @@ static void launch_bwdx(const ConvDesc& d, int n_src, const int* rrowptr, const 
 template <int ROLE, int LOUT>
 static void launch_bwde(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
                         const float* w, const float* gout, float inv_denom, float* dw, float* dY, int accumulate,
-                        float* dx, cudaStream_t st, const TabArg* tab = nullptr) {
+                        float* dx, cudaStream_t st, const TabArg* tab = nullptr, const ConvMode* mode = nullptr) {
   const int mul = ROLE == 0 ? d.m0 : (ROLE == 1 ? d.m1 : d.m2);
   if (mul == 0 || n_dst == 0) return;
+  const ConvMode md = mode ? *mode : plain_mode();
   const int mulpad = round_up(mul, 32);
   const int threads = mulpad * num_groups<ROLE, LOUT>();
   const size_t sm = (size_t)(threads / 32) * te_of<ROLE>() * (tab ? 9 : 8) * sizeof(float);
   if (tab) {
     if (dx)
       conv_bwde_kernel<ROLE, LOUT, true, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom,
-                                                                            nullptr, dY, accumulate, dx, *tab);
+                                                                            nullptr, dY, accumulate, dx, *tab, md);
     else
       conv_bwde_kernel<ROLE, LOUT, false, true><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom,
-                                                                             nullptr, dY, accumulate, nullptr, *tab);
+                                                                             nullptr, dY, accumulate, nullptr, *tab, md);
   } else if (dx) {
     conv_bwde_kernel<ROLE, LOUT, true, false><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw,
-                                                                           dY, accumulate, dx, TabArg{});
+                                                                           dY, accumulate, dx, TabArg{}, md);
   } else {
     conv_bwde_kernel<ROLE, LOUT, false, false><<<n_dst, threads, sm, st>>>(d, mulpad, rowptr, src, x, Y, w, gout, inv_denom, dw,
-                                                                            dY, accumulate, nullptr, TabArg{});
+                                                                            dY, accumulate, nullptr, TabArg{}, md);
   }
 }
 
@@ -674,19 +708,36 @@ static bool desc_ok(const ConvDesc& d) {
          d.m2 <= 64;
 }
 
-int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
-             const float* w, float denom, float* out, cudaStream_t st) {
+static int conv_fwd_mode(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                         const float* w, float denom, float* out, const ConvMode* md, cudaStream_t st) {
   B200_REQUIRE(desc_ok(d), "conv_fwd: unsupported irreps (m0<=256, m1<=128, m2<=64, lout in {0,2})");
   if (d.lout == 2) {
-    launch_fwd<0, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
-    launch_fwd<1, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
-    launch_fwd<2, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+    launch_fwd<0, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st, nullptr, md);
+    launch_fwd<1, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st, nullptr, md);
+    launch_fwd<2, 2>(d, n_dst, rowptr, src, x, Y, w, denom, out, st, nullptr, md);
   } else {
-    launch_fwd<0, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
-    launch_fwd<1, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
-    launch_fwd<2, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st);
+    launch_fwd<0, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st, nullptr, md);
+    launch_fwd<1, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st, nullptr, md);
+    launch_fwd<2, 0>(d, n_dst, rowptr, src, x, Y, w, denom, out, st, nullptr, md);
   }
   return check_launch("conv_fwd", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
+}
+int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+             const float* w, float denom, float* out, cudaStream_t st) {
+  return conv_fwd_mode(d, n_dst, rowptr, src, x, Y, w, denom, out, nullptr, st);
+}
+static bool fill_mode(const float* path_scale, int dw_mode, ConvMode& md) {
+  md = plain_mode();
+  if (path_scale)
+    for (int p = 0; p < kNumPaths; ++p) md.wscale[p] = path_scale[p];
+  md.dw_mode = dw_mode;
+  return dw_mode >= 0 && dw_mode <= 2;
+}
+int conv_fwd_scaled(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                    const float* w, float denom, float* out, const float* path_scale, cudaStream_t st) {
+  ConvMode md;
+  fill_mode(path_scale, 0, md);
+  return conv_fwd_mode(d, n_dst, rowptr, src, x, Y, w, denom, out, &md, st);
 }
 
 int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst, const float* gout,
@@ -707,24 +758,40 @@ int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid,
 
 // d weight, d edge_attr and (dx != nullptr) d x[src] in one pass over the destination-sorted edges: the gradient
 // rows of the source atoms are accumulated with RED.ADD, so the per-edge weights are read once for all three.
+static int conv_bwd_mode(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                         const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                         float* dx, const ConvMode* md, cudaStream_t st);
 int conv_bwd_edge_x(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
                     const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
                     float* dx, cudaStream_t st) {
+  return conv_bwd_mode(d, n_dst, n_src, n_edges, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, dx, nullptr, st);
+}
+int conv_bwd_scaled(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                    const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                    float* dx, const float* path_scale, int dw_mode, cudaStream_t st) {
+  ConvMode md;
+  B200_REQUIRE(fill_mode(path_scale, dw_mode, md), "conv_bwd_scaled: dw_mode must be 0, 1 or 2");
+  B200_REQUIRE(dw != nullptr || dw_mode == 2, "conv_bwd_scaled: d_weight is NULL");
+  return conv_bwd_mode(d, n_dst, n_src, n_edges, rowptr, src, x, Y, w, gout, denom, dw, dY, accumulate, dx, &md, st);
+}
+static int conv_bwd_mode(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                         const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                         float* dx, const ConvMode* md, cudaStream_t st) {
   B200_REQUIRE(desc_ok(d), "conv_bwd_edge: unsupported irreps");
   const float inv = 1.0f / denom;
   if (dx) cudaMemsetAsync(dx, 0, sizeof(float) * (size_t)n_src * d.xdim, st);
   // the three role kernels run back to back on one stream: the first may overwrite dY, the rest add
   int acc = accumulate;
   if (d.lout == 2) {
-    if (d.m0) { launch_bwde<0, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
-    if (d.m1) { launch_bwde<1, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
-    if (d.m2) { launch_bwde<2, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
+    if (d.m0) { launch_bwde<0, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st, nullptr, md); acc = 1; }
+    if (d.m1) { launch_bwde<1, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st, nullptr, md); acc = 1; }
+    if (d.m2) { launch_bwde<2, 2>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st, nullptr, md); acc = 1; }
   } else {
     // role 0 (path 000) does not touch dY
     if (!acc && !d.m1 && !d.m2) cudaMemsetAsync(dY, 0, sizeof(float) * 9 * (size_t)n_edges, st);
-    launch_bwde<0, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st);
-    if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
-    if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st); acc = 1; }
+    launch_bwde<0, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st, nullptr, md);
+    if (d.m1) { launch_bwde<1, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st, nullptr, md); acc = 1; }
+    if (d.m2) { launch_bwde<2, 0>(d, n_dst, rowptr, src, x, Y, w, gout, inv, dw, dY, acc, dx, st, nullptr, md); acc = 1; }
   }
   return check_launch("conv_bwd_edge", (d.m0 > 0) + (d.m1 > 0) + (d.m2 > 0));
 }

@@ -28,6 +28,13 @@ int radial_mlp_bwd(const MlpDesc& d, long long E, const float* emb, const float*
 
 int conv_fwd(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
              const float* w, float denom, float* out, cudaStream_t st);
+// second-order pass of the training path: per-path scale of the weights (in) and of the weight gradient (out), NULL = 1;
+// dw_mode 0: d weight overwritten, 1: added into, 2: not computed (dw may be nullptr)
+int conv_fwd_scaled(const ConvDesc& d, int n_dst, const int* rowptr, const int* src, const float* x, const float* Y,
+                    const float* w, float denom, float* out, const float* path_scale, cudaStream_t st);
+int conv_bwd_scaled(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,
+                    const float* Y, const float* w, const float* gout, float denom, float* dw, float* dY, int accumulate,
+                    float* dx, const float* path_scale, int dw_mode, cudaStream_t st);
 int conv_bwd_x(const ConvDesc& d, int n_src, const int* rrowptr, const int* eid, const int* dst, const float* gout,
                const float* Y, const float* w, float denom, float* dx, cudaStream_t st);
 int conv_bwd_edge_x(const ConvDesc& d, int n_dst, int n_src, int n_edges, const int* rowptr, const int* src, const float* x,

@@ -212,6 +212,44 @@ class ConvB(Function):
         def add(a, b):
             return b if a is None else a + b
 
+        if not torch.is_grad_enabled():
+            # the loss's own reverse pass (no third order asked for): the same three terms straight on the kernels, with the
+            # filter mask as a per-path scale inside them, ONE weight-gradient array the calls add into, and no outputs
+            # nobody reads - every [E, wn] tensor saved here is a pass over ~1 GB
+            graph, muls, lout, denom = args
+            rowptr, src = graph['rowptr_dst'], graph['src']
+            xc, Yc, wc, gc = _c(x), _c(Y), _c(w), _c(g)
+            mask = _y_scale((muls, lout))
+            want_dw, first = need[2], True
+            if ax is not None:
+                axc = _c(ax)
+                if need[3]:
+                    dg = add(dg, ops.conv_fwd(muls, lout, rowptr, src, axc, Yc, wc, denom))
+                if need[1] or need[2]:
+                    dw, dY, _ = ops.conv_bwd_scaled(muls, lout, x.shape[0], rowptr, src, axc, Yc, wc, gc, denom,
+                                                    dw_mode=0 if want_dw else 2, want_dx=False)
+                    first = not want_dw
+            if aY is not None:
+                aYc = _c(aY)
+                if need[3]:
+                    dg = add(dg, ops.conv_fwd_scaled(muls, lout, rowptr, src, xc, aYc, wc, denom, mask))
+                if need[0] or need[2]:
+                    mode = 2 if not want_dw else (0 if first else 1)
+                    tw, _, dx = ops.conv_bwd_scaled(muls, lout, x.shape[0], rowptr, src, xc, aYc, wc, gc, denom, path_scale=mask,
+                                                    dw=dw, dw_mode=mode, want_dx=need[0])
+                    if want_dw:
+                        dw, first = tw, False
+            if aw is not None:
+                awc = _c(aw)
+                if need[3]:
+                    dg = add(dg, ops.conv_fwd(muls, lout, rowptr, src, xc, Yc, awc, denom))
+                if need[0] or need[1]:
+                    _, dY, tx = ops.conv_bwd_scaled(muls, lout, x.shape[0], rowptr, src, xc, Yc, awc, gc, denom, dw_mode=2,
+                                                    dY=dY, want_dx=need[0])
+                    dx = add(dx, tx)
+            return (dx if need[0] else None), (dY if need[1] else None), (dw if need[2] else None), \
+                   (dg if need[3] else None), None, None, None, None
+
         # S = <g, T(ax, Y, w) + T(x, aY, w) + T(x, Y, aw)> (T trilinear); every term is one of the two kernels
         if ax is not None:
             if need[3]:
@@ -241,6 +279,10 @@ class ConvB(Function):
 
 
 _MASKS = {}
+def _y_scale(muls_lout=None):
+    """the mask of _y_mask as 15 per-path factors (canonical path order of csrc/common.cuh) for the *_scaled kernels."""
+    from .cg import ALL_PATHS
+    return [0.0 if l2 == 0 else 1.0 for (_, l2, _) in ALL_PATHS]
 
 
 def _y_mask(muls_lout, like):

@@ -247,6 +247,43 @@ def conv_bwd(muls, lout, n_src, rowptr, src, x, Y, w, gout, denom, dY=None):
     return dw, dY, dx
 
 
+def _path_scale(path_scale):
+    return None if path_scale is None else (C.c_float * 15)(*[float(v) for v in path_scale])
+
+
+@_timed
+def conv_fwd_scaled(muls, lout, rowptr, src, x, Y, w, denom, path_scale):
+    """conv_fwd with the weights of path p multiplied by path_scale[p] (15 host floats, canonical path order)."""
+    n = rowptr.shape[0] - 1
+    _, od = conv_dims(*muls, lout)
+    out = torch.empty(n, od, dtype=torch.float32, device=x.device)
+    check(lib().b200_conv_fwd_scaled(*muls, lout, n, _p(rowptr), _p(src), _p(x), _p(Y), _p(w), float(denom), _p(out),
+                                     _path_scale(path_scale), _stream()), 'conv_fwd_scaled')
+    return out
+
+
+@_timed
+def conv_bwd_scaled(muls, lout, n_src, rowptr, src, x, Y, w, gout, denom, path_scale=None, dw=None, dw_mode=0, dY=None,
+                    want_dx=True):
+    """conv_bwd for the second-order pass: per-path scale of the weights and of their gradient; dw_mode 0 = new d weight,
+    1 = added into `dw`, 2 = no weight gradient; dY given = added into; want_dx False = no d x.  -> (dw, dY, dx)."""
+    n = rowptr.shape[0] - 1
+    E = src.shape[0]
+    if dw_mode == 0:
+        dw = torch.empty_like(w)
+    elif dw_mode == 2:
+        dw = None
+    acc = dY is not None
+    if dY is None:
+        dY = torch.zeros(E, 9, dtype=torch.float32, device=x.device)
+    xdim = muls[0] + 3 * muls[1] + 5 * muls[2]
+    dx = torch.empty(n_src, xdim, dtype=torch.float32, device=x.device) if want_dx else None
+    check(lib().b200_conv_bwd_scaled(*muls, lout, n, n_src, E, _p(rowptr), _p(src), _p(x), _p(Y), _p(w), _p(gout), float(denom),
+                                     _p(dw), _p(dY), int(acc), _p(dx), _path_scale(path_scale), int(dw_mode), _stream()),
+          'conv_bwd_scaled')
+    return dw, dY, dx
+
+
 @_timed
 def conv_bwd_x(muls, lout, n_src, rrowptr, eid, dst, gout, Y, w, denom):
     xdim = muls[0] + 3 * muls[1] + 5 * muls[2]
