@@ -175,6 +175,16 @@ int b200_table_dot(int m, int wn, int64_t n_edges, float inv_h, int n_grid, cons
 int b200_table_scatter(int m, int wn, int64_t n_edges, float inv_h, int n_grid, const float* g, const float* coef, const float* r,
                        const int32_t* order, float* G, void* stream);
 
+/* b200_table_scatter(m, ...) and b200_table_dot(md, ...) of the same g in ONE pass over it (the two results of a reverse pass
+ * that read the [E, wn] gradient): G as above, dot[e] = sum_k g[e, k] d^md w_k / d r^md (r[e]) (coef does not enter dot) */
+int b200_table_scatter_dot(int m, int md, int wn, int64_t n_edges, float inv_h, int n_grid, const float* P, const float* g,
+                           const float* coef, const float* r, const int32_t* order, float* G, float* dot, void* stream);
+/* Z, dZ [n_grid + 1, wn] float64: weight_nn and its derivative in r on the grid points r_i = i h  ->  P[n_grid, 4, wn]
+ * (cubic Hermite coefficients per interval; the differences of neighbouring values are formed in float64) */
+int b200_table_hermite(int n_grid, int wn, double h, const double* Z, const double* dZ, float* P, void* stream);
+/* the adjoint: G = d L / d P  ->  d L / d Z, d L / d dZ (float64, [n_grid + 1, wn]) */
+int b200_table_hermite_adj(int n_grid, int wn, double h, const float* G, double* gZ, double* gdZ, void* stream);
+
 /* ---- node embedding: sevenn/nn/node_embedding.py:39-48 + nn/linear.py:37-44 (one-hot . W / sqrt(n_species)) */
 int b200_embed_fwd(int n_nodes, int n_species, int dim, const int32_t* types, const float* W, float* x, void* stream);
 

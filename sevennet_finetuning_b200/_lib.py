@@ -70,6 +70,9 @@ SIGNATURES = {
     'b200_gate_fwd': (_i, [_i, _i, _i, _i, _vp, _vp, _vp]),
     'b200_gate_bwd': (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     'b200_gate_bwd2': (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_table_scatter_dot': (_i, [_i, _i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'b200_table_hermite': (_i, [_i, _i, C.c_double, _vp, _vp, _vp, _vp]),
+    'b200_table_hermite_adj': (_i, [_i, _i, C.c_double, _vp, _vp, _vp, _vp]),
     'b200_table_interp': (_i, [_i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_table_dot': (_i, [_i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     'b200_table_scatter': (_i, [_i, _i, _i64, _f, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

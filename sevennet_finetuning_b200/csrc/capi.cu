@@ -176,6 +176,19 @@ int b200_table_scatter(int m, int wn, int64_t E, float inv_h, int n_grid, const 
   B200_REQUIRE(G && (E == 0 || (g && r)), "table_scatter: null argument");
   return table_scatter(m, wn, E, inv_h, n_grid, g, coef, r, order, G, ST(stream));
 }
+int b200_table_scatter_dot(int m, int md, int wn, int64_t E, float inv_h, int n_grid, const float* P, const float* g,
+                           const float* coef, const float* r, const int32_t* order, float* G, float* dot, void* stream) {
+  B200_REQUIRE(G && (E == 0 || (P && g && r && dot)), "table_scatter_dot: null argument");
+  return table_scatter_dot(m, md, wn, E, inv_h, n_grid, P, g, coef, r, order, G, dot, ST(stream));
+}
+int b200_table_hermite(int n_grid, int wn, double h, const double* Z, const double* dZ, float* P, void* stream) {
+  B200_REQUIRE(Z && dZ && P, "table_hermite: null argument");
+  return table_hermite(n_grid, wn, h, Z, dZ, P, ST(stream));
+}
+int b200_table_hermite_adj(int n_grid, int wn, double h, const float* G, double* gZ, double* gdZ, void* stream) {
+  B200_REQUIRE(G && gZ && gdZ, "table_hermite_adj: null argument");
+  return table_hermite_adj(n_grid, wn, h, G, gZ, gdZ, ST(stream));
+}
 int b200_gate_bwd2(int ns, int m1, int m2, int n, const float* in, const float* dout, const float* a, float* dx, float* dg,
                    void* stream) {
   B200_REQUIRE(n == 0 || (in && dout && a && dx && dg), "gate_bwd2: null argument");

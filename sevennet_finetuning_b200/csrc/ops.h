@@ -98,6 +98,12 @@ int table_dot(int m, int wn, long long E, float inv_h, int n_grid, const float* 
 int table_scatter(int m, int wn, long long E, float inv_h, int n_grid, const float* g, const float* coef, const float* r,
                   const int* order, float* G, cudaStream_t st);
 
+// table_scatter(m) and table_dot(md) of the same g in one pass over it
+int table_scatter_dot(int m, int md, int wn, long long E, float inv_h, int n_grid, const float* P, const float* g,
+                      const float* coef, const float* r, const int* order, float* G, float* dot, cudaStream_t st);
+int table_hermite(int n_grid, int wn, double h, const double* Z, const double* dZ, float* P, cudaStream_t st);
+int table_hermite_adj(int n_grid, int wn, double h, const float* G, double* gZ, double* gdZ, cudaStream_t st);
+
 int gate_fwd(int ns, int m1, int m2, int n_nodes, const float* in, float* out, cudaStream_t st);
 int gate_bwd(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, float* din, cudaStream_t st);
 int gate_bwd2(int ns, int m1, int m2, int n_nodes, const float* in, const float* dout, const float* a, float* dx,

@@ -108,13 +108,17 @@ constexpr int TS_EPC = 64;   // edges per CTA
 // CTA = TS_EPC consecutive positions of `order`; thread = up to TS_MAXQ float4 columns of the weights.  Edge id, interval
 // and the four coefficients coef * q_j(t) of the CTA's edges are staged in shared memory first; the sums of the current
 // interval stay in registers and go to G with one atomic add per element when the interval changes.
+// DOT: the same pass also emits dot[e] = sum_k g[e, k] d^md w_k / d r^md (r[e]) (the two reverse-pass results that read g).
+template <bool DOT>
 __global__ void __launch_bounds__(TS_T)
 table_scatter_kernel(int m, int wn, long long E, float inv_h, int n_grid, const float* __restrict__ g,
                      const float* __restrict__ coef, const float* __restrict__ r, const int* __restrict__ order,
-                     float* __restrict__ G) {
+                     float* __restrict__ G, int md, const float* __restrict__ P, float* __restrict__ dot) {
   __shared__ long long s_e[TS_EPC];
   __shared__ int s_i[TS_EPC];
   __shared__ float s_q[TS_EPC][4];
+  __shared__ float s_qd[DOT ? TS_EPC : 1][4];
+  __shared__ float s_dot[DOT ? TS_EPC : 1];
   const long long j0 = (long long)blockIdx.x * TS_EPC;
   const int ne = (int)min((long long)TS_EPC, E - j0);
   const int nq = wn >> 2;
@@ -129,6 +133,12 @@ table_scatter_kernel(int m, int wn, long long E, float inv_h, int n_grid, const 
     s_i[threadIdx.x] = i;
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) s_q[threadIdx.x][jj] = q[jj] * ce;
+    if constexpr (DOT) {
+      basis_m(md, t, inv_h, q);
+#pragma unroll
+      for (int jj = 0; jj < 4; ++jj) s_qd[threadIdx.x][jj] = q[jj];
+      s_dot[threadIdx.x] = 0.f;
+    }
   }
   __syncthreads();
   float4 acc[4][TS_MAXQ];
@@ -183,9 +193,70 @@ table_scatter_kernel(int m, int wn, long long E, float inv_h, int n_grid, const 
           acc[jj][u].w = fmaf(c, gv[d][u].w, acc[jj][u].w);
         }
       }
+      if constexpr (DOT) {
+        const float4* Pi = reinterpret_cast<const float4*>(P + (size_t)i * 4 * wn);
+        const float q0 = s_qd[j + d][0], q1 = s_qd[j + d][1], q2 = s_qd[j + d][2], q3 = s_qd[j + d][3];
+        float sdot = 0.f;
+#pragma unroll
+        for (int u = 0; u < TS_MAXQ; ++u) {
+          const int k = threadIdx.x + u * TS_T;
+          if (k < nq) {
+            const float4 a = __ldg(Pi + k), b = __ldg(Pi + nq + k), c = __ldg(Pi + 2 * nq + k), dd = __ldg(Pi + 3 * nq + k);
+            const float4 v = gv[d][u];
+            sdot += v.x * (q0 * a.x + q1 * b.x + q2 * c.x + q3 * dd.x) + v.y * (q0 * a.y + q1 * b.y + q2 * c.y + q3 * dd.y) +
+                    v.z * (q0 * a.z + q1 * b.z + q2 * c.z + q3 * dd.z) + v.w * (q0 * a.w + q1 * b.w + q2 * c.w + q3 * dd.w);
+          }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sdot += __shfl_xor_sync(0xffffffffu, sdot, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&s_dot[j + d], sdot);
+      }
     }
   }
   flush();
+  if constexpr (DOT) {
+    __syncthreads();
+    if (threadIdx.x < ne) dot[s_e[threadIdx.x]] = s_dot[threadIdx.x];
+  }
+}
+
+// nodal values and slopes (float64, [n_grid + 1, wn]) -> per-interval cubic coefficients (float32, [n_grid, 4, wn]):
+//   a = Z_i, b = h Z'_i, c = 3 (Z_{i+1} - Z_i) - 2 h Z'_i - h Z'_{i+1}, d = -2 (Z_{i+1} - Z_i) + h Z'_i + h Z'_{i+1}
+// The difference of neighbouring nodal values is formed in float64: in float32 it loses the digits the slope needs.
+__global__ void hermite_kernel(int n_grid, int wn, double h, const double* __restrict__ Z, const double* __restrict__ dZ,
+                               float* __restrict__ P) {
+  const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (id >= (long long)n_grid * wn) return;
+  const int i = (int)(id / wn), k = (int)(id % wn);
+  const double v0 = Z[(size_t)i * wn + k], v1 = Z[(size_t)(i + 1) * wn + k];
+  const double s0 = h * dZ[(size_t)i * wn + k], s1 = h * dZ[(size_t)(i + 1) * wn + k], dv = v1 - v0;
+  float* p = P + (size_t)i * 4 * wn + k;
+  p[0] = (float)v0;
+  p[wn] = (float)s0;
+  p[2 * wn] = (float)(3.0 * dv - 2.0 * s0 - s1);
+  p[3 * wn] = (float)(s0 + s1 - 2.0 * dv);
+}
+// the adjoint map: gradient with respect to P -> gradients with respect to Z and Z'
+__global__ void hermite_adj_kernel(int n_grid, int wn, double h, const float* __restrict__ G, double* __restrict__ gZ,
+                                   double* __restrict__ gdZ) {
+  const long long id = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (id >= (long long)(n_grid + 1) * wn) return;
+  const int i = (int)(id / wn), k = (int)(id % wn);
+  double z = 0.0, dz = 0.0;
+  if (i < n_grid) {       // left node of interval i
+    const float* g = G + (size_t)i * 4 * wn + k;
+    const double ga = g[0], gb = g[wn], gc = g[2 * wn], gd = g[3 * wn];
+    z += ga - 3.0 * gc + 2.0 * gd;
+    dz += gb - 2.0 * gc + gd;
+  }
+  if (i > 0) {            // right node of interval i - 1
+    const float* g = G + (size_t)(i - 1) * 4 * wn + k;
+    const double gc = g[2 * wn], gd = g[3 * wn];
+    z += 3.0 * gc - 2.0 * gd;
+    dz += gd - gc;
+  }
+  gZ[id] = z;
+  gdZ[id] = h * dz;
 }
 
 int check_shape(const char* what, int m, int wn, int n_grid, float inv_h) {
@@ -224,8 +295,37 @@ int table_scatter(int m, int wn, long long E, float inv_h, int n_grid, const flo
   }
   if (E == 0) return B200_OK;
   const unsigned blocks = (unsigned)((E + TS_EPC - 1) / TS_EPC);
-  table_scatter_kernel<<<blocks, TS_T, 0, st>>>(m, wn, E, inv_h, n_grid, g, coef, r, order, G);
+  table_scatter_kernel<false><<<blocks, TS_T, 0, st>>>(m, wn, E, inv_h, n_grid, g, coef, r, order, G, 0, nullptr, nullptr);
   return check_launch("table_scatter");
+}
+
+int table_scatter_dot(int m, int md, int wn, long long E, float inv_h, int n_grid, const float* P, const float* g,
+                      const float* coef, const float* r, const int* order, float* G, float* dot, cudaStream_t st) {
+  if (int rc = check_shape("table_scatter_dot", m, wn, n_grid, inv_h)) return rc;
+  B200_REQUIRE(md >= 0 && md <= 4, "table_scatter_dot: derivative order %d", md);
+  B200_REQUIRE(wn <= 4 * TS_T * TS_MAXQ, "table_scatter_dot: wn <= %d", 4 * TS_T * TS_MAXQ);
+  if (cudaMemsetAsync(G, 0, sizeof(float) * (size_t)n_grid * 4 * wn, st) != cudaSuccess) {
+    set_error("table_scatter_dot: memset failed");
+    return B200_ERR_CUDA;
+  }
+  if (E == 0) return B200_OK;
+  const unsigned blocks = (unsigned)((E + TS_EPC - 1) / TS_EPC);
+  table_scatter_kernel<true><<<blocks, TS_T, 0, st>>>(m, wn, E, inv_h, n_grid, g, coef, r, order, G, md, P, dot);
+  return check_launch("table_scatter_dot");
+}
+
+int table_hermite(int n_grid, int wn, double h, const double* Z, const double* dZ, float* P, cudaStream_t st) {
+  B200_REQUIRE(n_grid >= 1 && wn >= 1 && h > 0.0, "table_hermite: n_grid >= 1, wn >= 1, h > 0");
+  const long long n = (long long)n_grid * wn;
+  hermite_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n_grid, wn, h, Z, dZ, P);
+  return check_launch("table_hermite");
+}
+
+int table_hermite_adj(int n_grid, int wn, double h, const float* G, double* gZ, double* gdZ, cudaStream_t st) {
+  B200_REQUIRE(n_grid >= 1 && wn >= 1 && h > 0.0, "table_hermite_adj: n_grid >= 1, wn >= 1, h > 0");
+  const long long n = (long long)(n_grid + 1) * wn;
+  hermite_adj_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n_grid, wn, h, G, gZ, gdZ);
+  return check_launch("table_hermite_adj");
 }
 
 }  // namespace b200

@@ -320,6 +320,33 @@ class EmbedF(Function):
 # ---- train-mode radial weights from a table (csrc/table_train.cu; sevenn/nn/convolution.py:97-106) ------------------------
 # P[n_grid, 4, wn]: per-interval cubic coefficients of weight_nn as a function of the edge length, built by the caller with
 # differentiable tensor operations on the grid points.  tab = (inv_h, order): 1 / grid step (fp32-exact), edge ids sorted by interval (int32).
+class HermF(Function):
+    """(Z, dZ) float64 [n_grid + 1, wn] -> P float32 [n_grid, 4, wn] (linear; csrc/table_train.cu hermite_kernel)."""
+
+    @staticmethod
+    def forward(ctx, Z, dZ, h):
+        ctx.h = h
+        return ops.table_hermite(Z.detach().contiguous(), dZ.detach().contiguous(), h)
+
+    @staticmethod
+    def backward(ctx, G):
+        gZ, gdZ = HermT.apply(G, ctx.h)
+        return gZ, gdZ, None
+
+
+class HermT(Function):
+    """The adjoint of HermF."""
+
+    @staticmethod
+    def forward(ctx, G, h):
+        ctx.h = h
+        return ops.table_hermite_adj(_c(G.detach()), h)
+
+    @staticmethod
+    def backward(ctx, aZ, adZ):
+        return HermF.apply(aZ, adZ, ctx.h), None
+
+
 class TabInterp(Function):
     """[E, wn] = coef[e] * d^m w / d r^m (r[e])   (coef None = 1)."""
 
@@ -333,6 +360,12 @@ class TabInterp(Function):
     def backward(ctx, g):
         P, r, coef = ctx.saved_tensors
         dP = dr = dc = None
+        n = ctx.needs_input_grad
+        if not torch.is_grad_enabled() and n[0] and n[1] and not force_pass.active and not (coef is not None and n[2]):
+            # the loss's own reverse pass: both results that read g in one pass over it
+            dP, dr = ops.table_scatter_dot(ctx.m, ctx.m + 1, _c(P), ctx.tab[0], _c(g), _c(r), ctx.tab[1],
+                                           None if coef is None else _c(coef))
+            return dP, (dr if coef is None else dr * coef), None, None, None
         if ctx.needs_input_grad[0] and not force_pass.active:
             dP = TabScatter.apply(g, coef, r, ctx.m, P.shape[0], ctx.tab)
         if ctx.needs_input_grad[1]:
@@ -356,6 +389,11 @@ class TabDot(Function):
     @staticmethod
     def backward(ctx, a):
         P, r, g = ctx.saved_tensors
+        n = ctx.needs_input_grad
+        if not torch.is_grad_enabled() and n[0] and n[1] and not force_pass.active:
+            dP, dr = ops.table_scatter_dot(ctx.m, ctx.m + 1, _c(P), ctx.tab[0], _c(g), _c(r), ctx.tab[1], _c(a))
+            dg = ops.table_interp(ctx.m, _c(P), ctx.tab[0], _c(r), ctx.tab[1], _c(a)) if n[2] else None
+            return dP, a * dr, dg, None, None
         dP = TabScatter.apply(g, a, r, ctx.m, P.shape[0], ctx.tab) if ctx.needs_input_grad[0] and not force_pass.active else None
         dr = a * TabDot.apply(P, r, g, ctx.m + 1, ctx.tab) if ctx.needs_input_grad[1] else None
         dg = TabInterp.apply(P, r, a, ctx.m, ctx.tab) if ctx.needs_input_grad[2] else None

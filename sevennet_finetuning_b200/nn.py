@@ -502,10 +502,7 @@ class IrrepsConvolution(nn.Module):
             if not last:
                 sg = torch.sigmoid(z)
                 z, dz = c * z * sg, c * sg * (1.0 + z * (1.0 - sg)) * dz
-        h = 1.0 / tab['inv_h']
-        v0, v1, s0, s1 = z[:-1], z[1:], h * dz[:-1], h * dz[1:]
-        dv = v1 - v0
-        P = torch.stack([v0, s0, 3.0 * dv - 2.0 * s0 - s1, s0 + s1 - 2.0 * dv], dim=1).to(torch.float32)
+        P = ho.HermF.apply(z, dz, 1.0 / tab['inv_h'])
         key = None if g['perm'] is None else g['perm'].data_ptr()
         if tab.get('key', 0) != key:   # edge order of this graph: the same for every layer
             r = tab['r'] if g['perm'] is None else tab['r'].index_select(0, g['perm'])

@@ -391,6 +391,36 @@ def gate_bwd2(ns, m1, m2, x, gout, a):
 
 
 @_timed
+def table_scatter_dot(m, md, P, inv_h, g, r, order=None, coef=None):
+    """(table_scatter(m, g, coef), table_dot(md, P, g)) in one pass over g."""
+    n_grid, _, wn = P.shape
+    G = torch.empty(n_grid, 4, wn, dtype=torch.float32, device=r.device)
+    dot = torch.empty(r.shape[0], dtype=torch.float32, device=r.device)
+    check(lib().b200_table_scatter_dot(m, md, wn, r.shape[0], inv_h, n_grid, _p(P), _p(g), _p(coef), _p(r), _p(order), _p(G),
+                                       _p(dot), _stream()), 'table_scatter_dot')
+    return G, dot
+
+
+@_timed
+def table_hermite(Z, dZ, h):
+    """Nodal values / r-derivatives [n_grid + 1, wn] (float64) -> cubic coefficients P[n_grid, 4, wn] (float32)."""
+    n1, wn = Z.shape
+    P = torch.empty(n1 - 1, 4, wn, dtype=torch.float32, device=Z.device)
+    check(lib().b200_table_hermite(n1 - 1, wn, float(h), _p(Z), _p(dZ), _p(P), _stream()), 'table_hermite')
+    return P
+
+
+@_timed
+def table_hermite_adj(G, h):
+    """Adjoint of table_hermite: G[n_grid, 4, wn] (float32) -> (gZ, gdZ) [n_grid + 1, wn] (float64)."""
+    n, _, wn = G.shape
+    gZ = torch.empty(n + 1, wn, dtype=torch.float64, device=G.device)
+    gdZ = torch.empty_like(gZ)
+    check(lib().b200_table_hermite_adj(n, wn, float(h), _p(G), _p(gZ), _p(gdZ), _stream()), 'table_hermite_adj')
+    return gZ, gdZ
+
+
+@_timed
 def table_interp(m, P, inv_h, r, order=None, coef=None):
     """out[e, :] = coef[e] * d^m w / d r^m (r[e]) from per-interval cubic coefficients P[n_grid, 4, wn] on the grid r_i = i / inv_h
     (csrc/table_train.cu)."""
