@@ -170,6 +170,36 @@ table_scatter_kernel(int m, int wn, long long E, float inv_h, int n_grid, const 
         gv[d][u] = (j + d < ne && k < nq) ? __ldcs(reinterpret_cast<const float4*>(g + (size_t)s_e[j + d] * wn) + k)
                                           : make_float4(0.f, 0.f, 0.f, 0.f);
       }
+    if constexpr (DOT) {   // the four edges' dot products first: independent chains, one round of shuffles for all
+      float sdot[4];
+#pragma unroll
+      for (int d = 0; d < 4; ++d) {
+        sdot[d] = 0.f;
+        if (j + d < ne) {
+          const float4* Pi = reinterpret_cast<const float4*>(P + (size_t)s_i[j + d] * 4 * wn);
+          const float q0 = s_qd[j + d][0], q1 = s_qd[j + d][1], q2 = s_qd[j + d][2], q3 = s_qd[j + d][3];
+#pragma unroll
+          for (int u = 0; u < TS_MAXQ; ++u) {
+            const int k = threadIdx.x + u * TS_T;
+            if (k < nq) {
+              const float4 a = __ldg(Pi + k), b = __ldg(Pi + nq + k), c = __ldg(Pi + 2 * nq + k), dd = __ldg(Pi + 3 * nq + k);
+              const float4 v = gv[d][u];
+              sdot[d] += v.x * (q0 * a.x + q1 * b.x + q2 * c.x + q3 * dd.x) + v.y * (q0 * a.y + q1 * b.y + q2 * c.y + q3 * dd.y) +
+                         v.z * (q0 * a.z + q1 * b.z + q2 * c.z + q3 * dd.z) + v.w * (q0 * a.w + q1 * b.w + q2 * c.w + q3 * dd.w);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int d = 0; d < 4; ++d) sdot[d] += __shfl_xor_sync(0xffffffffu, sdot[d], o);
+      if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int d = 0; d < 4; ++d)
+          if (j + d < ne) atomicAdd(&s_dot[j + d], sdot[d]);
+      }
+    }
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
       if (j + d >= ne) break;
@@ -192,24 +222,6 @@ table_scatter_kernel(int m, int wn, long long E, float inv_h, int n_grid, const 
           acc[jj][u].z = fmaf(c, gv[d][u].z, acc[jj][u].z);
           acc[jj][u].w = fmaf(c, gv[d][u].w, acc[jj][u].w);
         }
-      }
-      if constexpr (DOT) {
-        const float4* Pi = reinterpret_cast<const float4*>(P + (size_t)i * 4 * wn);
-        const float q0 = s_qd[j + d][0], q1 = s_qd[j + d][1], q2 = s_qd[j + d][2], q3 = s_qd[j + d][3];
-        float sdot = 0.f;
-#pragma unroll
-        for (int u = 0; u < TS_MAXQ; ++u) {
-          const int k = threadIdx.x + u * TS_T;
-          if (k < nq) {
-            const float4 a = __ldg(Pi + k), b = __ldg(Pi + nq + k), c = __ldg(Pi + 2 * nq + k), dd = __ldg(Pi + 3 * nq + k);
-            const float4 v = gv[d][u];
-            sdot += v.x * (q0 * a.x + q1 * b.x + q2 * c.x + q3 * dd.x) + v.y * (q0 * a.y + q1 * b.y + q2 * c.y + q3 * dd.y) +
-                    v.z * (q0 * a.z + q1 * b.z + q2 * c.z + q3 * dd.z) + v.w * (q0 * a.w + q1 * b.w + q2 * c.w + q3 * dd.w);
-          }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sdot += __shfl_xor_sync(0xffffffffu, sdot, o);
-        if ((threadIdx.x & 31) == 0) atomicAdd(&s_dot[j + d], sdot);
       }
     }
   }

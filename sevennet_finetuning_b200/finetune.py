@@ -55,7 +55,9 @@ class LossDefinition:
     def get_loss(self, batch_data, model=None):
         pred, ref = self._preprocess(batch_data, model)
         weights = self._get_data_weight(batch_data) if self.use_weight else None
-        if self.delete_unlabeled:
+        # a loader that saw the labels on the host can vouch that none is missing (collate): boolean-mask indexing has a
+        # data-dependent size, i.e. a device->host synchronisation per loss term and another in its reverse pass
+        if self.delete_unlabeled and self.ref_key not in batch_data.get('_b200_all_labeled', ()):
             unl = torch.isnan(ref)
             pred, ref = pred[~unl], ref[~unl]
             if len(pred) == 0:
@@ -175,12 +177,14 @@ def collate(graphs, device=None, pin=False):
     if 'data_weight' in graphs[0]:   # dataset.py:430-450: {'per_atom_energy': w, 'force_of_atoms': w, 'stress': w} per structure
         out['data_weight'] = {k: torch.tensor([float(g['data_weight'][k]) for g in graphs], dtype=torch.float32)
                               for k in graphs[0]['data_weight']}
+    labeled = tuple(k for k in ('total_energy', 'force_of_atoms', 'stress') if k in out and not bool(torch.isnan(out[k]).any()))
     if pin:
         out = {k: ({kk: vv.pin_memory() for kk, vv in v.items()} if isinstance(v, dict) else v.pin_memory()) for k, v in out.items()}
     # edges of every structure sorted by their centre atom (what ase / the CUDA cell list emit) stay sorted under the
     # node offsets: let the convolution skip its sortedness check (nn._graph_of)
     if all(bool((torch.as_tensor(g['edge_index'])[0][1:] >= torch.as_tensor(g['edge_index'])[0][:-1]).all()) for g in graphs):
         out['_b200_dst_sorted'] = True
+    out['_b200_all_labeled'] = labeled   # keys whose labels hold no NaN: the losses skip their unlabelled-entry filter
     if device is not None:
         out = to_device(out, device)
     return out

@@ -64,6 +64,7 @@ class EdgeB(Function):
     def forward(ctx, vec, coeffs, gY, gemb, params):
         ctx.save_for_backward(vec, coeffs, gY, gemb)
         ctx.params = params
+        ctx.set_materialize_grads(False)   # an output nobody differentiates arrives as None, not as zeros to be tested on the host
         v, k = _c(vec.detach()), _c(coeffs.detach())
         gY_ = None if gY is None else _c(gY.detach())
         ge_ = None if gemb is None else _c(gemb.detach())

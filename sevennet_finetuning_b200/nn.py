@@ -50,9 +50,8 @@ def _graph_of(data):
         perm = torch.argsort(dst64, stable=True)
         dst64, src64 = dst64[perm], src64[perm]
     dst, src = dst64.to(torch.int32).contiguous(), src64.to(torch.int32).contiguous()
-    rowptr = torch.zeros(n_src + 1, dtype=torch.int32, device=ei.device)
-    if E:
-        rowptr[1:] = torch.cumsum(torch.bincount(dst64, minlength=n_src), 0).to(torch.int32)
+    # CSR offsets of the sorted destinations (bincount would read its output size back from the device)
+    rowptr = torch.searchsorted(dst64, torch.arange(n_src + 1, device=ei.device, dtype=dst64.dtype)).to(torch.int32)
     rrowptr, eid = ops.csr_transpose(n_src, src)
     g = dict(key=(ei.data_ptr(), ei.shape[1]), perm=perm, dst=dst, src=src, rowptr=rowptr, rrowptr=rrowptr, eid=eid,
              n_dst=n, n_src=n_src, rowptr_dst=rowptr[:n + 1].contiguous())
@@ -271,8 +270,8 @@ class EdgeEmbedding(nn.Module):
             h = r_on / math.floor(r_on / h + 0.5)
         inv_h = float(torch.tensor(1.0 / h, dtype=torch.float32))
         n_grid = int(math.ceil(rc * inv_h)) + 1
-        r = torch.arange(n_grid + 1, dtype=torch.float64, device=device) / inv_h
-        r[0] = 1e-6                               # sin(k r) / r at r = 0; no edge is that short
+        # (first point 1e-6 instead of 0: sin(k r) / r; no edge is that short)
+        r = (torch.arange(n_grid + 1, dtype=torch.float64, device=device) / inv_h).clamp_(min=1e-6)
         k = b.coeffs.to(torch.float64)
         ur, kr = r.unsqueeze(1), r.unsqueeze(1) * k.unsqueeze(0)
         bes = (2.0 / rc) * torch.sin(kr) / ur
