@@ -86,6 +86,7 @@ struct Layer {
   int lout;
   bool table;   // per-edge weights interpolated from the tabulated radial function (radial_table.cu)
   bool tabconv; // ... inside the convolution kernels: neither the weights nor their gradient are materialised
+  bool si1_cm;  // ... and self_interaction_1 produces / consumes that row layout directly
   bool pair;    // ... by the channel-pair kernels (conv_pair.cu): packed table, component-major source rows
 };
 
@@ -184,6 +185,10 @@ extern "C" int b200_model_create(const B200ModelConfig* cfg, B200Model** out) {
     L.table = radial_table_supported(L.mlp) && !(getenv("B200_RADIAL_TABLE") && atoi(getenv("B200_RADIAL_TABLE")) == 0);
     L.tabconv = L.table && !(getenv("B200_TABLE_IN_CONV") && atoi(getenv("B200_TABLE_IN_CONV")) == 0);
     L.pair = L.tabconv && conv_pair_supported(L.conv) && !(getenv("B200_CONV_PAIR") && atoi(getenv("B200_CONV_PAIR")) == 0);
+    // self_interaction_1 writes (and its transposed product reads) the component-major rows of the pair kernels itself
+    // (linear_tc.cu) instead of a transposition pass either way; B200_LINEAR_CM=0: the separate passes
+    L.si1_cm = L.pair && irreps_linear_tc_supported(L.si1, 0, kLinYcm) && irreps_linear_tc_supported(L.si1, 1, kLinXcm) &&
+               !(getenv("B200_LINEAR_CM") && atoi(getenv("B200_LINEAR_CM")) == 0);
     m->layers.push_back(L);
     m->split_bwd_x = getenv("B200_SPLIT_BWD_X") && atoi(getenv("B200_SPLIT_BWD_X")) != 0;
     const std::string s = std::to_string(t);
@@ -404,9 +409,15 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     OP(CAT_NODE, irreps_linear(L.sc, N, x, P(m, s + "_self_connection_intro.linear.weight"), b.gin[t], 0, 0, st));
     // layer 0: ghost rows are recomputed from their types (model_build.py:134-172 "ghost_" modules);
     // later layers: the owners' rows are fetched through the halo hook
-    OP(CAT_NODE, irreps_linear(L.si1, t == 0 ? NA : N, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
     // the channel-pair kernels read component-major rows; ghost rows arrive from their owners already transposed
-    if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, t == 0 ? NA : N, b.xs[t], 0, st));
+    const int n_si1 = t == 0 ? NA : N;
+    const bool cm = L.si1_cm && n_si1 >= 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+    if (cm) {
+      OP(CAT_NODE, irreps_linear_tc(L.si1, n_si1, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st, kLinYcm));
+    } else {
+      OP(CAT_NODE, irreps_linear(L.si1, n_si1, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+      if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, n_si1, b.xs[t], 0, st));
+    }
     if (t > 0) HALO(B200_HALO_FWD_X, t, b.xs[t], L.conv.xdim);
     const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
     const float* W1 = P(m, s + "_convolution.weight_nn.layer1.weight");
@@ -494,8 +505,12 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
       if (!L.tabconv && m->split_bwd_x)
         OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
-      if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, N, b.conv_out, 1, st));   // back to the standard row layout
-      OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
+      if (L.si1_cm && N >= 64 && (reinterpret_cast<uintptr_t>(b.conv_out) & 15) == 0) {
+        OP(CAT_NODE, irreps_linear_tc(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st, kLinXcm));
+      } else {
+        if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, N, b.conv_out, 1, st));   // back to the standard row layout
+        OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
+      }
       std::swap(g, gp);
     }
   }

@@ -35,11 +35,13 @@ struct LinTcBlock {
   int pack_off;               // float offset of the pass's operand pack
   int w_off, ldw;             // block offset in the flat weight vector, its row length (mul_out)
   int nchunk;                 // ceil(K / 16)
+  int Nblk;                   // output channels of the whole l-block (row length of a component in a component-major block)
   float scale;
 };
 struct LinTcPlan {
   int npass;
   int ldx, ldy;
+  int x_cm, y_cm;             // component-major blocks ([2l+1][mul] instead of [mul][2l+1]) on the input / output side
   int nblk, blk_first[16], blk_npass[16];   // groups of consecutive passes of one l-block: one CTA runs a group back to back
   LinTcBlock p[16];
 };
@@ -174,7 +176,8 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, int 
         for (int r = 0; r < 32; ++r) {
           const int orow = 32 * q + r, nl = orow / D, m = orow % D;
           if (nl >= nn) break;
-          float* p = y + (size_t)(n0 + nl) * pl.ldy + bp.yoff + (size_t)(bp.o0 + o) * D + m;
+          float* p = y + (size_t)(n0 + nl) * pl.ldy + bp.yoff +
+                     (pl.y_cm ? (size_t)m * bp.Nblk + (bp.o0 + o) : (size_t)(bp.o0 + o) * D + m);
           const float val = T[r][lane] * bp.scale;
           *p = accumulate ? (*p + val) : val;
         }
@@ -201,26 +204,30 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, int 
 #pragma unroll
   for (int u = 0; u < 2; ++u) {
     const int id = threadIdx.x + u * L_T, nl = id / PPN, p = id % PPN;
-    pfl[u] = id < TN * PPN ? p * 4 : (1 << 20);
-    psrc[u] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + p * 4;
+    // component-major input: piece p = (component p / 4, quarter p % 4 of its 16 k); the slot then holds [m][16 k]
+    pfl[u] = id < TN * PPN ? (pl.x_cm ? (p & 3) * 4 : p * 4) : (1 << 20);
+    psrc[u] = x + (size_t)(n0 + min(nl, nn - 1)) * pl.ldx + b.xoff + (pl.x_cm ? (p >> 2) * b.K + (p & 3) * 4 : p * 4);
     pdst[u] = smem_u32(&s.S[0][0]) + (uint32_t)(nl * RS + p * 4) * 4;
   }
+  const int cstep = pl.x_cm ? LK : LK * D;       // floats between the chunks of a piece
   auto stage = [&](int g) {                      // request stream position g (nothing past the end; the group is still committed)
     if (g < G) {
       const int c = g % nchunk;
-      const int kfl = min(LK, b.K - c * LK) * D; // valid floats of a node's chunk
+      const int kfl = min(LK, b.K - c * LK) * (pl.x_cm ? 1 : D);   // valid floats of a node's chunk (of one component of it)
       const uint32_t slot = (uint32_t)(g % L_NS) * (L_SFLOATS * 4);
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         const int nb = min(16, max(0, (kfl - pfl[u]) * 4));
         if (pfl[u] < (1 << 20))
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(pdst[u] + slot), "l"(psrc[u] + (size_t)c * (LK * D)), "r"(nb) : "memory");
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(pdst[u] + slot), "l"(psrc[u] + (size_t)c * cstep), "r"(nb) : "memory");
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
   const int row = threadIdx.x & 127, kp = threadIdx.x >> 7;
-  const int soff = min(row / D, TN - 1) * RS + kp * 8 * D + row % D;   // this thread's first element inside a slot
+  // this thread's first element inside a slot, and the distance between its k's
+  const int soff = min(row / D, TN - 1) * RS + (pl.x_cm ? (row % D) * LK + kp * 8 : kp * 8 * D + row % D);
+  const int sk = pl.x_cm ? 1 : D;
   const uint32_t aoff = (uint32_t)(2 * kp) * L_ACH + (uint32_t)row * 16;
   stage(0);
   stage(1);
@@ -238,7 +245,7 @@ __device__ __forceinline__ void lin_tile(LinTcSmem& s, const LinTcPlan& pl, int 
     {
       const float* sp = &s.S[g % L_NS][soff];
       float4 v0, v1, h0, l0, h1, l1;
-      if (D == 1) {
+      if (D == 1 || sk == 1) {
         v0 = *reinterpret_cast<const float4*>(sp);
         v1 = *reinterpret_cast<const float4*>(sp + 4);
       } else {
@@ -285,7 +292,9 @@ irreps_linear_tc_kernel(LinTcPlan pl, int n_nodes, const float* __restrict__ x, 
 }
 
 // plan: one pass per (block, <=256 output columns); returns false when a block is too small for the tensor-core path
-static bool build_lin_plan(const LinDesc& d, int transpose, int n_nodes, LinTcPlan& pl, size_t* pack_floats) {
+static bool build_lin_plan(const LinDesc& d, int transpose, int n_nodes, LinTcPlan& pl, size_t* pack_floats, int layout = 0) {
+  pl.x_cm = layout & 1;
+  pl.y_cm = (layout >> 1) & 1;
   pl.npass = 0;
   pl.nblk = 0;
   pl.ldx = transpose ? d.out_dim : d.in_dim;
@@ -296,6 +305,7 @@ static bool build_lin_plan(const LinDesc& d, int transpose, int n_nodes, LinTcPl
     const int K = transpose ? lb.mul_out : lb.mul_in, N = transpose ? lb.mul_in : lb.mul_out;
     if (K < 16 || N < 16) return false;
     if ((pl.ldx & 3) || ((transpose ? lb.out_off : lb.in_off) & 3)) return false;   // 16-byte cp.async pieces of the rows
+    if (pl.x_cm && (K & 3)) return false;   // component rows of a component-major block start on 16-byte boundaries
     const int npass = (N + L_MAXN - 1) / L_MAXN;
     // One CTA streams several passes of its tile (no TMEM allocation, pipeline refill and barrier setup per pass: with
     // K = 32 a pass is two chunks long) as long as that leaves at least two CTAs per resident slot; small inputs (the
@@ -320,6 +330,7 @@ static bool build_lin_plan(const LinDesc& d, int transpose, int n_nodes, LinTcPl
       b.xoff = transpose ? lb.out_off : lb.in_off;
       b.yoff = transpose ? lb.in_off : lb.out_off;
       b.nchunk = (K + LK - 1) / LK;
+      b.Nblk = N;
       b.scale = lb.scale;
       b.w_off = lb.w_off;
       b.ldw = lb.mul_out;
@@ -332,18 +343,18 @@ static bool build_lin_plan(const LinDesc& d, int transpose, int n_nodes, LinTcPl
   return pl.npass > 0;
 }
 
-bool irreps_linear_tc_supported(const LinDesc& d, int transpose) {
+bool irreps_linear_tc_supported(const LinDesc& d, int transpose, int layout) {
   LinTcPlan pl;
   size_t n;
   if (d.nblk < 1 || d.nblk > 4) return false;
-  return build_lin_plan(d, transpose, 1 << 30, pl, &n);
+  return build_lin_plan(d, transpose, 1 << 30, pl, &n, layout);
 }
 
 int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
-                     cudaStream_t st) {
+                     cudaStream_t st, int layout) {
   LinTcPlan pl;
   size_t pack_floats;
-  B200_REQUIRE(build_lin_plan(d, transpose, n_nodes, pl, &pack_floats), "irreps_linear_tc: unsupported shape");
+  B200_REQUIRE(build_lin_plan(d, transpose, n_nodes, pl, &pack_floats, layout), "irreps_linear_tc: unsupported shape");
   if (n_nodes == 0) return B200_OK;
   float* pack;
   keep_async_pool();
