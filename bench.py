@@ -25,7 +25,6 @@ import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 import numpy as np
@@ -52,14 +51,15 @@ _JSON_OUT = None
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons during the timed region (B200_PROFILING.md recipe), read through NVML in-process (the
+    counters nvidia-smi prints; spawning nvidia-smi from a process that maps >100 GB of device memory stalls the launching
+    thread for tens of milliseconds per sample).  One sample per timed step, taken by the MAIN thread right after it has
+    queued the step - the GPU is executing that step then.  A sampling thread beside the launching thread was the first
+    version: its NVML queries collided with the kernel launches in the driver and cost single timed steps 10-300 ms
+    (2 runs of 6, always the second step; none of 6 without the thread)."""
 
     def __init__(self, index):
-        self.rows, self.stop, self.index = [], False, index
-        self.t = threading.Thread(target=self._run, daemon=True)
-        # NVML in-process (the same counters nvidia-smi prints): spawning nvidia-smi from a process that maps >100 GB
-        # of device memory stalls the launching thread for tens of milliseconds per sample.  The library is loaded and
-        # initialised HERE, before the timed region (nvmlInit inside it cost one timed step 6-23 ms); the thread only queries.
+        self.rows, self.index = [], index
         self.nv = None
         try:
             import pynvml as nv
@@ -68,46 +68,33 @@ class ClockSampler:
             self.mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
             self.get_reasons = getattr(nv, 'nvmlDeviceGetCurrentClocksEventReasons', None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
             self.get_reasons(self.h)
+            self.bits = [(getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8), 0), (getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40), 1),
+                         (getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20), 2), (getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4), 3)]
             self.nv = nv
         except Exception:
             self.nv = None
 
-    def _run(self):
+    def sample(self):
         if self.nv is not None:
-            nv, h, mx = self.nv, self.h, self.mx
-            bits = [(getattr(nv, 'nvmlClocksEventReasonHwSlowdown', 0x8), 0), (getattr(nv, 'nvmlClocksEventReasonHwThermalSlowdown', 0x40), 1),
-                    (getattr(nv, 'nvmlClocksEventReasonSwThermalSlowdown', 0x20), 2), (getattr(nv, 'nvmlClocksEventReasonSwPowerCap', 0x4), 3)]
             try:
-                while not self.stop:
-                    r = self.get_reasons(h)
-                    flags = ['Not Active'] * 4
-                    for bit, k in bits:
-                        if r & bit:
-                            flags[k] = 'Active'
-                    self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(mx)] + flags)
-                    time.sleep(0.05)
+                r = self.get_reasons(self.h)
+                flags = ['Not Active'] * 4
+                for bit, k in self.bits:
+                    if r & bit:
+                        flags[k] = 'Active'
+                self.rows.append([str(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)), str(self.mx)] + flags)
                 return
             except Exception:
-                pass
+                self.nv = None
         q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
-        while not self.stop:
-            try:
-                out = subprocess.run(['nvidia-smi', f'--id={self.index}', f'--query-gpu={q}', '--format=csv,noheader,nounits'],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([t.strip() for t in out.split(',')])
-            except Exception:
-                pass
-            time.sleep(0.1)
-
-    def __enter__(self):
-        self.t.start()
-        return self
-
-    def __exit__(self, *a):
-        self.stop = True
-        self.t.join(timeout=6)
+        try:
+            out = subprocess.run(['nvidia-smi', f'--id={self.index}', f'--query-gpu={q}', '--format=csv,noheader,nounits'],
+                                 capture_output=True, text=True, timeout=5).stdout.strip()
+            if out:
+                self.rows.append([t.strip() for t in out.split(',')])
+        except Exception:
+            pass
 
     def summary(self):
         if not self.rows:
@@ -427,6 +414,8 @@ def finetune_bench(a, rank, world, local, warmup, cpu_baseline=True, clocks=True
         e0.record()
         for _ in range(steps):
             out = fn()
+            if cs:
+                cs.sample()   # the step is queued, the GPU is executing it
         e1.record()
         barrier()
         wall = time.perf_counter() - t0
@@ -435,21 +424,20 @@ def finetune_bench(a, rank, world, local, warmup, cpu_baseline=True, clocks=True
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), out
 
-    cs = ClockSampler(local)
-    if clocks:
-        cs.__enter__()   # before the warm-up: the sampler's start-up cost stays out of the timed steps
+    cs = ClockSampler(local) if clocks else None
     for _ in range(warmup):
         step_resident()
+        if cs:
+            cs.sample()
     launches0 = L.b200_launch_count()
     torch.cuda.synchronize()
-    cs.rows = []
+    if cs:
+        cs.rows = []
     t_res, _ = timed(step_resident, a.steps)
     launches = L.b200_launch_count() - launches0
     for _ in range(2):
         step_e2e()
     t_e2e, losses = timed(step_e2e, a.steps)
-    if clocks:
-        cs.__exit__()
     # which kernel family dominates: per-op CUDA events over two extra (untimed) steps
     ops.enable_timing(True)
     step_resident()
@@ -604,6 +592,7 @@ def main():
             ev = torch.cuda.Event(enable_timing=True)
             ev.record()
             evs.append(ev)
+            cs.sample()   # the step is queued, the GPU is executing it
         e1.record()
         barrier()
         wall = time.perf_counter() - t0
@@ -620,14 +609,13 @@ def main():
         parity = parity_vs_reference(model, a.cpu_atoms) if par is None else parity_parallel(model, par, dev)
     except Exception as ex:
         parity = {'error': repr(ex)[:300]}
-    # the clock sampler and the engine's per-category events are switched on BEFORE the warm-up steps: the sampler thread's
-    # start and first NVML queries, and the first event creations, otherwise land in the timed steps (the second timed step
-    # measured 1.1-5x the others in several runs); what they record during warm-up is discarded below
+    # the clock sampler and the engine's per-category events are switched on BEFORE the warm-up steps: the first NVML
+    # queries and the first event creations otherwise land in the timed steps; what they record during warm-up is discarded
     cs = ClockSampler(local)
-    cs.__enter__()
     L.b200_model_set_timing(model._h, 1)
     for _ in range(warmup):
         out = step_resident()
+        cs.sample()
     if par is None:
         n_edges, n_own = int(out['graph']['src'].shape[0]), n_total
     else:
@@ -638,21 +626,18 @@ def main():
         n_edges, n_own = int(per_rank[:, 0].sum()), int(out['n_local'])
         cfg['per_rank'] = {'edges': per_rank[:, 0].tolist(), 'local': per_rank[:, 1].tolist(), 'ghost': per_rank[:, 2].tolist()}
     launches0 = L.b200_launch_count()
-    try:
-        torch.cuda.synchronize()
-        L.b200_model_set_timing(model._h, 1)   # resets the accumulated events of the warm-up
-        cs.rows = []
-        t_res, out = timed(step_resident, a.steps)
-        per_step_res = list(timed.per_step)
-        cat = (C.c_float * 9)()
-        L.b200_model_get_timing(model._h, cat, 9)
-        L.b200_model_set_timing(model._h, 0)
-        launches = L.b200_launch_count() - launches0
-        for _ in range(2):
-            step_e2e()
-        t_e2e, _ = timed(step_e2e, a.steps)
-    finally:
-        cs.__exit__()
+    torch.cuda.synchronize()
+    L.b200_model_set_timing(model._h, 1)   # resets the accumulated events of the warm-up
+    cs.rows = []
+    t_res, out = timed(step_resident, a.steps)
+    per_step_res = list(timed.per_step)
+    cat = (C.c_float * 9)()
+    L.b200_model_get_timing(model._h, cat, 9)
+    L.b200_model_set_timing(model._h, 0)
+    launches = L.b200_launch_count() - launches0
+    for _ in range(2):
+        step_e2e()
+    t_e2e, _ = timed(step_e2e, a.steps)
     clocks = cs.summary()
     N, E = n_total, n_edges
     value = N * a.steps / t_res
