@@ -119,10 +119,14 @@ def _finetune_loss(out, lab, n):
     return le + 1.0 * lf + 0.01 * ls
 
 
-def test_parameter_gradients_of_force_stress_loss(twin, gold, weights):
+@pytest.mark.parametrize('train_table', [True, False])
+def test_parameter_gradients_of_force_stress_loss(twin, gold, weights, train_table, monkeypatch):
     """The fine-tuning gradient: d L(E, F, S) / d theta with F = -dE/dr taken with create_graph=True
     (sevenn/nn/force_output.py:165-170, sevenn/train/trainer.py:173-186) - a reverse pass through the reverse pass of
-    every kernel - against double-precision autograd through the oracle model."""
+    every kernel - against double-precision autograd through the oracle model.  train_table: weight_nn read from the per-step
+    table over the edge length (csrc/table_train.cu, the default) or evaluated once per edge (B200_TRAIN_TABLE=0)."""
+    import sevennet_finetuning_b200.nn as b200nn
+    monkeypatch.setattr(b200nn, '_TRAIN_TABLE', train_table)
     g = gold('hfo2_96.npz')
     dev = torch.device('cuda:0')
     n = len(g['pos'])

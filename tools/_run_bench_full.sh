@@ -2,4 +2,4 @@ cd /root/repo
 mkdir -p gpurun_out
 timeout 900 python bench.py > gpurun_out/bench_full.json 2> gpurun_out/bench_full.err; echo "rc=$?" >> gpurun_out/bench_full.err
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "rc=$?" >> gpurun_out/bench_ref.err
-tail -3 gpurun_out/bench_full.err gpurun_out/bench_ref.err
+tail -n 3 gpurun_out/bench_full.err; tail -n 3 gpurun_out/bench_ref.err
