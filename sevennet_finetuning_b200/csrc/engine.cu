@@ -106,6 +106,9 @@ struct B200Model {
   bool split_bwd_x = false;   // B200_SPLIT_BWD_X=1: d x[src] by the separate source-sorted kernel (deterministic sums)
   std::vector<float*> tables; // per layer: tabulated radial weights (device), rebuilt when a parameter changes
   bool tables_dirty = true;
+  // hi / lo operand packs of the tensor-core linears, one per (weight, transposed?): built at the first call after a
+  // parameter change, reused by every call after it
+  std::map<std::pair<const float*, int>, float*> packs;
   std::vector<cudaEvent_t> ev;
   std::vector<int> ev_cat;
   size_t ev_used = 0;
@@ -154,6 +157,9 @@ extern "C" int b200_model_get_timing(B200Model* m, float* ms_out, int n_out) {
   m->ev_used = 0;
   return B200_OK;
 }
+
+// slot of the operand pack of (weight, transposed?) in the model's cache
+static float** PACK(B200Model* m, const float* W, int transpose) { return &m->packs[{W, transpose}]; }
 
 static float* P(B200Model* m, const std::string& name) {
   auto it = m->params.find(name);
@@ -234,6 +240,11 @@ extern "C" int b200_model_set_param(B200Model* m, const char* name, const float*
     return B200_ERR_CUDA;
   }
   m->tables_dirty = true;
+  if (!m->packs.empty()) {
+    cudaDeviceSynchronize();
+    for (auto& kv : m->packs) cudaFree(kv.second);
+    m->packs.clear();
+  }
   const std::string nm(name);
   const std::string suffix = "_convolution.denominator";
   if (nm.size() > suffix.size() && nm.compare(nm.size() - suffix.size(), suffix.size(), suffix) == 0)
@@ -245,6 +256,7 @@ extern "C" void b200_model_destroy(B200Model* m) {
   if (!m) return;
   for (auto& kv : m->params) cudaFree(kv.second.first);
   for (auto t : m->tables) cudaFree(t);
+  for (auto& kv : m->packs) cudaFree(kv.second);
   for (auto e : m->ev) cudaEventDestroy(e);
   delete m;
 }
@@ -402,20 +414,26 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   float* xn = b.x[1];
   OP(CAT_NODE, embed_fwd(NA, c.n_species, c.mul[0][0], types, P(m, "onehot_to_feature_x.linear.weight"), x, st));
   const std::vector<float>& denom = m->denom;
+  // a node linear with the named weight; its tensor-core operand pack is kept in the model between calls
+  auto lin = [&](const LinDesc& d, int n, const float* xin, const std::string& name, float* yout, int transpose, int accumulate) {
+    const float* W = P(m, name);
+    return irreps_linear(d, n, xin, W, yout, transpose, accumulate, st, PACK(m, W, transpose));
+  };
   for (int t = 0; t < nl; ++t) {
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
     if (!lin_covers_output(L.sc)) cudaMemsetAsync(b.gin[t], 0, sizeof(float) * (size_t)N * L.sc.out_dim, st);
-    OP(CAT_NODE, irreps_linear(L.sc, N, x, P(m, s + "_self_connection_intro.linear.weight"), b.gin[t], 0, 0, st));
+    OP(CAT_NODE, lin(L.sc, N, x, s + "_self_connection_intro.linear.weight", b.gin[t], 0, 0));
     // layer 0: ghost rows are recomputed from their types (model_build.py:134-172 "ghost_" modules);
     // later layers: the owners' rows are fetched through the halo hook
     // the channel-pair kernels read component-major rows; ghost rows arrive from their owners already transposed
     const int n_si1 = t == 0 ? NA : N;
     const bool cm = L.si1_cm && n_si1 >= 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
     if (cm) {
-      OP(CAT_NODE, irreps_linear_tc(L.si1, n_si1, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st, kLinYcm));
+      OP(CAT_NODE, irreps_linear_tc(L.si1, n_si1, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st, kLinYcm,
+                                    PACK(m, P(m, s + "_self_interaction_1.linear.weight"), 0)));
     } else {
-      OP(CAT_NODE, irreps_linear(L.si1, n_si1, x, P(m, s + "_self_interaction_1.linear.weight"), b.xs[t], 0, 0, st));
+      OP(CAT_NODE, lin(L.si1, n_si1, x, s + "_self_interaction_1.linear.weight", b.xs[t], 0, 0));
       if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, n_si1, b.xs[t], 0, st));
     }
     if (t > 0) HALO(B200_HALO_FWD_X, t, b.xs[t], L.conv.xdim);
@@ -437,12 +455,12 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
         OP(CAT_CONV_FWD, conv_fwd(L.conv, N, rowptr, src, b.xs[t], b.Y, b.w[t], denom[t], b.conv_out, st));
       }
     }
-    OP(CAT_NODE, irreps_linear(L.si2, N, b.conv_out, P(m, s + "_self_interaction_2.linear.weight"), b.gin[t], 0, 1, st));
+    OP(CAT_NODE, lin(L.si2, N, b.conv_out, s + "_self_interaction_2.linear.weight", b.gin[t], 0, 1));
     OP(CAT_NODE, gate_fwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], xn, st));
     std::swap(x, xn);
   }
-  OP(CAT_NODE, irreps_linear(m->r1, N, x, P(m, "reduce_input_to_hidden.linear.weight"), b.h, 0, 0, st));
-  OP(CAT_NODE, irreps_linear(m->r2, N, b.h, P(m, "reduce_hidden_to_energy.linear.weight"), b.s, 0, 0, st));
+  OP(CAT_NODE, lin(m->r1, N, x, "reduce_input_to_hidden.linear.weight", b.h, 0, 0));
+  OP(CAT_NODE, lin(m->r2, N, b.h, "reduce_hidden_to_energy.linear.weight", b.s, 0, 0));
   OP(CAT_NODE, rescale_fwd(N, types, b.s, P(m, "rescale_atomic_energy.scale"), P(m, "rescale_atomic_energy.shift"),
                   c.species_wise_rescale, atomic_energy, st));
   OP(CAT_NODE, colsum(N, 1, atomic_energy, energy, st));
@@ -451,10 +469,10 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
   if (N > 0)
     rescale_bwd_kernel<<<(N + 255) / 256, 256, 0, st>>>(N, types, P(m, "rescale_atomic_energy.scale"),
                                                         c.species_wise_rescale, b.g_s);
-  OP(CAT_NODE, irreps_linear(m->r2, N, b.g_s, P(m, "reduce_hidden_to_energy.linear.weight"), b.g_h, 1, 0, st));
+  OP(CAT_NODE, lin(m->r2, N, b.g_s, "reduce_hidden_to_energy.linear.weight", b.g_h, 1, 0));
   float* g = b.g_x[0];
   float* gp = b.g_x[1];
-  OP(CAT_NODE, irreps_linear(m->r1, N, b.g_h, P(m, "reduce_input_to_hidden.linear.weight"), g, 1, 0, st));
+  OP(CAT_NODE, lin(m->r1, N, b.g_h, "reduce_input_to_hidden.linear.weight", g, 1, 0));
   bool dy_written = false, ddr_written = false, demb_written = false;   // which per-edge gradient buffers hold a sum already
   {   // the channel-pair kernels ADD their d Y and d E / d r into the per-edge buffers
     bool any_pair = false;
@@ -469,7 +487,7 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     const Layer& L = m->layers[t];
     const std::string s = std::to_string(t);
     OP(CAT_NODE, gate_bwd(L.out[0], L.out[1], L.out[2], N, b.gin[t], g, b.g_gin, st));
-    OP(CAT_NODE, irreps_linear(L.si2, N, b.g_gin, P(m, s + "_self_interaction_2.linear.weight"), b.g_conv, 1, 0, st));
+    OP(CAT_NODE, lin(L.si2, N, b.g_gin, s + "_self_interaction_2.linear.weight", b.g_conv, 1, 0));
     const float* W0 = P(m, s + "_convolution.weight_nn.layer0.weight");
     const float* W1 = P(m, s + "_convolution.weight_nn.layer1.weight");
     const float* W2 = P(m, s + "_convolution.weight_nn.layer2.weight");
@@ -501,15 +519,16 @@ extern "C" int b200_model_compute_halo(B200Model* m, int N, int n_ghost, int64_t
     }
     if (t > 0) {
       if (!lin_covers_input(L.sc)) cudaMemsetAsync(gp, 0, sizeof(float) * (size_t)N * L.sc.in_dim, st);
-      OP(CAT_NODE, irreps_linear(L.sc, N, b.g_gin, P(m, s + "_self_connection_intro.linear.weight"), gp, 1, 0, st));
+      OP(CAT_NODE, lin(L.sc, N, b.g_gin, s + "_self_connection_intro.linear.weight", gp, 1, 0));
       if (!L.tabconv && m->split_bwd_x)
         OP(CAT_CONV_BWD_X, conv_bwd_x(L.conv, NA, b.rrowptr, b.eid, dst, b.g_conv, b.Y, b.w[t], denom[t], b.conv_out, st));
       HALO(B200_HALO_BWD_X, t, b.conv_out, L.conv.xdim);   // ghost rows are added into their owners' rows
       if (L.si1_cm && N >= 64 && (reinterpret_cast<uintptr_t>(b.conv_out) & 15) == 0) {
-        OP(CAT_NODE, irreps_linear_tc(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st, kLinXcm));
+        OP(CAT_NODE, irreps_linear_tc(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st, kLinXcm,
+                                    PACK(m, P(m, s + "_self_interaction_1.linear.weight"), 1)));
       } else {
         if (L.pair) OP(CAT_NODE, conv_pair_interleave(L.conv, N, b.conv_out, 1, st));   // back to the standard row layout
-        OP(CAT_NODE, irreps_linear(L.si1, N, b.conv_out, P(m, s + "_self_interaction_1.linear.weight"), gp, 1, 1, st));
+        OP(CAT_NODE, lin(L.si1, N, b.conv_out, s + "_self_interaction_1.linear.weight", gp, 1, 1));
       }
       std::swap(g, gp);
     }

@@ -240,13 +240,13 @@ static bool lin_ok(const LinDesc& d) {
 }
 
 int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
-                  cudaStream_t st) {
+                  cudaStream_t st, float** pack_cache) {
   B200_REQUIRE(lin_ok(d), "irreps_linear: 1..4 blocks with 2l+1 in {1,3,5}");
   if (n_nodes == 0) return B200_OK;
   // dense channel mixing belongs on the tensor cores (linear_tc.cu); tiny blocks and tiny inputs stay on the FFMA kernel
   static const bool force_ffma = getenv("B200_LINEAR_FFMA") && atoi(getenv("B200_LINEAR_FFMA")) != 0;
   if (!force_ffma && n_nodes >= 64 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && irreps_linear_tc_supported(d, transpose))
-    return irreps_linear_tc(d, n_nodes, x, W, y, transpose, accumulate, st);
+    return irreps_linear_tc(d, n_nodes, x, W, y, transpose, accumulate, st, 0, pack_cache);
   int maxn = 0;
   for (int i = 0; i < d.nblk; ++i) maxn = max(maxn, transpose ? d.blk[i].mul_in : d.blk[i].mul_out);
   dim3 grid((n_nodes + (LT_M / 5) - 1) / (LT_M / 5), (maxn + LT_N - 1) / LT_N, d.nblk);

@@ -350,19 +350,34 @@ bool irreps_linear_tc_supported(const LinDesc& d, int transpose, int layout) {
   return build_lin_plan(d, transpose, 1 << 30, pl, &n, layout);
 }
 
+// pack_cache (optional): where the caller keeps the hi / lo operand pack of THIS (W, transpose) between calls - the weights
+// of an inference engine are constants, splitting them again in every call is 30 launches per force call for nothing.  The
+// pack layout does not depend on n_nodes.  nullptr: the pack lives for the call (stream-ordered allocation).
 int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
-                     cudaStream_t st, int layout) {
+                     cudaStream_t st, int layout, float** pack_cache) {
   LinTcPlan pl;
   size_t pack_floats;
   B200_REQUIRE(build_lin_plan(d, transpose, n_nodes, pl, &pack_floats, layout), "irreps_linear_tc: unsupported shape");
   if (n_nodes == 0) return B200_OK;
   float* pack;
-  keep_async_pool();
-  if (cudaMallocAsync((void**)&pack, pack_floats * sizeof(float), st) != cudaSuccess) {
-    set_error("irreps_linear_tc: cudaMallocAsync of the operand pack failed");
-    return B200_ERR_CUDA;
+  bool fresh = true;
+  if (pack_cache && *pack_cache) {
+    pack = *pack_cache;
+    fresh = false;
+  } else if (pack_cache) {
+    if (cudaMalloc((void**)&pack, pack_floats * sizeof(float)) != cudaSuccess) {
+      set_error("irreps_linear_tc: cudaMalloc of the operand pack failed");
+      return B200_ERR_CUDA;
+    }
+    *pack_cache = pack;
+  } else {
+    keep_async_pool();
+    if (cudaMallocAsync((void**)&pack, pack_floats * sizeof(float), st) != cudaSuccess) {
+      set_error("irreps_linear_tc: cudaMallocAsync of the operand pack failed");
+      return B200_ERR_CUDA;
+    }
   }
-  linear_prepack_kernel<<<dim3(16, pl.npass), 256, 0, st>>>(pl, W, transpose, pack);
+  if (fresh) linear_prepack_kernel<<<dim3(16, pl.npass), 256, 0, st>>>(pl, W, transpose, pack);
   cudaFuncSetAttribute(irreps_linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LinTcSmem));
   int mind = 5;
   for (int p = 0; p < pl.npass; ++p) mind = pl.p[p].D < mind ? pl.p[p].D : mind;
@@ -371,8 +386,8 @@ int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float*
   const int tn = 128 / maxd;   // the widest irrep has the fewest nodes per tile; surplus CTAs of the others exit
   dim3 grid((n_nodes + tn - 1) / tn, pl.nblk);
   irreps_linear_tc_kernel<<<grid, L_TT, sizeof(LinTcSmem), st>>>(pl, n_nodes, x, pack, y, accumulate);
-  cudaFreeAsync(pack, st);
-  return check_launch("irreps_linear_tc", 2);
+  if (!pack_cache) cudaFreeAsync(pack, st);
+  return check_launch("irreps_linear_tc", fresh ? 2 : 1);
 }
 
 }  // namespace b200

@@ -83,13 +83,13 @@ int radial_table_bwd(const EdgeParams& p, const MlpDesc& d, long long E, const f
 
 
 int irreps_linear(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
-                  cudaStream_t st);
+                  cudaStream_t st, float** pack_cache = nullptr);
 // layout bit 0 / bit 1: the l-blocks of the input / output rows are component-major ([2l+1][mul] instead of [mul][2l+1]),
 // the row layout of the channel-pair convolution kernels (conv_pair.cu)
 constexpr int kLinXcm = 1, kLinYcm = 2;
 bool irreps_linear_tc_supported(const LinDesc& d, int transpose, int layout = 0);
 int irreps_linear_tc(const LinDesc& d, int n_nodes, const float* x, const float* W, float* y, int transpose, int accumulate,
-                     cudaStream_t st, int layout = 0);
+                     cudaStream_t st, int layout = 0, float** pack_cache = nullptr);
 int irreps_linear_wgrad(const LinDesc& d, int n_nodes, const float* x, const float* dy, float* dW, int accumulate,
                         cudaStream_t st);
 

@@ -124,10 +124,19 @@ class B200SevenNet:
     SORT_MIN_ATOMS = 4096
 
     @staticmethod
-    def cell_order(pos, cell, cutoff):
+    def cell_order(pos, cell, cutoff, pbc=None):
         """Permutation that puts the atoms in cell-list order (bins of about one cutoff in fractional coordinates):
         neighbours of consecutive atoms overlap, so the x[src] gathers and the d x[src] RED.ADD scatter of the
-        convolution kernels stay in L2.  What LAMMPS' `atom_modify sort` does for the reference's pair styles."""
+        convolution kernels stay in L2.  What LAMMPS' `atom_modify sort` does for the reference's pair styles.
+        Fully periodic cells on the device: the binning kernel of the brick decomposition with ONE brick
+        (`b200_partition_keys`; the inverse cell is formed on the host) and one sort of its keys."""
+        if pos.is_cuda and pbc is not None and all(bool(b) for b in np.asarray(pbc).reshape(3)):
+            from .parallel import cell_heights
+            hc = np.asarray(cell, np.float64).reshape(3, 3)
+            hts = cell_heights(hc)
+            nbins = [max(1, int(hts[a] / cutoff)) for a in range(3)]
+            key = ops.partition_keys(pos, np.linalg.inv(hc), (1, 1, 1), (0, 0, 0), cutoff / hts, nbins)
+            return torch.sort(key, stable=True)[1]
         h = torch.as_tensor(np.asarray(cell, np.float64).reshape(3, 3), device=pos.device)
         frac = torch.linalg.solve(h.T, pos.T).T
         frac = frac - torch.floor(frac)
@@ -147,7 +156,7 @@ class B200SevenNet:
         (internal index -> caller's index)."""
         perm = None
         if sort_atoms and pos.shape[0] >= self.SORT_MIN_ATOMS:
-            perm = self.cell_order(pos, cell, self.config['cutoff'])
+            perm = self.cell_order(pos, cell, self.config['cutoff'], pbc)
             pos, types = pos[perm].contiguous(), types[perm].contiguous()
         g = ops.radius_graph(pos, cell, pbc, self.config['cutoff'])
         e, ae, f, vir = self.compute(types, g['rowptr'], g['src'], g['dst'], g['edge_vec'])
