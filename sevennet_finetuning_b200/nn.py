@@ -18,6 +18,7 @@ libsevennet_b200.so (the edge embedding's second derivatives are dual-number eva
 the reference.
 """
 import math
+import os
 from collections import OrderedDict
 
 import torch
@@ -98,8 +99,7 @@ def _num_structures(data):
 
 # train() mode: weight_nn through a table over the edge length rebuilt from the current parameters every forward
 # (csrc/table_train.cu) instead of one network evaluation per edge.  B200_TRAIN_TABLE=0 restores the per-edge network.
-import os as _os
-_TRAIN_TABLE = _os.environ.get('B200_TRAIN_TABLE', '1') != '0'
+_TRAIN_TABLE = os.environ.get('B200_TRAIN_TABLE', '1') != '0'
 
 
 def _second_order(module):
