@@ -58,7 +58,7 @@ def test_deployed_file_runs_without_the_python_package(weights, tmp_path):
         n = len(g['pos'])
         for key in ('False', 'True'):
             o = res[key]
-            etol = max(1e-6, 2.0 * float(np.spacing(np.float32(abs(o['e'])))) / n)
+            etol = max(1e-6, 3.0 * float(np.spacing(np.float32(abs(o["e"])))) / n)
             assert abs(o['e'] - float(g['ref_energy'])) / n <= etol and abs(o['e'] - float(g['o64_energy'])) / n <= etol
             # fp32 positions in the dict (as LAMMPS passes them): 4e-5 eV/A, see test_deployed_serial_form_matches_golden
             assert np.abs(np.array(o['f']) - g['ref_force']).max() <= 4e-5 and np.abs(np.array(o['f']) - g['o64_force']).max() <= 4e-5

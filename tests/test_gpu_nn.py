@@ -535,8 +535,10 @@ def test_deployed_serial_form_matches_golden(twin, gold, name):
         e = float(out['inferred_total_energy'].reshape(-1)[0])
         f = out['inferred_force'].detach().cpu().numpy()
         s = out['inferred_stress'].detach().cpu().numpy().reshape(-1)
-        # 1e-6 eV/atom, but never tighter than two fp32 ulps of the total energy (96 atoms at -972 eV: one ulp = 6.4e-7 eV/atom)
-        etol = max(1e-6, 2.0 * float(np.spacing(np.float32(abs(e)))) / n)
+        # 1e-6 eV/atom, but never tighter than three fp32 ulps of the total energy (96 atoms at -972 eV: one ulp = 6.4e-7
+        # eV/atom; Si-216 at -1158.7 eV: 1e-6 eV/atom is 1.8 ulp, and the shuffled / batched variants reach the total through a
+        # different summation order - 1 run in 6 landed 2.16 ulp from the float64 value)
+        etol = max(1e-6, 3.0 * float(np.spacing(np.float32(abs(e)))) / n)
         assert abs(e - float(g['ref_energy'])) / n <= etol and abs(e - float(g['o64_energy'])) / n <= etol
         # fp32 positions: an edge vector carries ~2e-6 A of rounding before anything is computed (the reference's frozen graph,
         # fed the same dict, sits 1-2e-5 eV/A from float64 for the same reason), hence 4e-5 against both
